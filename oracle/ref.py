@@ -1,0 +1,154 @@
+"""ORACLE / TEST INFRASTRUCTURE ONLY -- ctypes loader for oracle/_ref/libcofhe_ref.so.
+
+The library is the UNMODIFIED reference (CoFHE CPUCryptoSystem + BICYCL + system libgmp) behind the tiny
+C ABI of oracle/ref_capi.cpp.  Only tests/, tools/gen_golden.py, __graft_entry__.build()/smoke() and
+bench.py's cpu_baseline / --impl reference legs may import this module.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libcofhe_ref.so")
+
+
+def available():
+    if not os.path.exists(LIB_PATH):
+        return False
+    try:
+        _load()
+        return True
+    except OSError:
+        return False
+
+
+_lib = None
+
+
+def _load():
+    global _lib
+    if _lib is None:
+        lib = ctypes.CDLL(LIB_PATH)
+        lib.ref_new.restype = ctypes.c_void_p
+        lib.ref_new.argtypes = [ctypes.c_uint, ctypes.c_uint]
+        lib.ref_free.argtypes = [ctypes.c_void_p]
+        lib.ref_call.restype = ctypes.c_void_p
+        lib.ref_call.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_char_p]
+        lib.ref_free_str.argtypes = [ctypes.c_void_p]
+        lib.ref_num_threads.restype = ctypes.c_int
+        lib.ref_set_threads.argtypes = [ctypes.c_int]
+        u32p = ctypes.c_void_p
+        lib.ref_bulk_matadd.restype = ctypes.c_double
+        lib.ref_bulk_matadd.argtypes = [ctypes.c_void_p, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint,
+                                        u32p, u32p, u32p, ctypes.c_uint, ctypes.c_uint]
+        lib.ref_bulk_scal_matmul.restype = ctypes.c_double
+        lib.ref_bulk_scal_matmul.argtypes = [ctypes.c_void_p, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint,
+                                             ctypes.c_uint, ctypes.c_char_p, u32p, u32p, ctypes.c_uint,
+                                             ctypes.c_uint]
+        lib.ref_bulk_encrypt.restype = ctypes.c_double
+        lib.ref_bulk_encrypt.argtypes = [ctypes.c_void_p, ctypes.c_uint, u32p, ctypes.c_uint, u32p,
+                                         ctypes.c_uint, u32p, ctypes.c_uint, ctypes.c_uint]
+        lib.ref_bulk_part_decrypt.restype = ctypes.c_double
+        lib.ref_bulk_part_decrypt.argtypes = [ctypes.c_void_p, ctypes.c_uint, ctypes.c_char_p, u32p, u32p,
+                                              ctypes.c_uint, ctypes.c_uint]
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class Reference:
+    """One reference CPUCryptoSystem(nbits, k) (default-seeded RandGen, deterministic) plus a key pair."""
+
+    def __init__(self, nbits=128, k=128):
+        self.lib = _load()
+        self.h = self.lib.ref_new(nbits, k)
+        if not self.h:
+            raise RuntimeError("reference constructor failed")
+        self.nbits, self.k = nbits, k
+
+    def close(self):
+        if self.h:
+            self.lib.ref_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def call(self, op, *args):
+        flat = []
+        for a in args:
+            if isinstance(a, (list, tuple)):
+                flat.extend(_flatten(a))
+            else:
+                flat.append(a)
+        s = " ".join(str(int(x)) for x in flat).encode()
+        p = self.lib.ref_call(self.h, op.encode(), s)
+        out = ctypes.string_at(p).decode()
+        self.lib.ref_free_str(p)
+        if not out.startswith("OK"):
+            raise RuntimeError("reference %s: %s" % (op, out))
+        return [int(t) for t in out[2:].split()]
+
+    def params(self):
+        v = self.call("params")
+        names = ["N", "DeltaK", "Delta", "k", "exponent_bound", "d", "e"]
+        p = dict(zip(names, v[:7]))
+        p["h"] = tuple(v[7:10]); p["h_e"] = tuple(v[10:13]); p["h_d"] = tuple(v[13:16]); p["h_de"] = tuple(v[16:19])
+        p["L"] = v[19]; p["large_message"] = bool(v[20]); p["secretkey_bound"] = v[21]; p["cleartext_bound"] = v[22]
+        return p
+
+    def threads(self):
+        return self.lib.ref_num_threads()
+
+    def set_threads(self, n):
+        self.lib.ref_set_threads(int(n))
+
+    # ---- bulk workloads (see ref_capi.cpp) -------------------------------------------------------
+    def bulk_matadd(self, rows, cols, iters, na=0, nc=0, export=False):
+        n = rows * cols
+        bufs = [np.zeros((2, 2 * na + nc, n), dtype=np.uint32) for _ in range(3)] if export else [None] * 3
+        dt = self.lib.ref_bulk_matadd(self.h, rows, cols, iters, _ptr(bufs[0]), _ptr(bufs[1]), _ptr(bufs[2]), na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_matadd failed")
+        return dt, bufs
+
+    def bulk_scal_matmul(self, n, m, p, iters=1, scalars=None, na=0, nc=0, export=False):
+        bi = np.zeros((2, 2 * na + nc, n * m), dtype=np.uint32) if export else None
+        bo = np.zeros((2, 2 * na + nc, n * p), dtype=np.uint32) if export else None
+        s = None if scalars is None else " ".join(str(int(x)) for x in scalars).encode()
+        dt = self.lib.ref_bulk_scal_matmul(self.h, n, m, p, iters, s, _ptr(bi), _ptr(bo), na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_scal_matmul failed")
+        return dt, bi, bo
+
+    def bulk_encrypt(self, count, nm, nr, na, nc):
+        mo = np.zeros((nm, count), dtype=np.uint32)
+        ro = np.zeros((nr, count), dtype=np.uint32)
+        co = np.zeros((2, 2 * na + nc, count), dtype=np.uint32)
+        dt = self.lib.ref_bulk_encrypt(self.h, count, _ptr(mo), nm, _ptr(ro), nr, _ptr(co), na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_encrypt failed")
+        return dt, mo, ro, co
+
+    def bulk_part_decrypt(self, count, share, na, nc):
+        co = np.zeros((2, 2 * na + nc, count), dtype=np.uint32)
+        do = np.zeros((2 * na + nc, count), dtype=np.uint32)
+        dt = self.lib.ref_bulk_part_decrypt(self.h, count, str(int(share)).encode(), _ptr(co), _ptr(do), na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_part_decrypt failed")
+        return dt, co, do
+
+
+def _flatten(a):
+    for x in a:
+        if isinstance(x, (list, tuple)):
+            yield from _flatten(x)
+        else:
+            yield x
