@@ -1,0 +1,46 @@
+"""TEST INFRASTRUCTURE: builds and loads tests/_hostsim/libhostsim.so (the device headers compiled with g++)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+OUT = os.path.join(ROOT, "tests", "_hostsim")
+LIB = os.path.join(OUT, "libhostsim.so")
+SRC = os.path.join(HERE, "hostsim.cpp")
+CSRC = os.path.join(ROOT, "cofhe_b200", "csrc")
+
+_lib = None
+
+
+def _stale():
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    deps = [SRC, os.path.join(HERE, "hostsim_extra.inc")] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if _stale():
+            os.makedirs(OUT, exist_ok=True)
+            subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function",
+                                   "-I" + CSRC, "-I" + HERE, "-o", LIB, SRC])
+        _lib = ctypes.CDLL(LIB)
+    return _lib
+
+
+def P(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def cap_for(nd):
+    need = 2 * nd + 4
+    for c in (32, 48, 136, 216):
+        if c >= need:
+            return c
+    raise ValueError("discriminant too large")
