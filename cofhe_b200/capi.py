@@ -1,0 +1,55 @@
+"""ctypes binding of the C ABI (include/cofhe_b200.h).  Loading fails loudly when the CUDA library has not been
+built; there is no CPU fallback anywhere in this package."""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libcofhe_b200.so")
+
+OK, EINVAL, ECUDA, EARITH, ENOMEM, ESTATE = 0, 1, 2, 3, 4, 5
+_NAMES = {1: "EINVAL", 2: "ECUDA", 3: "EARITH", 4: "ENOMEM", 5: "ESTATE"}
+
+
+class CofheError(RuntimeError):
+    def __init__(self, code, what):
+        super().__init__("cofhe_b200: %s failed with %s" % (what, _NAMES.get(code, code)))
+        self.code = code
+
+
+_lib = None
+vp, u32, i32, sz, u64 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int, ctypes.c_size_t, ctypes.c_uint64
+
+SIGNATURES = {
+    "cofhe_b200_version": (ctypes.c_char_p, []),
+    "cofhe_b200_create": (i32, [ctypes.POINTER(vp), i32, vp, u32]),
+    "cofhe_b200_destroy": (None, [vp]),
+    "cofhe_b200_shape": (i32, [vp, ctypes.POINTER(u32), ctypes.POINTER(u32), ctypes.POINTER(u32)]),
+    "cofhe_b200_status": (i32, [vp, vp]),
+    "cofhe_b200_launch_count": (u64, [vp]),
+    "cofhe_b200_nucomp": (i32, [vp, sz, vp, vp, vp, i32, vp]),
+    "cofhe_b200_nudupl": (i32, [vp, sz, vp, vp, vp]),
+    "cofhe_b200_reduce": (i32, [vp, sz, vp, u32, u32, vp, vp]),
+    "cofhe_b200_nupow": (i32, [vp, sz, vp, vp, u32, i32, vp, i32, vp, vp]),
+    "cofhe_b200_add_ciphertexts": (i32, [vp, sz, vp, vp, vp, vp]),
+    "cofhe_b200_add_ciphertexts_host": (i32, [vp, sz, vp, vp, vp]),
+}
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("cofhe_b200: %s is missing -- build it with `python -m cofhe_b200.build` "
+                              "(nvcc, sm_100a); there is no CPU fallback" % LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc, what):
+    if rc != OK:
+        raise CofheError(rc, what)

@@ -1,0 +1,274 @@
+// cofhe_b200 -- CUDA kernels and the C ABI (include/cofhe_b200.h).  sm_100a only.
+//
+// One thread owns one form operation (independent elements of a batch).  Buffers are
+// structure-of-arrays limbs so that a warp's loads/stores of one limb row are one coalesced 128-byte line.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+
+#include "cofhe_b200.h"
+#include "ops.cuh"
+
+using namespace cofhe;
+
+struct cofhe_b200_ctx {
+  int device;
+  int cap;            // capacity class of the generic integer layer
+  u32 na, nc, nd;
+  void *d_group;      // Group<CAP> in device memory
+  int *d_err;         // sticky per-context element status (max of Err codes)
+  cudaStream_t xfer;  // internal stream of the _host entry points
+  uint64_t launches;
+};
+
+namespace {
+
+constexpr int kBlock = 128;
+
+#define CUDA_TRY(x)                                   \
+  do {                                                \
+    cudaError_t _e = (x);                             \
+    if (_e != cudaSuccess) return COFHE_B200_ECUDA;   \
+  } while (0)
+
+#define CAP_DISPATCH(cap, ...)                                   \
+  switch (cap) {                                                 \
+    case 32: { constexpr int CAP = 32; __VA_ARGS__; } break;     \
+    case 48: { constexpr int CAP = 48; __VA_ARGS__; } break;     \
+    case 136: { constexpr int CAP = 136; __VA_ARGS__; } break;   \
+    case 216: { constexpr int CAP = 216; __VA_ARGS__; } break;   \
+    default: return COFHE_B200_EINVAL;                           \
+  }
+
+int cap_for(u32 nd) {
+  u32 need = 2 * nd + 4;
+  const int caps[] = {32, 48, 136, 216};
+  for (int c : caps)
+    if ((u32)c >= need) return c;
+  return 0;
+}
+
+inline unsigned grid_for(size_t n) { return (unsigned)((n + kBlock - 1) / kBlock); }
+
+// grid.y selects the form block inside a ciphertext batch (0: c1, 1: c2); plain form batches use grid.y == 1
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_compose(const Group<CAP> *G, Shape s, size_t n, const u32 *in1, const u32 *in2,
+                                                    u32 *out, int neg2, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  size_t off = (size_t)blockIdx.y * form_limbs(s) * n;
+  int c = op_compose<CAP>(*G, s, n, idx, in1 + off, in2 + off, out + off, neg2 != 0);
+  if (c) atomicMax(err, c);
+}
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_square(const Group<CAP> *G, Shape s, size_t n, const u32 *in, u32 *out, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  size_t off = (size_t)blockIdx.y * form_limbs(s) * n;
+  int c = op_square<CAP>(*G, s, n, idx, in + off, out + off);
+  if (c) atomicMax(err, c);
+}
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_reduce(const Group<CAP> *G, Shape sin, Shape sout, size_t n, const u32 *in, u32 *out,
+                                                   int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  int c = op_reduce<CAP>(*G, sin, sout, n, idx, in, out);
+  if (c) atomicMax(err, c);
+}
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_pow(const Group<CAP> *G, Shape s, size_t n, const u32 *in, u32 *out, const u32 *exp,
+                                                int el, int per_elem, const unsigned char *expneg, int shared_neg, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  size_t off = (size_t)blockIdx.y * form_limbs(s) * n;
+  int c = op_pow<CAP>(*G, s, n, idx, in + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
+  if (c) atomicMax(err, c);
+}
+
+int check_launch(cofhe_b200_ctx *ctx) {
+  ctx->launches++;
+  return cudaGetLastError() == cudaSuccess ? COFHE_B200_OK : COFHE_B200_ECUDA;
+}
+
+struct DevGuard {
+  int prev;
+  bool ok;
+  explicit DevGuard(int dev) : prev(-1), ok(false) {
+    if (cudaGetDevice(&prev) != cudaSuccess) return;
+    ok = (prev == dev) || cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DevGuard() { if (ok && prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+extern "C" {
+
+const char *cofhe_b200_version(void) { return "cofhe_b200 0.1 sm_100a"; }
+
+int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delta, uint32_t nd) {
+  if (!out || !abs_delta || nd == 0) return COFHE_B200_EINVAL;
+  *out = nullptr;
+  u32 n = (u32)bn_norm(abs_delta, (int)nd);
+  if (n == 0) return COFHE_B200_EINVAL;
+  int cap = cap_for(n);
+  if (!cap) return COFHE_B200_EINVAL;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return COFHE_B200_ECUDA;
+  DevGuard g(device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cofhe_b200_ctx *ctx = new (std::nothrow) cofhe_b200_ctx();
+  if (!ctx) return COFHE_B200_ENOMEM;
+  ctx->device = device;
+  ctx->cap = cap;
+  ctx->nd = n;
+  int dbits = bn_bits(abs_delta, (int)n);
+  ctx->na = (u32)((dbits / 2 + 1 + 31) / 32);
+  ctx->nc = n;
+  ctx->launches = 0;
+  ctx->d_group = nullptr;
+  ctx->d_err = nullptr;
+  ctx->xfer = nullptr;
+  int rc = COFHE_B200_OK;
+  CAP_DISPATCH(cap, {
+    Group<CAP> *G = new (std::nothrow) Group<CAP>();
+    if (!G) { delete ctx; return COFHE_B200_ENOMEM; }
+    memset(G, 0, sizeof(*G));
+    G->absD.n = (int)n; G->absD.neg = 0;
+    for (u32 i = 0; i < n; i++) G->absD.d[i] = abs_delta[i];
+    G->dbits = dbits;
+    if (cudaMalloc(&ctx->d_group, sizeof(*G)) != cudaSuccess ||
+        cudaMemcpy(ctx->d_group, G, sizeof(*G), cudaMemcpyHostToDevice) != cudaSuccess)
+      rc = COFHE_B200_ECUDA;
+    delete G;
+  })
+  if (rc == COFHE_B200_OK && (cudaMalloc(&ctx->d_err, sizeof(int)) != cudaSuccess ||
+                              cudaMemset(ctx->d_err, 0, sizeof(int)) != cudaSuccess ||
+                              cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking) != cudaSuccess))
+    rc = COFHE_B200_ECUDA;
+  if (rc != COFHE_B200_OK) { cofhe_b200_destroy(ctx); return rc; }
+  *out = ctx;
+  return COFHE_B200_OK;
+}
+
+void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
+  if (!ctx) return;
+  DevGuard g(ctx->device);
+  if (ctx->d_group) cudaFree(ctx->d_group);
+  if (ctx->d_err) cudaFree(ctx->d_err);
+  if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
+  delete ctx;
+}
+
+int cofhe_b200_shape(const cofhe_b200_ctx *ctx, uint32_t *na, uint32_t *nc, uint32_t *nd) {
+  if (!ctx) return COFHE_B200_EINVAL;
+  if (na) *na = ctx->na;
+  if (nc) *nc = ctx->nc;
+  if (nd) *nd = ctx->nd;
+  return COFHE_B200_OK;
+}
+
+int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream) {
+  if (!ctx) return COFHE_B200_EINVAL;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  int h = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemcpyAsync(&h, ctx->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  if (h) {
+    CUDA_TRY(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return COFHE_B200_EARITH;
+  }
+  return COFHE_B200_OK;
+}
+
+uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int cofhe_b200_nucomp(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f1, const uint32_t *f2, uint32_t *out, int negf2,
+                      void *stream) {
+  if (!ctx || (n && (!f1 || !f2 || !out))) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  CAP_DISPATCH(ctx->cap, k_compose<CAP><<<dim3(grid_for(n), 1), kBlock, 0, (cudaStream_t)stream>>>(
+                             (const Group<CAP> *)ctx->d_group, s, n, f1, f2, out, negf2, ctx->d_err))
+  return check_launch(ctx);
+}
+
+int cofhe_b200_nudupl(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!f || !out))) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  CAP_DISPATCH(ctx->cap, k_square<CAP><<<dim3(grid_for(n), 1), kBlock, 0, (cudaStream_t)stream>>>(
+                             (const Group<CAP> *)ctx->d_group, s, n, f, out, ctx->d_err))
+  return check_launch(ctx);
+}
+
+int cofhe_b200_reduce(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t na_in, uint32_t nc_in, uint32_t *out,
+                      void *stream) {
+  if (!ctx || (n && (!f || !out)) || na_in == 0 || nc_in == 0) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape sin{(int)na_in, (int)nc_in}, sout{(int)ctx->na, (int)ctx->nc};
+  CAP_DISPATCH(ctx->cap, k_reduce<CAP><<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>((const Group<CAP> *)ctx->d_group, sin,
+                                                                                         sout, n, f, out, ctx->d_err))
+  return check_launch(ctx);
+}
+
+int cofhe_b200_nupow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, const uint32_t *exp, uint32_t el, int per_elem,
+                     const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!f || !out || !exp)) || el == 0) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  CAP_DISPATCH(ctx->cap, k_pow<CAP><<<dim3(grid_for(n), 1), kBlock, 0, (cudaStream_t)stream>>>(
+                             (const Group<CAP> *)ctx->d_group, s, n, f, out, exp, (int)el, per_elem, expneg, shared_neg,
+                             ctx->d_err))
+  return check_launch(ctx);
+}
+
+int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
+                               void *stream) {
+  if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  CAP_DISPATCH(ctx->cap, k_compose<CAP><<<dim3(grid_for(n), 2), kBlock, 0, (cudaStream_t)stream>>>(
+                             (const Group<CAP> *)ctx->d_group, s, n, ct1, ct2, out, 0, ctx->d_err))
+  return check_launch(ctx);
+}
+
+int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
+                                    uint32_t *out) {
+  if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  size_t bytes = (size_t)2 * (2 * ctx->na + ctx->nc) * n * sizeof(u32);
+  u32 *d1 = nullptr, *d2 = nullptr, *d3 = nullptr;
+  int rc = COFHE_B200_OK;
+  if (cudaMalloc(&d1, bytes) != cudaSuccess || cudaMalloc(&d2, bytes) != cudaSuccess || cudaMalloc(&d3, bytes) != cudaSuccess)
+    rc = COFHE_B200_ENOMEM;
+  if (rc == COFHE_B200_OK && (cudaMemcpyAsync(d1, ct1, bytes, cudaMemcpyHostToDevice, ctx->xfer) != cudaSuccess ||
+                              cudaMemcpyAsync(d2, ct2, bytes, cudaMemcpyHostToDevice, ctx->xfer) != cudaSuccess))
+    rc = COFHE_B200_ECUDA;
+  if (rc == COFHE_B200_OK) rc = cofhe_b200_add_ciphertexts(ctx, n, d1, d2, d3, ctx->xfer);
+  if (rc == COFHE_B200_OK && cudaMemcpyAsync(out, d3, bytes, cudaMemcpyDeviceToHost, ctx->xfer) != cudaSuccess)
+    rc = COFHE_B200_ECUDA;
+  if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->xfer);
+  else cudaStreamSynchronize(ctx->xfer);
+  cudaFree(d1); cudaFree(d2); cudaFree(d3);
+  return rc;
+}
+
+}  // extern "C"

@@ -47,13 +47,14 @@ QF_HDN int op_square(const Group<CAP> &G, const Shape &s, size_t n, size_t idx, 
   return e.code;
 }
 template <int CAP>
-QF_HDN int op_reduce(const Group<CAP> &G, const Shape &s, size_t n, size_t idx, const u32 *in, u32 *out) {
+QF_HDN int op_reduce(const Group<CAP> &G, const Shape &sin, const Shape &sout, size_t n, size_t idx, const u32 *in,
+                     u32 *out) {
   (void)G;
   Err e; e.code = 0;
   Form<CAP> f;
-  form_load(e, f, in, s, n, idx);
+  form_load(e, f, in, sin, n, idx);
   qf_reduce(e, f);
-  form_store(e, f, out, s, n, idx);
+  form_store(e, f, out, sout, n, idx);
   return e.code;
 }
 // out[idx] = in[idx]^exp; exponent magnitude has el limbs; per_elem: exp is [el][n] (limb-major), sign in

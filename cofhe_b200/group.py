@@ -1,0 +1,128 @@
+"""Host-side handle on a class group living on one B200: thin Python mirror of the reference's
+BICYCL::ClassGroup batched over SoA limb tensors (torch is used only for device memory and streams)."""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import capi
+from . import limbs as L
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def to_device(arr, device):
+    """numpy uint32 -> torch int32 on device (bit pattern preserved)."""
+    return torch.from_numpy(np.ascontiguousarray(arr).view(np.int32)).to(device, non_blocking=False)
+
+
+def to_host(t):
+    return t.detach().cpu().numpy().view(np.uint32)
+
+
+class ClassGroupB200:
+    """Class group of discriminant D < 0 on CUDA device `device`."""
+
+    def __init__(self, D, device=0):
+        if D >= 0:
+            raise ValueError("discriminant must be negative")
+        if not torch.cuda.is_available():
+            raise RuntimeError("cofhe_b200 needs a CUDA device (no CPU fallback)")
+        self.lib = capi.load()
+        self.D = int(D)
+        self.device = torch.device("cuda", device)
+        nd = ((-D).bit_length() + 31) // 32
+        dl = L.ints_to_limbs([-D], nd)[:, 0].copy()
+        h = ctypes.c_void_p()
+        capi.check(self.lib.cofhe_b200_create(ctypes.byref(h), device, dl.ctypes.data_as(ctypes.c_void_p), nd), "create")
+        self.h = h
+        na, nc, nd2 = ctypes.c_uint32(), ctypes.c_uint32(), ctypes.c_uint32()
+        capi.check(self.lib.cofhe_b200_shape(self.h, ctypes.byref(na), ctypes.byref(nc), ctypes.byref(nd2)), "shape")
+        self.na, self.nc, self.nd = na.value, nc.value, nd2.value
+        self.fl = 2 * self.na + self.nc
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.cofhe_b200_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- marshalling -----------------------------------------------------------------------------
+    def forms(self, fs):
+        return to_device(L.forms_to_limbs(fs, self.na, self.nc), self.device)
+
+    def cts(self, cs):
+        return to_device(L.cts_to_limbs(cs, self.na, self.nc), self.device)
+
+    def forms_out(self, t):
+        return L.limbs_to_forms(to_host(t), self.na, self.nc)
+
+    def cts_out(self, t):
+        return L.limbs_to_cts(to_host(t), self.na, self.nc)
+
+    def status(self):
+        capi.check(self.lib.cofhe_b200_status(self.h, _stream()), "status")
+
+    def launches(self):
+        return int(self.lib.cofhe_b200_launch_count(self.h))
+
+    # ---- batched form arithmetic (device tensors in, device tensors out) ------------------------------
+    def nucomp(self, f1, f2, negf2=False, out=None):
+        n = f1.shape[-1]
+        out = torch.empty_like(f1) if out is None else out
+        capi.check(self.lib.cofhe_b200_nucomp(self.h, n, _ptr(f1), _ptr(f2), _ptr(out), int(negf2), _stream()), "nucomp")
+        return out
+
+    def nudupl(self, f, out=None):
+        n = f.shape[-1]
+        out = torch.empty_like(f) if out is None else out
+        capi.check(self.lib.cofhe_b200_nudupl(self.h, n, _ptr(f), _ptr(out), _stream()), "nudupl")
+        return out
+
+    def reduce(self, f, na_in, nc_in):
+        n = f.shape[-1]
+        out = torch.empty((self.fl, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_reduce(self.h, n, _ptr(f), na_in, nc_in, _ptr(out), _stream()), "reduce")
+        return out
+
+    def nupow(self, f, exps=None, shared=None):
+        """exps: list of ints (per element) or shared: one int."""
+        n = f.shape[-1]
+        out = torch.empty_like(f)
+        if shared is not None:
+            el = max(1, (abs(shared).bit_length() + 31) // 32)
+            ex = to_device(L.ints_to_limbs([abs(shared)], el)[:, 0].copy(), self.device)
+            capi.check(self.lib.cofhe_b200_nupow(self.h, n, _ptr(f), _ptr(ex), el, 0, None, int(shared < 0), _ptr(out),
+                                                 _stream()), "nupow")
+        else:
+            el = max(1, max((abs(e).bit_length() + 31) // 32 for e in exps))
+            ex = to_device(L.ints_to_limbs([abs(e) for e in exps], el), self.device)
+            sg = torch.tensor([1 if e < 0 else 0 for e in exps], dtype=torch.uint8, device=self.device)
+            capi.check(self.lib.cofhe_b200_nupow(self.h, n, _ptr(f), _ptr(ex), el, 1, _ptr(sg), 0, _ptr(out), _stream()),
+                       "nupow")
+        return out
+
+    def add_ciphertexts(self, ct1, ct2, out=None):
+        n = ct1.shape[-1]
+        out = torch.empty_like(ct1) if out is None else out
+        capi.check(self.lib.cofhe_b200_add_ciphertexts(self.h, n, _ptr(ct1), _ptr(ct2), _ptr(out), _stream()), "add")
+        return out
+
+    def add_ciphertexts_host(self, ct1, ct2, out):
+        """numpy uint32 host buffers [2, fl, n]; transfers happen inside the call."""
+        n = ct1.shape[-1]
+        vp = ctypes.c_void_p
+        capi.check(self.lib.cofhe_b200_add_ciphertexts_host(self.h, n, ct1.ctypes.data_as(vp), ct2.ctypes.data_as(vp),
+                                                            out.ctypes.data_as(vp)), "add_host")
+        return out

@@ -1,0 +1,87 @@
+/* cofhe_b200 -- C ABI of the B200-native backend for CoFHE's data-parallel ciphertext hot path
+ * (batched arithmetic on binary quadratic forms of a class group: CL_HSM2k over an imaginary quadratic order).
+ *
+ * The reference has no FFI: its seam is the C++ class CPUCryptoSystem used as a template argument
+ * (reference include/x86_64/cpu_cryptosystem.hpp:23-172).  The drop-in class for that seam is
+ * include/cuda/cuda_cryptosystem.hpp (it replaces the reference's 3-line "#error" stub of the same path); it
+ * marshals Tensor<CipherText*> into the buffers below and calls these entry points.  Each entry point cites the
+ * reference code whose results it reproduces bit for bit.
+ *
+ * Layout.  All big integers cross this ABI as structure-of-arrays 32-bit limbs, limb-major / element-minor:
+ * limb i of element e of an n-element batch is word [i*n + e].  Limbs are little endian; `b` coefficients are
+ * two's complement over their limbs.  A batch of forms is  a[na] | b[na] | c[nc]  = (2*na+nc) limb rows of n words;
+ * a batch of ciphertexts is c1-forms followed by c2-forms: [2][2*na+nc][n].  (na, nc) come from
+ * cofhe_b200_shape(): na = ceil((bits(|D|)/2 + 1)/32) holds every reduced a and b; nc = ceil(bits(|D|)/32)
+ * holds every reduced c.  Exponents/scalars are magnitudes [el][n] plus an optional sign byte per element.
+ *
+ * Pointers.  Entry points without suffix take DEVICE pointers and a CUDA stream (cudaStream_t passed as
+ * void*; NULL = legacy default stream) and are asynchronous.  Entry points ending in _host take HOST
+ * pointers, do the transfers on an internal stream and return when the result is in the output buffer.
+ *
+ * Errors.  Every call returns a COFHE_B200_* code; nothing throws across this boundary.  Arithmetic failures
+ * of individual elements (operand not a form of this discriminant, value outside the limb shape) are
+ * sticky per context: cofhe_b200_status() synchronises the stream and reports/clears them; _host calls
+ * report them directly.  There is NO CPU fallback: without a CUDA device every call fails with
+ * COFHE_B200_ECUDA.
+ */
+#ifndef COFHE_B200_H
+#define COFHE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define COFHE_B200_OK 0
+#define COFHE_B200_EINVAL 1 /* bad argument / shape mismatch (reference: std::invalid_argument) */
+#define COFHE_B200_ECUDA 2  /* CUDA runtime failure, or no device */
+#define COFHE_B200_EARITH 3 /* an element failed: not a form of this discriminant / does not fit the limb shape */
+#define COFHE_B200_ENOMEM 4
+#define COFHE_B200_ESTATE 5 /* scheme parameters / public key not set for an operation that needs them */
+
+typedef struct cofhe_b200_ctx cofhe_b200_ctx;
+
+/* Library self-description: "cofhe_b200 <version> sm_100a". */
+const char *cofhe_b200_version(void);
+
+/* Class group of discriminant D = -abs_delta (nd limbs) on CUDA device `device`.
+ * Replaces BICYCL::ClassGroup(D) (reference thirdparty/bicycl/src/bicycl/qfi.inl:1293-1331). */
+int cofhe_b200_create(cofhe_b200_ctx **ctx, int device, const uint32_t *abs_delta, uint32_t nd);
+void cofhe_b200_destroy(cofhe_b200_ctx *ctx);
+/* Limb shape of form buffers for this context. */
+int cofhe_b200_shape(const cofhe_b200_ctx *ctx, uint32_t *na, uint32_t *nc, uint32_t *nd);
+/* Synchronise `stream`, return COFHE_B200_EARITH if any element failed since the last call, then clear. */
+int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream);
+/* Number of kernel launches issued through this context so far (bench.py reports it as gpu_launches). */
+uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx);
+
+/* out[e] = f1[e] o f2[e]   (negf2 != 0: f1[e] o f2[e]^-1), reduced.
+ * ClassGroup::nucomp / nucompinv (qfi.inl:1441-1451 -> QFI::nucomp qfi.inl:683-818). */
+int cofhe_b200_nucomp(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f1, const uint32_t *f2, uint32_t *out, int negf2,
+                      void *stream);
+/* out[e] = f[e]^2, reduced.  ClassGroup::nudupl (qfi.inl:1453-1471 -> QFI::nudupl qfi.inl:861-955). */
+int cofhe_b200_nudupl(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *out, void *stream);
+/* out[e] = the reduced form equivalent to f[e] (QFI::reduction, qfi.inl:523-548).  Input rows may be wider
+ * than the context shape (unreduced forms): a/b have na_in limbs, c has nc_in limbs; output uses the context shape. */
+int cofhe_b200_reduce(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t na_in, uint32_t nc_in, uint32_t *out,
+                      void *stream);
+/* out[e] = f[e]^x.  per_elem != 0: x = exp[.][e] (el limb rows) with sign expneg[e] (NULL = all positive);
+ * per_elem == 0: one shared exponent exp[0..el) (device memory) with sign shared_neg.
+ * ClassGroup::nupow (qfi.inl:1473-1477 -> QFI::nupow qfi.inl:977-1064): x == 0 gives the neutral form, x < 0 gives
+ * QFI::neg of f^|x|. */
+int cofhe_b200_nupow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, const uint32_t *exp, uint32_t el, int per_elem,
+                     const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream);
+
+/* out[e] = ct1[e] + ct2[e] (homomorphic add, no re-randomisation): c1 o c1', c2 o c2'.
+ * CPUCryptoSystem::add_ciphertext_tensors / add_ciphertext_vectors
+ * (reference include/x86_64/cpu_cryptosystem_tensor_ops.inl:197-267, cpu_cryptosystem_vector_ops.inl:58-120). */
+int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
+                               void *stream);
+int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
+                                    uint32_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COFHE_B200_H */

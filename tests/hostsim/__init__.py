@@ -13,6 +13,7 @@ SRC = os.path.join(HERE, "hostsim.cpp")
 CSRC = os.path.join(ROOT, "cofhe_b200", "csrc")
 
 _lib = None
+EXTRA_SIGS = {}
 
 
 def _stale():
@@ -31,6 +32,18 @@ def load():
             subprocess.check_call(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wall", "-Wno-unused-function",
                                    "-I" + CSRC, "-I" + HERE, "-o", LIB, SRC])
         _lib = ctypes.CDLL(LIB)
+        vp, i, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+        sigs = {
+            "hs_compose": [i, vp, i, i, i, sz, vp, vp, vp, i],
+            "hs_square": [i, vp, i, i, i, sz, vp, vp],
+            "hs_reduce": [i, vp, i, i, i, i, i, sz, vp, vp],
+            "hs_pow": [i, vp, i, i, i, sz, vp, vp, vp, i, i, vp, i],
+        }
+        sigs.update(EXTRA_SIGS)
+        for name, args in sigs.items():
+            fn = getattr(_lib, name)
+            fn.restype = i
+            fn.argtypes = args
     return _lib
 
 

@@ -45,11 +45,12 @@ int hs_square(int cap, const u32 *absD, int nd, int na, int nc, size_t n, const 
   })
   return rc;
 }
-int hs_reduce(int cap, const u32 *absD, int nd, int na, int nc, size_t n, const u32 *in, u32 *out) {
+int hs_reduce(int cap, const u32 *absD, int nd, int na_in, int nc_in, int na, int nc, size_t n, const u32 *in, u32 *out) {
   int rc = 0;
   DISPATCH(cap, {
     Group<CAP> G; mk_group(G, absD, nd); Shape s{na, nc};
-    for (size_t i = 0; i < n; i++) { int c = op_reduce<CAP>(G, s, n, i, in, out); if (c && !rc) rc = c; }
+    Shape sin{na_in, nc_in};
+    for (size_t i = 0; i < n; i++) { int c = op_reduce<CAP>(G, sin, s, n, i, in, out); if (c && !rc) rc = c; }
   })
   return rc;
 }

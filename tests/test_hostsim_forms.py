@@ -41,10 +41,10 @@ class Sim:
         # unreduced inputs may need wider limbs: use nd for everything
         n = len(f)
         w = self.nd + 2
-        a, o = L.forms_to_limbs(f, w, w), np.zeros((3 * w, n), dtype=np.uint32)
-        rc = self.lib.hs_reduce(self.cap, HS.P(self.dl), self.nd, w, w, n, HS.P(a), HS.P(o))
+        a, o = L.forms_to_limbs(f, w, w), self._out(n)
+        rc = self.lib.hs_reduce(self.cap, HS.P(self.dl), self.nd, w, w, self.na, self.nc, n, HS.P(a), HS.P(o))
         assert rc == 0, rc
-        return L.limbs_to_forms(o, w, w)
+        return L.limbs_to_forms(o, self.na, self.nc)
 
     def pow(self, f, exps):
         n = len(f)
