@@ -50,19 +50,19 @@ QF_HD int ctz32(u32 x) {
 // ------------------------------------------------------------------------------------------------
 // magnitude (mpn-like) primitives on (pointer, length); lengths are "normalised" (top limb != 0, 0 = zero)
 // ------------------------------------------------------------------------------------------------
-QF_HDN int bn_norm(const u32 *a, int n) {
+QF_HD int bn_norm(const u32 *a, int n) {
   while (n > 0 && a[n - 1] == 0) n--;
   return n;
 }
-QF_HDN int bn_cmp(const u32 *a, int na, const u32 *b, int nb) {
+QF_HD int bn_cmp(const u32 *a, int na, const u32 *b, int nb) {
   if (na != nb) return na < nb ? -1 : 1;
   for (int i = na - 1; i >= 0; i--)
     if (a[i] != b[i]) return a[i] < b[i] ? -1 : 1;
   return 0;
 }
-QF_HDN int bn_bits(const u32 *a, int na) { return na ? 32 * na - clz32(a[na - 1]) : 0; }
+QF_HD int bn_bits(const u32 *a, int na) { return na ? 32 * na - clz32(a[na - 1]) : 0; }
 // r = a + b; r may alias a or b; r must hold max(na,nb)+1 limbs
-QF_HDN int bn_add(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
+QF_HD int bn_add(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
   if (na < nb) { const u32 *t = a; a = b; b = t; int k = na; na = nb; nb = k; }
   u64 c = 0;
   int i = 0;
@@ -72,7 +72,7 @@ QF_HDN int bn_add(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
   return i;
 }
 // r = a - b, requires a >= b; r may alias a or b
-QF_HDN int bn_sub(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
+QF_HD int bn_sub(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
   i64 c = 0;
   int i = 0;
   for (; i < nb; i++) { c += (i64)a[i] - (i64)b[i]; r[i] = (u32)c; c >>= 32; }
@@ -80,7 +80,7 @@ QF_HDN int bn_sub(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
   return bn_norm(r, na);
 }
 // r = a * b (no aliasing); r holds na+nb limbs
-QF_HDN int bn_mul(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
+QF_HD int bn_mul(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
   if (na == 0 || nb == 0) return 0;
   for (int i = 0; i < na + nb; i++) r[i] = 0;
   for (int i = 0; i < na; i++) {
@@ -91,7 +91,7 @@ QF_HDN int bn_mul(u32 *r, const u32 *a, int na, const u32 *b, int nb) {
   return bn_norm(r, na + nb);
 }
 // r = a << bits (r may alias a); r holds na + bits/32 + 1 limbs
-QF_HDN int bn_shl(u32 *r, const u32 *a, int na, unsigned bits) {
+QF_HD int bn_shl(u32 *r, const u32 *a, int na, unsigned bits) {
   if (na == 0) return 0;
   int ws = bits >> 5, bs = bits & 31;
   if (bs == 0) {
@@ -105,7 +105,7 @@ QF_HDN int bn_shl(u32 *r, const u32 *a, int na, unsigned bits) {
   return bn_norm(r, na + ws + (bs ? 1 : 0));
 }
 // r = a >> bits (floor on magnitude; r may alias a)
-QF_HDN int bn_shr(u32 *r, const u32 *a, int na, unsigned bits) {
+QF_HD int bn_shr(u32 *r, const u32 *a, int na, unsigned bits) {
   int ws = bits >> 5, bs = bits & 31;
   if (ws >= na) return 0;
   int n = na - ws;
@@ -118,23 +118,22 @@ QF_HDN int bn_shr(u32 *r, const u32 *a, int na, unsigned bits) {
   return bn_norm(r, n);
 }
 // number of trailing zero bits (a != 0)
-QF_HDN int bn_ctz(const u32 *a, int na) {
+QF_HD int bn_ctz(const u32 *a, int na) {
   for (int i = 0; i < na; i++)
     if (a[i]) return 32 * i + ctz32(a[i]);
   return 0;
 }
 
 // Knuth algorithm D.  q gets na-nb+1 limbs, r gets nb limbs; `an` is scratch of na+1 limbs, `bs` of nb limbs.
-// q and r must not alias a or b.  Returns lengths through nq/nr.
+// q and r must not alias a or b.  Returns lengths through nq/nr.  Single exit on purpose (the 64-bit divisions are
+// calls on the device; see DESIGN.md "device-code rules").
 QF_HDN void bn_divrem(u32 *q, int *nq, u32 *r, int *nr, const u32 *a, int na, const u32 *b, int nb, u32 *an,
                       u32 *bs) {
   if (bn_cmp(a, na, b, nb) < 0) {
     for (int i = 0; i < na; i++) r[i] = a[i];
     *nr = na;
     *nq = 0;
-    return;
-  }
-  if (nb == 1) {
+  } else if (nb == 1) {
     u64 rem = 0;
     u32 d = b[0];
     for (int i = na - 1; i >= 0; i--) {
@@ -145,8 +144,7 @@ QF_HDN void bn_divrem(u32 *q, int *nq, u32 *r, int *nr, const u32 *a, int na, co
     r[0] = (u32)rem;
     *nr = rem ? 1 : 0;
     *nq = bn_norm(q, na);
-    return;
-  }
+  } else {
   int s = clz32(b[nb - 1]);
   if (s) {
     for (int i = nb - 1; i > 0; i--) bs[i] = (b[i] << s) | (b[i - 1] >> (32 - s));
@@ -196,6 +194,7 @@ QF_HDN void bn_divrem(u32 *q, int *nq, u32 *r, int *nr, const u32 *a, int na, co
     for (int i = 0; i < nb; i++) r[i] = an[i];
   }
   *nr = bn_norm(r, nb);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -352,20 +351,26 @@ QF_HDN void z_shr(Err &e, Z<CAP> &r, const Z<CA> &a, unsigned bits) {
 // truncated division: a = q*b + r, |r| < |b|, sign(r) = sign(a).  q, r must not alias a, b.
 template <int CAP, int CQ, int CR, int CA, int CB>
 QF_HDN void z_tdiv_qr(Err &e, Z<CQ> &q, Z<CR> &r, const Z<CA> &a, const Z<CB> &b) {
-  if (b.n == 0) { e.code = 3; q.n = r.n = 0; q.neg = r.neg = 0; return; }
-  if (a.n > CAP || b.n > CAP) { e.code = 1; q.n = r.n = 0; q.neg = r.neg = 0; return; }
-  if (bn_cmp(a.d, a.n, b.d, b.n) < 0) {
-    if (a.n > CR) { e.code = 1; q.n = r.n = 0; q.neg = r.neg = 0; return; }
+  // NB single exit on purpose: see DESIGN.md "device-code rules" (early returns around calls under divergence)
+  int mode;  // 0: error, 1: |a| < |b|, 2: divide
+  if (b.n == 0) { e.code = 3; mode = 0; }
+  else if (a.n > CAP || b.n > CAP) { e.code = 1; mode = 0; }
+  else if (bn_cmp(a.d, a.n, b.d, b.n) < 0) {
+    if (a.n > CR) { e.code = 1; mode = 0; } else mode = 1;
+  } else if (a.n - b.n + 1 > CQ || b.n > CR) { e.code = 1; mode = 0; }
+  else mode = 2;
+  if (mode == 2) {
+    u32 an[CAP + 1], bs[CAP];
+    int nq, nr;
+    bn_divrem(q.d, &nq, r.d, &nr, a.d, a.n, b.d, b.n, an, bs);
+    q.n = nq; q.neg = nq ? (a.neg ^ b.neg) : 0;
+    r.n = nr; r.neg = nr ? a.neg : 0;
+  } else if (mode == 1) {
     for (int i = 0; i < a.n; i++) r.d[i] = a.d[i];
     r.n = a.n; r.neg = a.neg; q.n = 0; q.neg = 0;
-    return;
+  } else {
+    q.n = r.n = 0; q.neg = r.neg = 0;
   }
-  if (a.n - b.n + 1 > CQ || b.n > CR) { e.code = 1; q.n = r.n = 0; q.neg = r.neg = 0; return; }
-  u32 an[CAP + 1], bs[CAP];
-  int nq, nr;
-  bn_divrem(q.d, &nq, r.d, &nr, a.d, a.n, b.d, b.n, an, bs);
-  q.n = nq; q.neg = nq ? (a.neg ^ b.neg) : 0;
-  r.n = nr; r.neg = nr ? a.neg : 0;
 }
 // floor division: a = q*b + r with 0 <= r < b for b > 0
 template <int CAP, int CQ, int CR, int CA, int CB>

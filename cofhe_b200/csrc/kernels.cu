@@ -4,6 +4,7 @@
 // structure-of-arrays limbs so that a warp's loads/stores of one limb row are one coalesced 128-byte line.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <new>
 
@@ -119,6 +120,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return COFHE_B200_ECUDA;
   DevGuard g(device);
   if (!g.ok) return COFHE_B200_ECUDA;
+  if (getenv("COFHE_B200_STACK")) cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(getenv("COFHE_B200_STACK")));
   cofhe_b200_ctx *ctx = new (std::nothrow) cofhe_b200_ctx();
   if (!ctx) return COFHE_B200_ENOMEM;
   ctx->device = device;

@@ -26,20 +26,21 @@ struct Group {
 // -a < b <= a  (qfi.inl:473-485): b <- b + 2a*q', c <- c + q'*(b + a*q'), q' = floor((a-b)/(2a))
 template <int CAP>
 QF_HDN void qf_normalize(Err &e, Form<CAP> &f) {
-  // fast exit: |b| < a, or b == a
+  // already normal when |b| < a, or b == a  (single exit: see DESIGN.md "device-code rules")
   int c = z_cmpabs(f.b, f.a);
-  if (c < 0 || (c == 0 && !f.b.neg)) return;
-  Z<CAP> t, q, r, a2;
-  z_sub(e, t, f.a, f.b);       // a - b
-  z_shl(e, a2, f.a, 1);        // 2a
-  z_fdiv_qr<CAP>(e, q, r, t, a2);  // t = q*2a + r, 0 <= r < 2a
-  // c += q*(b + a*q)
-  z_mul(e, t, f.a, q);
-  z_add(e, t, t, f.b);
-  z_mul(e, a2, q, t);
-  z_add(e, f.c, f.c, a2);
-  // b = a - r
-  z_sub(e, f.b, f.a, r);
+  if (!(c < 0 || (c == 0 && !f.b.neg))) {
+    Z<CAP> t, q, r, a2;
+    z_sub(e, t, f.a, f.b);       // a - b
+    z_shl(e, a2, f.a, 1);        // 2a
+    z_fdiv_qr<CAP>(e, q, r, t, a2);  // t = q*2a + r, 0 <= r < 2a
+    // c += q*(b + a*q)
+    z_mul(e, t, f.a, q);
+    z_add(e, t, t, f.b);
+    z_mul(e, a2, q, t);
+    z_add(e, f.c, f.c, a2);
+    // b = a - r
+    z_sub(e, f.b, f.a, r);
+  }
 }
 
 template <int CAP>
@@ -74,8 +75,7 @@ QF_HDN void qf_identity(Err &e, const Group<CAP> &G, Form<CAP> &f) {
 // QFI::neg (qfi.inl:171-176): (a,-b,c) unless that would not be reduced (a == c or a == b)
 template <int CAP>
 QF_HDN void qf_inverse(Form<CAP> &f) {
-  if (z_cmp(f.a, f.c) == 0 || z_cmp(f.a, f.b) == 0) return;
-  z_neg(f.b);
+  if (!(z_cmp(f.a, f.c) == 0 || z_cmp(f.a, f.b) == 0)) z_neg(f.b);
 }
 
 // r = f1 o f2 (neg2: f1 o f2^-1), reduced.  Inputs must be forms of discriminant -absD; they need not be reduced,
@@ -190,18 +190,22 @@ QF_HDN void qf_compose(Err &e, const Group<CAP> &G, Form<CAP> &r, const Form<CAP
 template <int CAP>
 QF_HDN void qf_pow(Err &e, const Group<CAP> &G, Form<CAP> &r, const Form<CAP> &f, const u32 *n, int nl, size_t stride,
                    bool nneg) {
-  int top = nl - 1;
-  while (top >= 0 && n[(size_t)top * stride] == 0) top--;
-  if (top < 0) { qf_identity(e, G, r); return; }
-  Form<CAP> base;
-  z_copy(e, base.a, f.a); z_copy(e, base.b, f.b); z_copy(e, base.c, f.c);
-  z_copy(e, r.a, f.a); z_copy(e, r.b, f.b); z_copy(e, r.c, f.c);
-  int bit = 31 - clz32(n[(size_t)top * stride]);
-  for (int i = 32 * top + bit - 1; i >= 0 && !e.code; i--) {
-    qf_compose(e, G, r, r, r, false, true);
-    if ((n[(size_t)(i >> 5) * stride] >> (i & 31)) & 1) qf_compose(e, G, r, r, base, false, false);
+  int top = -1;
+  for (int i = 0; i < nl; i++)
+    if (n[(size_t)i * stride] != 0) top = i;
+  if (top >= 0) {
+    Form<CAP> base;
+    z_copy(e, base.a, f.a); z_copy(e, base.b, f.b); z_copy(e, base.c, f.c);
+    z_copy(e, r.a, f.a); z_copy(e, r.b, f.b); z_copy(e, r.c, f.c);
+    int bit = 31 - clz32(n[(size_t)top * stride]);
+    for (int i = 32 * top + bit - 1; i >= 0 && !e.code; i--) {
+      qf_compose(e, G, r, r, r, false, true);
+      if ((n[(size_t)(i >> 5) * stride] >> (i & 31)) & 1) qf_compose(e, G, r, r, base, false, false);
+    }
+    if (nneg) qf_inverse(r);
+  } else {
+    qf_identity(e, G, r);
   }
-  if (nneg) qf_inverse(r);
 }
 
 }  // namespace cofhe
