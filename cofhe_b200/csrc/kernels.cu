@@ -274,3 +274,63 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// Integer-multiply roofline probe: independent 32x32->64 multiply-accumulate chains (IMAD.WIDE.U32), all SMs.
+// bench.py divides algorithmic MACs/s by this measured rate (SURVEY.md section 8d "Governing roofline").
+// ---------------------------------------------------------------------------------------------------
+namespace {
+template <int WIDE>
+__global__ void __launch_bounds__(256) k_imad_probe(u32 *out, u32 seed, int iters) {
+  u32 x = seed + threadIdx.x, y = seed * 7u + blockIdx.x;
+  u64 a0 = x, a1 = y, a2 = x ^ y, a3 = x + y, a4 = x * 3u, a5 = y * 5u, a6 = x - y, a7 = ~x;
+  u32 b0 = x, b1 = y, b2 = x ^ y, b3 = x + y, b4 = x * 3u, b5 = y * 5u, b6 = x - y, b7 = ~x;
+  for (int i = 0; i < iters; i++) {
+    if (WIDE) {
+#define STEP(a) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(a) : "r"(x), "r"(y));
+      STEP(a0) STEP(a1) STEP(a2) STEP(a3) STEP(a4) STEP(a5) STEP(a6) STEP(a7)
+#undef STEP
+    } else {
+#define STEP(b) asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(b) : "r"(x), "r"(y));
+      STEP(b0) STEP(b1) STEP(b2) STEP(b3) STEP(b4) STEP(b5) STEP(b6) STEP(b7)
+#undef STEP
+    }
+  }
+  u64 s = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
+  u32 t = b0 ^ b1 ^ b2 ^ b3 ^ b4 ^ b5 ^ b6 ^ b7;
+  if (((u32)s ^ (u32)(s >> 32) ^ t) == 0x12345u) out[0] = 1;  // keep the chains alive
+}
+}  // namespace
+
+extern "C" int cofhe_b200_imad_probe(int device, int wide, double *macs_per_s) {
+  if (!macs_per_s) return COFHE_B200_EINVAL;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return COFHE_B200_ECUDA;
+  DevGuard g(device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  u32 *d = nullptr;
+  CUDA_TRY(cudaMalloc(&d, 4));
+  const int iters = 1 << 14, blocks = prop.multiProcessorCount * 8, threads = 256;
+  cudaEvent_t e0, e1;
+  CUDA_TRY(cudaEventCreate(&e0));
+  CUDA_TRY(cudaEventCreate(&e1));
+  double best = 0;
+  for (int rep = 0; rep < 6; rep++) {
+    cudaEventRecord(e0);
+    if (wide) k_imad_probe<1><<<blocks, threads>>>(d, 12345u + rep, iters);
+    else k_imad_probe<0><<<blocks, threads>>>(d, 12345u + rep, iters);
+    cudaEventRecord(e1);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return COFHE_B200_ECUDA; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    double rate = (double)blocks * threads * iters * 8.0 / (ms * 1e-3);
+    if (rep > 0 && rate > best) best = rate;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *macs_per_s = best;
+  return COFHE_B200_OK;
+}

@@ -1,0 +1,565 @@
+// cofhe_b200 -- register-resident fast path: NUCOMP / NUDUPL with partial reduction and canonical reduction on
+// fixed-width limbs (N = limbs of a and b), one form per thread, no local memory, no dynamic indexing.
+//
+// Same mathematics as qform.cuh (the robust path) -- the 2x4 matrix view of composition with the C and D columns
+// recovered through the orthogonality relations -- but organised for the GPU:
+//   * Euclid runs as single-precision Lehmer rounds (32-bit leading digits, Jebelean's exactness test), operands
+//     kept left-justified by whole limbs so every register index is static;
+//   * the exact divisions by a1 are 2-adic (Jebelean) on half-width operands: only the low limbs of the
+//     numerators are ever formed;
+//   * everything after the partial Euclid is half-width (M limbs) two's-complement/sign-magnitude arithmetic.
+// Whatever falls outside the shapes this path is built for (gcd(a1,a2) >= 2^32, a quotient of 31+ bits, tiny `a` /
+// huge `c`, a1 divisible by 2^32, ...) is detected and reported through `bail`; the caller then runs the robust
+// path on that element.  Both paths end in the unique reduced form, so which one ran is not observable.
+#pragma once
+#include "fw.cuh"
+#include "lehmer.cuh"
+
+namespace cofhe {
+
+template <int N>
+struct FormR {
+  u32 a[N];      // > 0
+  u32 b[N];      // two's complement
+  u32 c[N + 1];  // > 0
+};
+
+// floor(a / b) and remainder for a >= b > 0: float reciprocal estimate biased low, then exact fix-up
+QF_HD u32 divmod32(u32 a, u32 b, u32 *rem) {
+  u32 q = 0, r = a;
+  do {
+    float fb = (float)b, fr = (float)r, rc;
+#if defined(__CUDA_ARCH__)
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(fb));
+#else
+    rc = 1.0f / fb;
+#endif
+    u32 qe = (u32)(fr * rc * 0.9999995f);
+    u64 p = (u64)qe * b;
+    if (p > r) { qe = r / b; p = (u64)qe * b; }  // never expected (estimate is biased low)
+    if (qe == 0) { qe = 1; p = b; }
+    q += qe;
+    r -= (u32)p;
+  } while (r >= b);
+  *rem = r;
+  return q;
+}
+
+// Single-precision Lehmer step: as hgcd2 (lehmer.cuh) on 32-bit leading parts; cofactors stay below 2^30.
+QF_HD Mat2 hgcd32(u32 ah, u32 bh, bool exact, u32 min_r) {
+  u32 r0 = ah, r1 = bh;
+  u32 S0 = 1, T0 = 0, S1 = 0, T1 = 1;
+  int j = 1;
+  for (;;) {
+    if (r1 == 0 || r1 < min_r) break;
+    u32 r2;
+    u32 q = divmod32(r0, r1, &r2);
+    u64 S2 = (u64)q * S1 + S0, T2 = (u64)q * T1 + T0;
+    if ((S2 | T2) >> 30) break;
+    if (!exact) {
+      bool ok;
+      if (j & 1) ok = r2 >= T2 && (u64)(r1 - r2) >= S2 + S1;
+      else ok = r2 >= S2 && (u64)(r1 - r2) >= T2 + T1;
+      if (!ok) break;
+    }
+    r0 = r1; r1 = r2; S0 = S1; S1 = (u32)S2; T0 = T1; T1 = (u32)T2;
+    j++;
+  }
+  Mat2 m;
+  m.S0 = S0; m.T0 = T0; m.S1 = S1; m.T1 = T1; m.j = j;
+  return m;
+}
+
+// r = |x*A - y*B| where the sign is known: neg == true means the combination is <= 0.  x, y < 2^30.
+template <int N>
+QF_HD void fw_lin_sub(u32 *r, u32 x, const u32 *A, u32 y, const u32 *B, bool neg) {
+  i64 c = 0;
+  QF_UNROLL for (int i = 0; i < N; i++) {
+    i64 d = (i64)((u64)x * A[i]) - (i64)((u64)y * B[i]) + c;
+    r[i] = (u32)d;
+    c = d >> 32;
+  }
+  fw_cneg<N>(r, r, neg);
+}
+// r = x*A + y*B, returns the carry-out limb
+template <int N>
+QF_HD u32 fw_lin_add(u32 *r, u32 x, const u32 *A, u32 y, const u32 *B) {
+  u64 c = 0;
+  QF_UNROLL for (int i = 0; i < N; i++) {
+    u64 p = (u64)x * A[i] + (c & 0xffffffffu);
+    u64 q = (u64)y * B[i] + (u32)p;
+    r[i] = (u32)q;
+    c = (c >> 32) + (p >> 32) + (q >> 32);
+  }
+  return (u32)c | (u32)(c >> 32);
+}
+
+// Half-extended Euclid on fixed-width magnitudes, same contract as z_hxgcd (lehmer.cuh): in (R0 >= R1, C0, C1),
+// runs until the first remainder with bits <= stop_bits, returns the number of Euclidean steps.  `bail` is
+// raised when the sequence needs something this path does not do (a 31+ bit quotient, cofactor overflow).
+template <int N, int NC>
+QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail) {
+  int lsh = fw_lead_zero_limbs<N>(R0);
+  if (lsh >= N) { bail = true; return 0; }
+  fw_shl_limbs<N>(R0, lsh);
+  fw_shl_limbs<N>(R1, lsh);
+  int sb = stop_bits + 32 * lsh;
+  int steps = 0;
+  for (int guard = 0; guard < 80 * N; guard++) {
+    if (R0[N - 1] == 0) {
+      QF_UNROLL for (int i = N - 1; i > 0; i--) { R0[i] = R0[i - 1]; R1[i] = R1[i - 1]; }
+      R0[0] = 0; R1[0] = 0;
+      lsh++; sb += 32;
+      continue;
+    }
+    int b1 = fw_bits<N>(R1);
+    if (b1 <= sb) break;  // includes R1 == 0
+    bool exact = lsh == N - 1;
+    int sh = exact ? 0 : clz32(R0[N - 1]);
+    u32 ah = R0[N - 1], bh = R1[N - 1];
+    if (sh) {
+      ah = (ah << sh) | (R0[N >= 2 ? N - 2 : 0] >> (32 - sh));
+      bh = (bh << sh) | (R1[N >= 2 ? N - 2 : 0] >> (32 - sh));
+    }
+    int h = 32 * (N - 1) - sh;
+    u32 min_r = sb > h ? (1u << (sb - h)) : 0u;
+    Mat2 M = hgcd32(ah, bh, exact, min_r);
+    if (M.j == 1) {
+      // one full-precision division step with a quotient of at most 30 bits
+      int b0 = 32 * N - clz32(R0[N - 1]);
+      if (b0 - b1 > 29) { bail = true; break; }
+      int s2 = clz32(R0[N - 1]);
+      u64 A64 = ((u64)R0[N - 1] << 32) | R0[N >= 2 ? N - 2 : 0];
+      u64 B64 = ((u64)R1[N - 1] << 32) | R1[N >= 2 ? N - 2 : 0];
+      if (s2) {
+        u32 a0 = N >= 3 ? R0[N >= 3 ? N - 3 : 0] : 0, b0l = N >= 3 ? R1[N >= 3 ? N - 3 : 0] : 0;
+        A64 = (A64 << s2) | (a0 >> (32 - s2));
+        B64 = (B64 << s2) | (b0l >> (32 - s2));
+      }
+      u64 q64 = (B64 == ~(u64)0) ? 0 : A64 / (B64 + 1);
+      u32 q = (u32)q64;
+      u32 t[N];
+      fw_copy<N>(t, R0);
+      u32 bo = fw_submul1<N>(t, R1, q);
+      if (bo) { bail = true; break; }  // cannot happen: q underestimates
+      int fix = 0;
+      while (!fw_lt<N>(t, R1)) {
+        fw_sub<N>(t, t, R1);
+        q++;
+        if (++fix > 8) { bail = true; break; }
+      }
+      if (bail) break;
+      u32 cn[NC + 1];
+      fw_mul1<NC>(cn, C1, q);
+      u32 cy = fw_add<NC>(cn, cn, C0);
+      if (cn[NC] | cy) { bail = true; break; }
+      fw_copy<N>(R0, R1);
+      fw_copy<N>(R1, t);
+      fw_copy<NC>(C0, C1);
+      fw_copy<NC>(C1, cn);
+      steps++;
+    } else {
+      u32 t0[N], t1[N];
+      bool odd = M.j & 1;
+      // j odd : X_{j-1} = S0*A - T0*B >= 0 , X_j = T1*B - S1*A >= 0 ; j even: signs flipped
+      fw_lin_sub<N>(t0, M.S0, R0, M.T0, R1, !odd);
+      fw_lin_sub<N>(t1, M.S1, R0, M.T1, R1, odd);
+      fw_copy<N>(R0, t0);
+      fw_copy<N>(R1, t1);
+      u32 c0[NC], c1[NC];
+      u32 o0 = fw_lin_add<NC>(c0, M.S0, C0, M.T0, C1);
+      u32 o1 = fw_lin_add<NC>(c1, M.S1, C0, M.T1, C1);
+      if (o0 | o1) { bail = true; break; }
+      fw_copy<NC>(C0, c0);
+      fw_copy<NC>(C1, c1);
+      steps += M.j - 1;
+    }
+    if (guard == 80 * N - 1) bail = true;
+  }
+  fw_shr_limbs<N>(R0, lsh);
+  fw_shr_limbs<N>(R1, lsh);
+  return steps;
+}
+
+// exact 32-bit Euclid with one signed cofactor: g = gcd(a, b), y*b == g (mod a); a >= 1
+QF_HD u32 xgcd32(u32 a, u32 b, i64 *y) {
+  u32 r0 = a, r1 = b;
+  i64 y0 = 0, y1 = 1;
+  while (r1) {
+    u32 r2;
+    u32 q = r0 >= r1 ? divmod32(r0, r1, &r2) : (r2 = r0, 0u);
+    i64 y2 = y0 - (i64)q * y1;
+    r0 = r1; r1 = r2; y0 = y1; y1 = y2;
+  }
+  *y = y0;
+  return r0;
+}
+
+// canonical reduction on fixed width: a[N], b two's complement [N+1], c[N+1]; returns false on bail.
+template <int N>
+QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
+  constexpr int W = N + 1;
+  for (int it = 0; it < 64; it++) {
+    // ---- normalise: -a < b <= a
+    int ba = fw_bits<N>(a);
+    // c stays within W limbs only while a is not too small
+    if (ba == 0 || ba < dbits - 32 * W + 3) return false;
+    bool bneg = b[W - 1] >> 31;
+    u32 bm[W];
+    fw_cneg<W>(bm, b, bneg);
+    int bb = fw_bits<W>(bm);
+    if (bb >= ba) {
+      if (bb - ba > 28) return false;
+      // k = round-ish(b / 2a) from the leading 64 bits, then exact fix-up
+      u32 aw[W];
+      fw_ext<W, N>(aw, a, false);
+      int sh = 32 * W - bb;  // left shift that brings |b|'s msb to the top
+      // leading 64 bits of |b| and of a under the same shift (static extraction through a barrel shift)
+      u32 tb[W], ta[W];
+      fw_copy<W>(tb, bm);
+      fw_copy<W>(ta, aw);
+      fw_shl_limbs<W>(tb, sh >> 5);
+      fw_shl_limbs<W>(ta, sh >> 5);
+      u32 tb2[W], ta2[W];
+      fw_shl_bits<W>(tb2, tb, sh & 31);
+      fw_shl_bits<W>(ta2, ta, sh & 31);
+      u64 B64 = ((u64)tb2[W - 1] << 32) | tb2[W - 2];
+      u64 A64 = ((u64)ta2[W - 1] << 32) | ta2[W - 2];
+      double kd = (double)B64 / (2.0 * (double)A64 + 2.0);
+      u32 k = (u32)kd;  // underestimate of floor(|b| / 2a), < 2^29
+      // r = |b| - 2a*k  (>= 0)
+      u32 a2[W];
+      fw_shl_bits<W>(a2, aw, 1);
+      u32 r[W];
+      fw_copy<W>(r, bm);
+      if (k) { if (fw_submul1<W>(r, a2, k)) return false; }
+      // bring r into (-a, a] for b > 0, [-a, a) for b < 0  (r is treated as signed from here)
+      int fix = 0;
+      for (;;) {
+        bool rneg = r[W - 1] >> 31;
+        if (rneg) break;  // can only get here after an overshoot below; not expected
+        int cmp = fw_cmp<W>(r, aw);
+        bool over = bneg ? cmp >= 0 : cmp > 0;  // r >= a (b<0)  /  r > a (b>0)
+        if (!over) break;
+        fw_sub<W>(r, r, a2);
+        k++;
+        if (++fix > 8) return false;
+      }
+      // signed k and new b:  b' = sign * r ; c' = c - ks*(b + b')/2 , with (b + b')/2 = sign*(|b| + r)/2
+      u32 hs[W];
+      fw_add<W>(hs, bm, r);  // |b| + r  (r may be negative two's complement; sum >= 0)
+      fw_shr_bits<W>(hs, hs, 1);
+      // c' = c - k*hs  (sign*sign = +)
+      if (k) {
+        u32 bo = fw_submul1<W>(c, hs, k);
+        if (bo) return false;
+      }
+      fw_cneg<W>(b, r, bneg);
+    }
+    // ---- rho step if a > c
+    u32 aw[W];
+    fw_ext<W, N>(aw, a, false);
+    int cmp = fw_cmp<W>(aw, c);
+    if (cmp <= 0) {
+      if (cmp == 0 && (b[W - 1] >> 31)) fw_neg<W>(b, b);
+      return true;
+    }
+    if (c[N] != 0) return false;  // cannot be: c < a
+    u32 t[N];
+    fw_copy<N>(t, a);
+    fw_copy<N>(a, c);
+    fw_ext<W, N>(c, t, false);
+    fw_neg<W>(b, b);
+  }
+  return false;
+}
+
+// r = f1 o f2 (neg2: f1 o f2^-1; DUPL: f1^2, f2 ignored).  Returns false (bail) when the element must take the
+// robust path; r is unspecified then.  dbits = bit length of |Delta|.
+template <int N, bool DUPL>
+QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool neg2, int dbits) {
+  constexpr int W = N + 1;
+  constexpr int M = (N + 1) / 2 + 1;  // half width of the post-Euclid quantities
+  constexpr int L = M + 1;            // numerators carry one extra limb for the 2-adic shift
+  bool bail = false;
+
+  // ---- operands, larger `a` first
+  u32 a1[N], a2[N], b1[W], b2[W], c2[W];
+  bool sw = !DUPL && fw_lt<N>(f1.a, f2.a);
+  {
+    const FormR<N> &p = sw ? f2 : f1, &q = DUPL ? f1 : (sw ? f1 : f2);
+    fw_copy<N>(a1, p.a);
+    fw_copy<N>(a2, q.a);
+    fw_ext<W, N>(b1, p.b, true);
+    fw_ext<W, N>(b2, q.b, true);
+    fw_copy<W>(c2, q.c);
+    if (!DUPL && neg2) { if (sw) fw_neg<W>(b1, b1); else fw_neg<W>(b2, b2); }
+  }
+  // s = (b1+b2)/2, m = (b2-b1)/2  (two's complement, W limbs)
+  u32 s[W], m[W];
+  fw_add<W>(s, b1, b2);
+  fw_shr_bits<W>(s, s, 1, s[W - 1] >> 31);
+  fw_sub<W>(m, b2, s);
+
+  // ---- F = gcd(a1, a2) with v*a2 == F (mod a1)   [DUPL: F = a, G = gcd(a, b)]
+  u32 By[N], Bx[N];
+  u32 G = 1;
+  if (!DUPL) {
+    u32 R0[N], R1[N], C0[N], C1[N];
+    fw_copy<N>(R0, a1); fw_copy<N>(R1, a2); fw_zero<N>(C0); fw_zero<N>(C1); C1[0] = 1;
+    int st = fw_hxgcd<N, N>(R0, R1, C0, C1, 0, bail);
+    if (bail) return false;
+    if (!fw_high_zero<N, 1>(R0)) return false;  // gcd(a1,a2) >= 2^32: robust path
+    u32 F = R0[0];
+    bool vneg = (st & 1) == 0;  // sign(C_st) = (-1)^(st+1)
+    // t = |v| * |m| mod By, with By = a1/G
+    u32 mneg = m[W - 1] >> 31;
+    u32 mm[W];
+    fw_cneg<W>(mm, m, mneg);
+    if (mm[N] != 0) return false;
+    u32 x0m = 1; bool x0neg = false; u32 y0m = 0; bool y0neg = false;
+    u32 x0big[N]; bool x0_is_big = false;
+    fw_zero<N>(x0big);
+    if (F != 1) {
+      // G = gcd(F, s) = x0*F + y0*s
+      u32 sneg = s[W - 1] >> 31;
+      u32 sm_[W];
+      fw_cneg<W>(sm_, s, sneg);
+      if (sm_[N] != 0) return false;
+      u32 srem = fw_mod1<N>(sm_, F);  // |s| mod F
+      if (srem == 0) {
+        G = F;
+      } else {
+        i64 y;
+        G = xgcd32(F, srem, &y);       // y*|s| == G (mod F)
+        if (sneg) y = -y;              // y*s == G (mod F)
+        // reduce y into (-F, F) is already true; x0 = (G - y*s)/F  (exact), N+1 limbs signed
+        y0neg = y < 0;
+        y0m = (u32)(y0neg ? -y : y);
+        // |y|*|s| then sign, G - that, / F
+        u32 ys[W];
+        fw_mul1<N>(ys, sm_, y0m);
+        bool ysneg = (y0neg != (sneg != 0)) && !fw_is_zero<W>(ys);
+        // num = G - y*s = G - (ysneg ? -ys : ys) = ysneg ? G + ys : G - ys
+        u32 num[W], g1[W];
+        fw_zero<W>(g1); g1[0] = G;
+        bool nneg;
+        if (ysneg) { fw_add<W>(num, g1, ys); nneg = false; }
+        else {
+          if (fw_lt<W>(g1, ys)) { fw_sub<W>(num, ys, g1); nneg = true; }
+          else { fw_sub<W>(num, g1, ys); nneg = false; }
+        }
+        u32 xq[W];
+        fw_divexact1<W>(xq, num, F);
+        if (xq[N] != 0) return false;
+        fw_copy<N>(x0big, xq);
+        x0neg = nneg;
+        x0_is_big = true;
+      }
+    }
+    // By = a1 / G
+    if (G == 1) fw_copy<N>(By, a1); else fw_divexact1<N>(By, a1, G);
+    // t = (|v|*|m|) mod By
+    u32 prod[2 * N], t[N];
+    fw_mul<N, N>(prod, C0, mm);
+    if (!fw_mod<2 * N, N>(t, prod, By)) return false;
+    bool tneg = (vneg != (mneg != 0));
+    if (F != 1) {
+      // t <- x0 * t (mod By)
+      if (x0_is_big) {
+        u32 xr[N];
+        if (!fw_mod<N, N>(xr, x0big, By)) return false;
+        fw_mul<N, N>(prod, xr, t);
+        if (!fw_mod<2 * N, N>(t, prod, By)) return false;
+        tneg = tneg != x0neg;
+      }
+      (void)x0m;
+      // u = y0 * (c2 mod By) (mod By)
+      if (y0m) {
+        u32 cr[N];
+        if (!fw_mod<W, N>(cr, c2, By)) return false;
+        u32 yc[W];
+        fw_mul1<N>(yc, cr, y0m);
+        u32 u[N];
+        if (!fw_mod<W, N>(u, yc, By)) return false;
+        // Bx = (tneg ? -t : t) + (y0neg ? -u : u)  (mod By)
+        // fold signs: bring both to [0, By)
+        if (tneg && !fw_is_zero<N>(t)) fw_sub<N>(t, By, t);
+        tneg = false;
+        if (y0neg && !fw_is_zero<N>(u)) fw_sub<N>(u, By, u);
+        u32 cy = fw_add<N>(t, t, u);
+        if (cy || !fw_lt<N>(t, By)) fw_sub<N>(t, t, By);
+      }
+    }
+    if (tneg && !fw_is_zero<N>(t)) fw_sub<N>(t, By, t);
+    fw_copy<N>(Bx, t);
+  } else {
+    // NUDUPL: s = b, m = 0, F = a.  G = gcd(a, b) = . + y*b ; Bx = y*c mod (a/G)
+    u32 bneg = b1[W - 1] >> 31;
+    u32 bm[W];
+    fw_cneg<W>(bm, b1, bneg);
+    if (bm[N] != 0) return false;
+    bool yneg = false;
+    u32 ym[N];
+    fw_zero<N>(ym);
+    if (fw_is_zero<N>(bm)) {
+      // b == 0: G = a; By = 1; Bx = 0
+      return false;  // rare (ambiguous forms): robust path
+    }
+    {
+      u32 R0[N], R1[N], C0[N], C1[N];
+      fw_copy<N>(R0, a1); fw_copy<N>(R1, bm);
+      // |b| <= a for reduced input; an unreduced input may have |b| > a: robust path
+      if (fw_lt<N>(R0, R1)) return false;
+      fw_zero<N>(C0); fw_zero<N>(C1); C1[0] = 1;
+      int st = fw_hxgcd<N, N>(R0, R1, C0, C1, 0, bail);
+      if (bail) return false;
+      if (!fw_high_zero<N, 1>(R0)) return false;
+      G = R0[0];
+      fw_copy<N>(ym, C0);
+      yneg = ((st & 1) == 0) != (bneg != 0);  // y*|b| == G  ->  y*b == G needs the sign of b
+    }
+    if (G == 1) fw_copy<N>(By, a1); else fw_divexact1<N>(By, a1, G);
+    // Bx = y * c mod By
+    u32 cr[N];
+    if (!fw_mod<W, N>(cr, c2, By)) return false;
+    u32 prod[2 * N], t[N];
+    fw_mul<N, N>(prod, ym, cr);
+    if (!fw_mod<2 * N, N>(t, prod, By)) return false;
+    if (yneg && !fw_is_zero<N>(t)) fw_sub<N>(t, By, t);
+    fw_copy<N>(Bx, t);
+  }
+
+  // ---- partial Euclid on (By, Bx) down to about sqrt(a1/a2) * |D|^(1/4)
+  int ba1 = fw_bits<N>(a1), ba2 = fw_bits<N>(a2);
+  int stop = (ba1 - ba2) / 2 + dbits / 4;
+  if (stop < 1) stop = 1;
+  u32 C0[M], C1[M];
+  fw_zero<M>(C0); fw_zero<M>(C1); C1[0] = 1;
+  int st = fw_hxgcd<N, M>(By, Bx, C0, C1, stop, bail);  // (By, Bx) <- (R_{i-1}, R_i)
+  if (bail) return false;
+  int idx = 1 + st;
+  // rows: x' = (Ax, Bxp) with Ax = G*C0 >= 0, Bxp = (-1)^idx R_{i-1};  y' = (Ay, Byp) with Ay = (-1)^(idx+1) G*C1, Byp = R_i
+  if (!fw_high_zero<N, M>(By) || !fw_high_zero<N, M>(Bx)) return false;
+  if ((By[M - 1] | Bx[M - 1]) >> 30) return false;
+  u32 Ax[M], Ay[M], Rx[M], Ry[M];
+  fw_copy<M>(Rx, By);
+  fw_copy<M>(Ry, Bx);
+  {
+    u32 t[M + 1];
+    fw_mul1<M>(t, C0, G); if (t[M] | (t[M - 1] >> 30)) return false; fw_copy<M>(Ax, t);
+    fw_mul1<M>(t, C1, G); if (t[M] | (t[M - 1] >> 30)) return false; fw_copy<M>(Ay, t);
+  }
+  bool ay_neg = (idx & 1) == 0, rx_neg = (idx & 1) != 0;
+  // size guards for the quotients (they must fit M limbs signed):
+  //   |C| <= (a2*|B| + |m|*|A|)/a1 ,  |D| <= (|s|*|B| + c2*|A|)/a1
+  {
+    int bAx = fw_bits<M>(Ax), bAy = fw_bits<M>(Ay), bRx = fw_bits<M>(Rx), bRy = fw_bits<M>(Ry);
+    int bm = fw_sbits<W>(m), bs = fw_sbits<W>(s), bc2 = fw_bits<W>(c2);
+    int lim = 32 * M - 3;
+    int mxA = bAx > bAy ? bAx : bAy, mxR = bRx > bRy ? bRx : bRy;
+    int t1 = ba2 + mxR, t2 = bm + mxA, t3 = bs + mxR, t4 = bc2 + mxA;
+    int mx = t1 > t2 ? t1 : t2;
+    mx = mx > t3 ? mx : t3;
+    mx = mx > t4 ? mx : t4;
+    if (mx + 2 - (ba1 - 1) > lim) return false;
+  }
+  // 2-adic exact division by a1 = 2^tz * a1o
+  int tz = fw_ctz<N>(a1);
+  if (tz > 31) return false;
+  u32 a1o[M];
+  {
+    u32 t[N];
+    fw_shr_bits<N>(t, a1, tz);
+    fw_copy<M>(a1o, t);
+  }
+  u32 a1inv = inv32(a1o[0]);
+  // quotient Q = (p*B - q*A)/a1 for (p, q) = (a2, m) -> C and (s, c2) -> D; B, A given as magnitude + sign
+  u32 Cx[M], Cy[M], Dx[M], Dy[M];
+  {
+    u32 a2l[L], ml[L], sl[L], c2l[L];
+    QF_UNROLL for (int i = 0; i < L; i++) {
+      a2l[i] = i < N ? a2[i] : 0;
+      ml[i] = m[i < W ? i : W - 1];
+      sl[i] = s[i < W ? i : W - 1];
+      c2l[i] = i < W ? c2[i] : 0;
+    }
+    static_assert(L <= W, "half width must not exceed the operand width");
+    // helper lambda-free: compute into q[M]
+#define QF_ORTHO(QOUT, PL, QL, BMAG, BNEG, AMAG, ANEG)                         \
+    {                                                                          \
+      u32 n1[L], n2[L];                                                        \
+      fw_mul_lo<L, L, M>(n1, PL, BMAG);                                        \
+      fw_cneg<L>(n1, n1, BNEG);                                                \
+      fw_mul_lo<L, L, M>(n2, QL, AMAG);                                        \
+      fw_cneg<L>(n2, n2, ANEG);                                                \
+      fw_sub<L>(n1, n1, n2);                                                   \
+      u32 sh_[L];                                                              \
+      fw_shr_bits<L>(sh_, n1, tz);                                             \
+      u32 nm[M];                                                               \
+      fw_copy<M>(nm, sh_);                                                     \
+      fw_divexact_2adic<M>(QOUT, nm, a1o, a1inv);                              \
+    }
+    QF_ORTHO(Cy, a2l, ml, Ry, false, Ay, ay_neg)
+    QF_ORTHO(Dy, sl, c2l, Ry, false, Ay, ay_neg)
+    QF_ORTHO(Cx, a2l, ml, Rx, rx_neg, Ax, false)
+    QF_ORTHO(Dx, sl, c2l, Rx, rx_neg, Ax, false)
+#undef QF_ORTHO
+  }
+  if (DUPL) {
+    // C column equals the B column for a square
+    fw_cneg<M>(Cy, Ry, false);
+    fw_cneg<M>(Cx, Rx, rx_neg);
+  }
+  // ---- the composed form (two's complement, 2M limbs):
+  //   a3 = By*Cy - Ay*Dy ; c3 = Bx*Cx - Ax*Dx ; b3 = (Ax*Dy + Ay*Dx) - (Bx*Cy + By*Cx)
+  constexpr int P = 2 * M;
+  u32 a3[P], b3[P], c3[P];
+  {
+    // sign-magnitude of the quotients
+    bool ncx = Cx[M - 1] >> 31, ncy = Cy[M - 1] >> 31, ndx = Dx[M - 1] >> 31, ndy = Dy[M - 1] >> 31;
+    u32 mcx[M], mcy[M], mdx[M], mdy[M];
+    fw_cneg<M>(mcx, Cx, ncx); fw_cneg<M>(mcy, Cy, ncy); fw_cneg<M>(mdx, Dx, ndx); fw_cneg<M>(mdy, Dy, ndy);
+    u32 p[P], q[P];
+    fw_mul<M, M>(p, Ry, mcy); fw_cneg<P>(p, p, ncy);
+    fw_mul<M, M>(q, Ay, mdy); fw_cneg<P>(q, q, ay_neg != ndy);
+    fw_sub<P>(a3, p, q);
+    fw_mul<M, M>(p, Rx, mcx); fw_cneg<P>(p, p, rx_neg != ncx);
+    fw_mul<M, M>(q, Ax, mdx); fw_cneg<P>(q, q, ndx);
+    fw_sub<P>(c3, p, q);
+    fw_mul<M, M>(p, Ax, mdy); fw_cneg<P>(p, p, ndy);
+    fw_mul<M, M>(q, Ay, mdx); fw_cneg<P>(q, q, ay_neg != ndx);
+    fw_add<P>(b3, p, q);
+    fw_mul<M, M>(p, Rx, mcy); fw_cneg<P>(p, p, rx_neg != ncy);
+    fw_sub<P>(b3, b3, p);
+    fw_mul<M, M>(p, Ry, mcx); fw_cneg<P>(p, p, ncx);
+    fw_sub<P>(b3, b3, p);
+  }
+  // must fit the working shape: 0 < a3 < 2^(32N-1), 0 < c3 < 2^(32W-1), |b3| < 2^(32W-1)
+  static_assert(P >= W, "2M >= N+1");
+  if ((a3[P - 1] >> 31) || (c3[P - 1] >> 31)) return false;
+  if (!fw_high_zero<P, N>(a3) || (a3[N - 1] >> 31) || fw_is_zero<P>(a3)) return false;
+  if (!fw_high_zero<P, W>(c3) || (c3[W - 1] >> 31)) return false;
+  {
+    u32 fill = (b3[P - 1] >> 31) ? 0xffffffffu : 0u;
+    u32 o = 0;
+    QF_UNROLL for (int i = W; i < P; i++) o |= b3[i] ^ fill;
+    if (o || ((b3[W - 1] >> 31) != (fill & 1))) return false;
+  }
+  u32 ra[N], rb[W], rc[W];
+  fw_copy<N>(ra, a3);
+  fw_copy<W>(rb, b3);
+  fw_copy<W>(rc, c3);
+  if (!fw_reduce<N>(ra, rb, rc, dbits)) return false;
+  // b must fit N limbs signed
+  {
+    u32 fill = (rb[W - 1] >> 31) ? 0xffffffffu : 0u;
+    if (rb[N] != fill || ((rb[N - 1] >> 31) != (fill & 1))) return false;
+  }
+  fw_copy<N>(r.a, ra);
+  fw_copy<N>(r.b, rb);
+  fw_copy<W>(r.c, rc);
+  return true;
+}
+
+}  // namespace cofhe

@@ -81,6 +81,11 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out);
 
+/* Measurement helper (no reference counterpart): sustained rate of independent 32x32->64-bit multiply-accumulates
+ * (wide != 0: IMAD.WIDE.U32) or 32-bit multiply-adds (wide == 0: IMAD) over all SMs of `device`, in MACs/s.
+ * bench.py uses it as the integer-multiply roofline denominator. */
+int cofhe_b200_imad_probe(int device, int wide, double *macs_per_s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,10 @@ SRC = os.path.join(HERE, "hostsim.cpp")
 CSRC = os.path.join(ROOT, "cofhe_b200", "csrc")
 
 _lib = None
-EXTRA_SIGS = {}
+EXTRA_SIGS = {
+    "hs_fast_compose": [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p,
+                        ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p],
+}
 
 
 def _stale():
