@@ -1,0 +1,111 @@
+// cofhe_b200 -- per-element bodies of the batched entry points on the register-resident fast path (qf_fast.cuh).
+//
+// One thread owns one form.  Whatever the fast path declines (`bail`: see qf_fast.cuh) is appended to a per-context
+// list and redone by a second, sparse kernel on the robust path (ops.cuh); both end in the unique reduced form, so
+// the split is not observable in the results.
+#pragma once
+#include "ops.cuh"
+#include "qf_fast.cuh"
+
+namespace cofhe {
+
+// SoA buffer (shape s, n elements per limb row) -> registers.  Returns false when the element does not fit the
+// fast shape (c wider than N+1 limbs).
+template <int N>
+QF_HD bool fr_load(FormR<N> &f, const u32 *p, int nc, size_t n, size_t idx) {
+  QF_UNROLL for (int i = 0; i < N; i++) f.a[i] = p[(size_t)i * n + idx];
+  QF_UNROLL for (int i = 0; i < N; i++) f.b[i] = p[(size_t)(N + i) * n + idx];
+  QF_UNROLL for (int i = 0; i < N + 1; i++) f.c[i] = i < nc ? p[(size_t)(2 * N + i) * n + idx] : 0;
+  u32 hi = 0;
+  for (int i = N + 1; i < nc; i++) hi |= p[(size_t)(2 * N + i) * n + idx];
+  return hi == 0;
+}
+template <int N>
+QF_HD void fr_store(const FormR<N> &f, u32 *p, int nc, size_t n, size_t idx) {
+  QF_UNROLL for (int i = 0; i < N; i++) p[(size_t)i * n + idx] = f.a[i];
+  QF_UNROLL for (int i = 0; i < N; i++) p[(size_t)(N + i) * n + idx] = f.b[i];
+  QF_UNROLL for (int i = 0; i < N + 1; i++) if (i < nc) p[(size_t)(2 * N + i) * n + idx] = f.c[i];
+  for (int i = N + 1; i < nc; i++) p[(size_t)(2 * N + i) * n + idx] = 0;
+}
+
+// QFI::neg (reference qfi.inl:171-176) on registers: (a,-b,c) unless a == c or a == b
+template <int N>
+QF_HD void fr_inverse(FormR<N> &f) {
+  u32 aw[N + 1];
+  fw_ext<N + 1, N>(aw, f.a, false);
+  bool a_eq_c = fw_cmp<N + 1>(aw, f.c) == 0;
+  bool a_eq_b = fw_cmp<N>(f.a, f.b) == 0;  // b == a > 0: same bit pattern
+  if (!(a_eq_c || a_eq_b)) fw_neg<N>(f.b, f.b);
+}
+
+// packed table entry: a[N] b[N] c[N+1] = 3N+1 words
+template <int N>
+QF_HD void fr_pack(u32 *t, const FormR<N> &f) {
+  QF_UNROLL for (int i = 0; i < N; i++) { t[i] = f.a[i]; t[N + i] = f.b[i]; }
+  QF_UNROLL for (int i = 0; i < N + 1; i++) t[2 * N + i] = f.c[i];
+}
+template <int N>
+QF_HD void fr_unpack(FormR<N> &f, const u32 *t) {
+  QF_UNROLL for (int i = 0; i < N; i++) { f.a[i] = t[i]; f.b[i] = t[N + i]; }
+  QF_UNROLL for (int i = 0; i < N + 1; i++) f.c[i] = t[2 * N + i];
+}
+
+// w-bit digit number `win` (from the least significant end) of an exponent stored with `stride` words between limbs
+QF_HD u32 exp_digit(const u32 *e, int el, size_t stride, int win, int w) {
+  int bit = win * w, li = bit >> 5, sh = bit & 31;
+  if (li >= el) return 0;
+  u64 v = e[(size_t)li * stride];
+  if (li + 1 < el) v |= (u64)e[(size_t)(li + 1) * stride] << 32;
+  return (u32)(v >> sh) & ((1u << w) - 1);
+}
+
+// x <- f^|e| by fixed 2^W-ary windows (left to right).  The loop is a small state machine with exactly one
+// squaring site and one composition site, so the inlined composition code exists twice in the kernel, not once
+// per use.  Fixed windows keep the op sequence of a warp uniform even when every thread has its own exponent
+// (threads whose leading digits are zero idle until their first non-zero digit).
+// tab = per-thread scratch of (2^W - 1) packed forms f^1 .. f^(2^W-1).
+// Returns false on bail or when e == 0 (the neutral form does not fit the register shape: robust path).
+template <int N, int W>
+QF_HD bool fr_pow(FormR<N> &x, const FormR<N> &f, const u32 *e, int el, size_t stride, int dbits, u32 *tab) {
+  constexpr int TE = 3 * N + 1, NT = (1 << W) - 1;
+  int win = (32 * el + W - 1) / W - 1;
+  fr_pack<N>(tab, f);
+  x = f;
+  bool ok = true, started = false;
+  int built = 1, sq_left = 0;
+  u32 d = exp_digit(e, el, stride, win, W);
+  for (;;) {
+    // ---- decide: 0 nothing, 1 square x, 2 compose x with table entry `src`, 3 load x from table entry `src`
+    int op, src = 0;
+    if (built < NT) { op = built == 1 ? 1 : 2; }
+    else if (sq_left > 0) { op = started ? 1 : 0; }
+    else if (d) { op = started ? 2 : 3; src = (int)d - 1; }
+    else op = 0;
+    // ---- execute
+    FormR<N> r;
+    if (op == 1) ok = fq_compose<N, true>(r, x, x, false, dbits);
+    else if (op == 2) {
+      FormR<N> t;
+      fr_unpack<N>(t, tab + src * TE);
+      ok = fq_compose<N, false>(r, x, t, false, dbits);
+    } else if (op == 3) { fr_unpack<N>(r, tab + src * TE); started = true; }
+    else r = x;
+    if (!ok) break;
+    x = r;
+    // ---- advance
+    if (built < NT) {
+      fr_pack<N>(tab + built * TE, x);
+      built++;
+    } else if (sq_left > 0) {
+      sq_left--;
+    } else {
+      win--;
+      if (win < 0) break;
+      sq_left = W;
+      d = exp_digit(e, el, stride, win, W);
+    }
+  }
+  return ok && started;
+}
+
+}  // namespace cofhe

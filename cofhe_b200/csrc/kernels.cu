@@ -9,18 +9,26 @@
 #include <new>
 
 #include "cofhe_b200.h"
-#include "ops.cuh"
+#include "fast_ops.cuh"
 
 using namespace cofhe;
 
 struct cofhe_b200_ctx {
   int device;
   int cap;            // capacity class of the generic integer layer
-  u32 na, nc, nd;
+  u32 na, nc, nd, dbits;
   void *d_group;      // Group<CAP> in device memory
   int *d_err;         // sticky per-context element status (max of Err codes)
   cudaStream_t xfer;  // internal stream of the _host entry points
   uint64_t launches;
+  int fastn;          // limbs of the register-resident instantiation serving this shape (0: none, robust path only)
+  u32 *d_bail;        // elements the fast path declined, redone by the sparse robust kernels
+  int *d_nbail;       // two counters used alternately (the sparse kernel of call k clears the one of call k+1)
+  size_t bail_cap;
+  int flip;
+  // staging of the _host entry points (grown on demand, reused across calls)
+  u32 *d_stage;
+  size_t stage_bytes;
 };
 
 namespace {
@@ -88,9 +96,113 @@ __global__ void __launch_bounds__(kBlock) k_pow(const Group<CAP> *G, Shape s, si
   if (c) atomicMax(err, c);
 }
 
+
+// ---- register-resident fast path (fast_ops.cuh) + sparse robust redo of what it declines -------------------------
+template <int N, bool DUPL>
+__global__ void __launch_bounds__(kBlock) k_fast_compose(int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
+                                                         int neg2, u32 *bail, int *nbail) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
+  FormR<N> f1, f2, r;
+  bool ok = fr_load<N>(f1, in1 + off, nc, n, idx);
+  if (!DUPL) ok = fr_load<N>(f2, in2 + off, nc, n, idx) && ok;
+  ok = ok && fq_compose<N, DUPL>(r, f1, DUPL ? f1 : f2, neg2 != 0, dbits);
+  if (ok) fr_store<N>(r, out + off, nc, n, idx);
+  else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
+}
+template <int N>
+__global__ void __launch_bounds__(kBlock) k_fast_pow(int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
+                                                     int per_elem, const unsigned char *expneg, int shared_neg, u32 *bail,
+                                                     int *nbail) {
+  constexpr int W = 4;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
+  u32 tab[((1 << W) - 1) * (3 * N + 1)];
+  FormR<N> f, r;
+  bool ok = fr_load<N>(f, in + off, nc, n, idx);
+  ok = ok && (per_elem ? fr_pow<N, W>(r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, W>(r, f, exp, el, 1, dbits, tab));
+  if (ok) {
+    if (per_elem ? (expneg && expneg[idx]) : shared_neg != 0) fr_inverse<N>(r);
+    fr_store<N>(r, out + off, nc, n, idx);
+  } else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
+}
+// op: 0 compose, 1 square, 2 pow.  Grid-stride over the bail list; clears the counter of the next call.
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, size_t n, int op, const u32 *in1, const u32 *in2,
+                                                 u32 *out, int neg2, const u32 *exp, int el, int per_elem,
+                                                 const unsigned char *expneg, int shared_neg, const u32 *bail, const int *nbail,
+                                                 int *nbail_next, int *err) {
+  int cnt = *nbail;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *nbail_next = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += gridDim.x * blockDim.x) {
+    u32 e = bail[i];
+    size_t y = e / n, idx = e % n, off = y * form_limbs(s) * n;
+    int c;
+    if (op == 0) c = op_compose<CAP>(*G, s, n, idx, in1 + off, in2 + off, out + off, neg2 != 0);
+    else if (op == 1) c = op_square<CAP>(*G, s, n, idx, in1 + off, out + off);
+    else c = op_pow<CAP>(*G, s, n, idx, in1 + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
+    if (c) atomicMax(err, c);
+  }
+}
+
+#define FAST_DISPATCH(fn, ...)                                 \
+  switch (fn) {                                                \
+    case 2: { constexpr int FN = 2; __VA_ARGS__; } break;      \
+    case 4: { constexpr int FN = 4; __VA_ARGS__; } break;      \
+    case 7: { constexpr int FN = 7; __VA_ARGS__; } break;      \
+    case 11: { constexpr int FN = 11; __VA_ARGS__; } break;    \
+    default: return COFHE_B200_EINVAL;                         \
+  }
+int fast_n_for(u32 na) { return (na == 2 || na == 4 || na == 7 || na == 11) && !getenv("COFHE_B200_NO_FAST") ? (int)na : 0; }
+
+int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
+  if (entries >> 32) return COFHE_B200_EINVAL;
+  if (entries <= ctx->bail_cap) return COFHE_B200_OK;
+  if (ctx->d_bail) cudaFree(ctx->d_bail);  // synchronises with kernels still reading the old list
+  ctx->d_bail = nullptr; ctx->bail_cap = 0;
+  if (cudaMalloc(&ctx->d_bail, entries * sizeof(u32)) != cudaSuccess) return COFHE_B200_ENOMEM;
+  ctx->bail_cap = entries;
+  return COFHE_B200_OK;
+}
+
 int check_launch(cofhe_b200_ctx *ctx) {
   ctx->launches++;
   return cudaGetLastError() == cudaSuccess ? COFHE_B200_OK : COFHE_B200_ECUDA;
+}
+
+
+// One batched form operation (op: 0 compose, 1 square, 2 pow) over ny form blocks of n elements.
+int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1, const u32 *in2, u32 *out, int neg2,
+              const u32 *exp, int el, int per_elem, const unsigned char *expneg, int shared_neg, cudaStream_t st) {
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  dim3 grid(grid_for(n), ny);
+  if (!ctx->fastn) {
+    CAP_DISPATCH(ctx->cap, {
+      const Group<CAP> *G = (const Group<CAP> *)ctx->d_group;
+      if (op == 0) k_compose<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, in2, out, neg2, ctx->d_err);
+      else if (op == 1) k_square<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, ctx->d_err);
+      else k_pow<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_err);
+    })
+    return check_launch(ctx);
+  }
+  int rc = ensure_bail(ctx, (size_t)ny * n);
+  if (rc != COFHE_B200_OK) return rc;
+  int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
+  ctx->flip ^= 1;
+  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  FAST_DISPATCH(ctx->fastn, {
+    if (op == 0) k_fast_compose<FN, false><<<grid, kBlock, 0, st>>>(dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+    else if (op == 1) k_fast_compose<FN, true><<<grid, kBlock, 0, st>>>(dbits, nc, n, in1, in1, out, 0, ctx->d_bail, cnt);
+    else k_fast_pow<FN><<<grid, kBlock, 0, st>>>(dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_bail, cnt);
+  })
+  rc = check_launch(ctx);
+  if (rc != COFHE_B200_OK) return rc;
+  unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
+  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, op, in1, in2, out, neg2, exp, el,
+                                                          per_elem, expneg, shared_neg, ctx->d_bail, cnt, cnt_next, ctx->d_err))
+  return check_launch(ctx);
 }
 
 struct DevGuard {
@@ -130,6 +242,10 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->na = (u32)((dbits / 2 + 1 + 31) / 32);
   ctx->nc = n;
   ctx->launches = 0;
+  ctx->dbits = (u32)dbits;
+  ctx->fastn = fast_n_for(ctx->na);
+  ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
+  ctx->d_stage = nullptr; ctx->stage_bytes = 0;
   ctx->d_group = nullptr;
   ctx->d_err = nullptr;
   ctx->xfer = nullptr;
@@ -148,6 +264,8 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   })
   if (rc == COFHE_B200_OK && (cudaMalloc(&ctx->d_err, sizeof(int)) != cudaSuccess ||
                               cudaMemset(ctx->d_err, 0, sizeof(int)) != cudaSuccess ||
+                              cudaMalloc(&ctx->d_nbail, 2 * sizeof(int)) != cudaSuccess ||
+                              cudaMemset(ctx->d_nbail, 0, 2 * sizeof(int)) != cudaSuccess ||
                               cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking) != cudaSuccess))
     rc = COFHE_B200_ECUDA;
   if (rc != COFHE_B200_OK) { cofhe_b200_destroy(ctx); return rc; }
@@ -160,6 +278,9 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   DevGuard g(ctx->device);
   if (ctx->d_group) cudaFree(ctx->d_group);
   if (ctx->d_err) cudaFree(ctx->d_err);
+  if (ctx->d_bail) cudaFree(ctx->d_bail);
+  if (ctx->d_nbail) cudaFree(ctx->d_nbail);
+  if (ctx->d_stage) cudaFree(ctx->d_stage);
   if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
   delete ctx;
 }
@@ -196,10 +317,7 @@ int cofhe_b200_nucomp(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f1, const u
   if (n == 0) return COFHE_B200_OK;
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
-  Shape s{(int)ctx->na, (int)ctx->nc};
-  CAP_DISPATCH(ctx->cap, k_compose<CAP><<<dim3(grid_for(n), 1), kBlock, 0, (cudaStream_t)stream>>>(
-                             (const Group<CAP> *)ctx->d_group, s, n, f1, f2, out, negf2, ctx->d_err))
-  return check_launch(ctx);
+  return launch_op(ctx, 0, 1, n, f1, f2, out, negf2, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
 
 int cofhe_b200_nudupl(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *out, void *stream) {
@@ -207,10 +325,7 @@ int cofhe_b200_nudupl(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t
   if (n == 0) return COFHE_B200_OK;
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
-  Shape s{(int)ctx->na, (int)ctx->nc};
-  CAP_DISPATCH(ctx->cap, k_square<CAP><<<dim3(grid_for(n), 1), kBlock, 0, (cudaStream_t)stream>>>(
-                             (const Group<CAP> *)ctx->d_group, s, n, f, out, ctx->d_err))
-  return check_launch(ctx);
+  return launch_op(ctx, 1, 1, n, f, f, out, 0, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
 
 int cofhe_b200_reduce(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t na_in, uint32_t nc_in, uint32_t *out,
@@ -231,11 +346,7 @@ int cofhe_b200_nupow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, const uin
   if (n == 0) return COFHE_B200_OK;
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
-  Shape s{(int)ctx->na, (int)ctx->nc};
-  CAP_DISPATCH(ctx->cap, k_pow<CAP><<<dim3(grid_for(n), 1), kBlock, 0, (cudaStream_t)stream>>>(
-                             (const Group<CAP> *)ctx->d_group, s, n, f, out, exp, (int)el, per_elem, expneg, shared_neg,
-                             ctx->d_err))
-  return check_launch(ctx);
+  return launch_op(ctx, 2, 1, n, f, f, out, 0, exp, (int)el, per_elem, expneg, shared_neg, (cudaStream_t)stream);
 }
 
 int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
@@ -244,10 +355,7 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
   if (n == 0) return COFHE_B200_OK;
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
-  Shape s{(int)ctx->na, (int)ctx->nc};
-  CAP_DISPATCH(ctx->cap, k_compose<CAP><<<dim3(grid_for(n), 2), kBlock, 0, (cudaStream_t)stream>>>(
-                             (const Group<CAP> *)ctx->d_group, s, n, ct1, ct2, out, 0, ctx->d_err))
-  return check_launch(ctx);
+  return launch_op(ctx, 0, 2, n, ct1, ct2, out, 0, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
 
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
@@ -257,10 +365,14 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
   size_t bytes = (size_t)2 * (2 * ctx->na + ctx->nc) * n * sizeof(u32);
-  u32 *d1 = nullptr, *d2 = nullptr, *d3 = nullptr;
   int rc = COFHE_B200_OK;
-  if (cudaMalloc(&d1, bytes) != cudaSuccess || cudaMalloc(&d2, bytes) != cudaSuccess || cudaMalloc(&d3, bytes) != cudaSuccess)
-    rc = COFHE_B200_ENOMEM;
+  if (ctx->stage_bytes < 3 * bytes) {
+    if (ctx->d_stage) cudaFree(ctx->d_stage);
+    ctx->d_stage = nullptr; ctx->stage_bytes = 0;
+    if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) rc = COFHE_B200_ENOMEM;
+    else ctx->stage_bytes = 3 * bytes;
+  }
+  u32 *d1 = ctx->d_stage, *d2 = d1 + bytes / 4, *d3 = d2 + bytes / 4;
   if (rc == COFHE_B200_OK && (cudaMemcpyAsync(d1, ct1, bytes, cudaMemcpyHostToDevice, ctx->xfer) != cudaSuccess ||
                               cudaMemcpyAsync(d2, ct2, bytes, cudaMemcpyHostToDevice, ctx->xfer) != cudaSuccess))
     rc = COFHE_B200_ECUDA;
@@ -269,7 +381,6 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
     rc = COFHE_B200_ECUDA;
   if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->xfer);
   else cudaStreamSynchronize(ctx->xfer);
-  cudaFree(d1); cudaFree(d2); cudaFree(d3);
   return rc;
 }
 

@@ -138,3 +138,44 @@ def test_fast_vs_generic_chained(name, n, rounds):
     # self-compositions (same `a` in both operands) are the only expected bails
     assert total_bail < n * rounds * 3 * 0.002, total_bail
     print("bails", total_bail, "of", n * rounds * 3)
+
+
+def test_fast_pow_kat_and_fixtures():
+    """fr_pow (fixed 4-bit windows on the register path) against the reference's nupow KATs and fixtures."""
+    kat = load_golden("bicycl_nupow_kat.json")["vectors"]
+    by = {}
+    for v in kat:
+        f, n, r = I(v["f"]), int(v["n"]), I(v["r"])
+        by.setdefault(O.disc(f), []).append((f, n, r))
+    for name in ("tiny", "t0", "node"):
+        t = load_golden("ref_%s.json" % name)
+        by.setdefault(int(t["params"]["Delta"]), []).extend((I(v["f"]), abs(int(v["n"])), None) for v in t["nupow"])
+    ran = 0
+    for D, vs in by.items():
+        S = FastSim(D)
+        if not S.ok():
+            continue
+        n = len(vs)
+        el = max(1, max((e.bit_length() + 31) // 32 for _, e, _ in vs))
+        inp = L.forms_to_limbs([v[0] for v in vs], S.na, S.nc)
+        ex = L.ints_to_limbs([v[1] for v in vs], el)
+        out = np.zeros_like(inp)
+        bail = np.zeros(n, dtype=np.uint8)
+        S.lib.hs_fast_pow(S.na, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(ex), el, 1, HS.P(bail))
+        got = L.limbs_to_forms(out, S.na, S.nc)
+        for i, (f, e, r) in enumerate(vs):
+            if e == 0:
+                assert bail[i]
+                continue
+            if not bail[i]:
+                assert got[i] == (r if r is not None else O.power(f, e)), (D, i)
+                ran += 1
+        # shared exponent
+        e = vs[0][1] or 5
+        exs = L.ints_to_limbs([e], max(1, (e.bit_length() + 31) // 32))[:, 0].copy()
+        S.lib.hs_fast_pow(S.na, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(exs), len(exs), 0, HS.P(bail))
+        got = L.limbs_to_forms(out, S.na, S.nc)
+        for i in range(min(n, 6)):
+            if not bail[i]:
+                assert got[i] == O.power(vs[i][0], e)
+    assert ran >= 100
