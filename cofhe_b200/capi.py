@@ -32,6 +32,7 @@ SIGNATURES = {
     "cofhe_b200_nupow": (i32, [vp, sz, vp, vp, u32, i32, vp, i32, vp, vp]),
     "cofhe_b200_add_ciphertexts": (i32, [vp, sz, vp, vp, vp, vp]),
     "cofhe_b200_add_ciphertexts_host": (i32, [vp, sz, vp, vp, vp]),
+    "cofhe_b200_scal_matmul": (i32, [vp, sz, sz, sz, vp, vp, u32, u32, vp, vp, vp]),
     "cofhe_b200_imad_probe": (i32, [i32, i32, ctypes.POINTER(ctypes.c_double)]),
 }
 

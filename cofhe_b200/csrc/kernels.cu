@@ -10,6 +10,7 @@
 
 #include "cofhe_b200.h"
 #include "fast_ops.cuh"
+#include "matmul.cuh"
 
 using namespace cofhe;
 
@@ -29,6 +30,9 @@ struct cofhe_b200_ctx {
   // staging of the _host entry points (grown on demand, reused across calls)
   u32 *d_stage;
   size_t stage_bytes;
+  // scratch of the composite operations (matmul tables and partial products, fixed-base digits, ...)
+  u32 *d_work;
+  size_t work_bytes;
 };
 
 namespace {
@@ -167,6 +171,15 @@ int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
   return COFHE_B200_OK;
 }
 
+int ensure_work(cofhe_b200_ctx *ctx, size_t bytes) {
+  if (bytes <= ctx->work_bytes) return COFHE_B200_OK;
+  if (ctx->d_work) cudaFree(ctx->d_work);  // synchronises with kernels still using the old scratch
+  ctx->d_work = nullptr; ctx->work_bytes = 0;
+  if (cudaMalloc(&ctx->d_work, bytes) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+  ctx->work_bytes = bytes;
+  return COFHE_B200_OK;
+}
+
 int check_launch(cofhe_b200_ctx *ctx) {
   ctx->launches++;
   return cudaGetLastError() == cudaSuccess ? COFHE_B200_OK : COFHE_B200_ECUDA;
@@ -246,6 +259,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->fastn = fast_n_for(ctx->na);
   ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
   ctx->d_stage = nullptr; ctx->stage_bytes = 0;
+  ctx->d_work = nullptr; ctx->work_bytes = 0;
   ctx->d_group = nullptr;
   ctx->d_err = nullptr;
   ctx->xfer = nullptr;
@@ -281,6 +295,7 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_bail) cudaFree(ctx->d_bail);
   if (ctx->d_nbail) cudaFree(ctx->d_nbail);
   if (ctx->d_stage) cudaFree(ctx->d_stage);
+  if (ctx->d_work) cudaFree(ctx->d_work);
   if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
   delete ctx;
 }
@@ -358,6 +373,65 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
   return launch_op(ctx, 0, 2, n, ct1, ct2, out, 0, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
 
+int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct, const uint32_t *scal,
+                           uint32_t el, uint32_t ebits, const uint32_t *init, uint32_t *out, void *stream) {
+  if (!ctx || el == 0 || !init || ((n && p) && !out) || ((n && m) && !ct) || ((m && p) && !scal)) return COFHE_B200_EINVAL;
+  if (n == 0 || p == 0) return COFHE_B200_OK;
+  if ((n * p) >> 30 || (n * m) >> 30 || (m * p) >> 30) return COFHE_B200_EINVAL;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  Shape sh{(int)ctx->na, (int)ctx->nc};
+  MMShape s;
+  s.n = (unsigned)n; s.m = (unsigned)m; s.p = (unsigned)p; s.el = (int)el;
+  s.W = 4;
+  if (const char *w = getenv("COFHE_B200_MM_W")) { int v = atoi(w); if (v >= 2 && v <= 8) s.W = v; }
+  if (ebits == 0 || ebits > 32 * el) ebits = 32 * el;
+  s.nwin = (int)((ebits + s.W - 1) / s.W);
+  size_t no = n * p;
+  if (!ctx->fastn || m == 0) {
+    // robust path over every output (tiers without a register-resident instantiation)
+    s.chunks = 1; s.jper = (unsigned)m;
+    unsigned blocks = (unsigned)((2 * no + kMMBlock - 1) / kMMBlock);
+    CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
+                                                                       nullptr, nullptr, nullptr, ctx->d_err))
+    return check_launch(ctx);
+  }
+  // split the j range so that small n*p still fills the machine
+  size_t want = (size_t)148 * 4 * kMMBlock;
+  size_t ch = (want + 2 * no - 1) / (2 * no);
+  if (ch > m / 2) ch = m / 2;
+  if (ch < 1) ch = 1;
+  if (const char *c = getenv("COFHE_B200_MM_CHUNKS")) { int v = atoi(c); if (v >= 1 && (size_t)v <= m) ch = (size_t)v; }
+  s.jper = (unsigned)((m + ch - 1) / ch);
+  s.chunks = (unsigned)((m + s.jper - 1) / s.jper);
+  int rc = ensure_bail(ctx, 2 * no);
+  if (rc != COFHE_B200_OK) return rc;
+  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  FAST_DISPATCH(ctx->fastn, {
+    constexpr int TE = MMLayout<FN>::TE;
+    size_t tab_words = (size_t)2 * n * m * s.nwin * ((1u << s.W) - 1) * TE;
+    size_t part_words = (size_t)s.chunks * 2 * no * TE;
+    rc = ensure_work(ctx, (tab_words + part_words) * sizeof(u32));
+    if (rc != COFHE_B200_OK) return rc;
+    u32 *tab = ctx->d_work, *part = tab + tab_words;
+    size_t nb = n * m;
+    k_mm_chain<FN><<<dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(dbits, nc, s, ct, tab);
+    ctx->launches++;
+    k_mm_fill<FN><<<dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(dbits, s, tab);
+    ctx->launches++;
+    k_mm_accum<FN><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), kMMBlock, 0, st>>>(dbits, s, scal, tab, part);
+    ctx->launches++;
+    int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
+    ctx->flip ^= 1;
+    k_mm_final<FN><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(dbits, nc, s, init, part, out, ctx->d_bail, cnt);
+    ctx->launches++;
+    CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<32, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
+                                                                   ctx->d_bail, cnt, cnt_next, ctx->d_err))
+  })
+  return check_launch(ctx);
+}
+
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out) {
   if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
@@ -368,7 +442,9 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   int rc = COFHE_B200_OK;
   if (ctx->stage_bytes < 3 * bytes) {
     if (ctx->d_stage) cudaFree(ctx->d_stage);
+  if (ctx->d_work) cudaFree(ctx->d_work);
     ctx->d_stage = nullptr; ctx->stage_bytes = 0;
+  ctx->d_work = nullptr; ctx->work_bytes = 0;
     if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) rc = COFHE_B200_ENOMEM;
     else ctx->stage_bytes = 3 * bytes;
   }

@@ -1,0 +1,196 @@
+// cofhe_b200 -- scalar x ciphertext matmul as a batched multi-exponentiation (register-resident fast path).
+//
+//   out[i,k] = init o prod_j ct[i,j]^{s[j,k]}          ct: n x m ciphertexts, s: m x p non-negative scalars
+//
+// replaces CPUCryptoSystem::scal_ciphertext_tensors, matmul branch (reference
+// include/x86_64/cpu_cryptosystem_tensor_ops.inl:346-461: qfi_nupow per (i,j) over the p scalars of row j, then the
+// accumulation over j).  Only the reduced results are contractual, so the work is organised for the GPU instead:
+//   1. k_mm_chain : per base form ct[i,j]:   B_w = ct[i,j]^(2^(W*w)),  w = 0..nwin-1      (W squarings per window)
+//   2. k_mm_fill  : per (base, window):      T[w][d] = B_w^d,  d = 1..2^W-1               (one squaring, 2^W-3 comps)
+//   3. k_mm_accum : per (chunk, i, k):       P = prod_{j in chunk} prod_w T_{ij}[w][digit_w(s[j,k])]   (comps only)
+//   4. k_mm_final : per (i, k):              out = init o prod_chunks P
+// Every product is a plain composition, so there is no squaring chain per output and the j range can be split
+// into chunks freely to fill the machine when n*p is small.  Each base is reused by p outputs and each scalar by n.
+// Elements the fast path declines anywhere are appended to the bail list and recomputed on the robust path.
+#pragma once
+#include "fast_ops.cuh"
+
+namespace cofhe {
+
+// packed table entry stride (words), padded to 16 bytes
+template <int N>
+struct MMLayout {
+  static constexpr int TE = ((3 * N + 1) + 3) & ~3;
+};
+// entry markers (a[0] == 0 never happens for a valid form whose a > 0 fits... use a full-zero `a` instead):
+// valid form: a != 0.  a == 0 && b[0] == 0: "empty product".  a == 0 && b[0] == 1: "declined".
+template <int N>
+QF_HD void mm_mark(u32 *t, u32 kind) {
+  QF_UNROLL for (int i = 0; i < MMLayout<N>::TE; i++) t[i] = 0;
+  t[N] = kind;
+}
+template <int N>
+QF_HD int mm_kind(const u32 *t) {  // 0 valid, 1 empty, 2 declined
+  u32 o = 0;
+  QF_UNROLL for (int i = 0; i < N; i++) o |= t[i];
+  return o ? 0 : (t[N] ? 2 : 1);
+}
+template <int N>
+QF_HD void mm_store(u32 *t, const FormR<N> &f) {
+  fr_pack<N>(t, f);
+  QF_UNROLL for (int i = 3 * N + 1; i < MMLayout<N>::TE; i++) t[i] = 0;
+}
+
+struct MMShape {
+  unsigned n, m, p;     // ct is n x m, scalars m x p
+  int nwin, W;          // windows per scalar, window width
+  int el;               // limbs per scalar
+  unsigned chunks, jper;  // j range split: chunks * jper >= m
+};
+
+QF_HD size_t mm_tab_index(const MMShape &s, unsigned y, size_t base, int win, int d) {
+  return ((((size_t)y * s.n * s.m + base) * s.nwin + win) * ((1u << s.W) - 1) + (d - 1));
+}
+
+
+#if defined(__CUDACC__)
+constexpr int kMMBlock = 128;
+
+// 1. one thread per (y, base): B_w = ct^(2^(W*w)) into T[w][1]
+template <int N>
+__global__ void __launch_bounds__(kMMBlock) k_mm_chain(int dbits, int nc, MMShape s, const u32 *ct, u32 *tab) {
+  constexpr int TE = MMLayout<N>::TE;
+  size_t nb = (size_t)s.n * s.m;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nb) return;
+  unsigned y = blockIdx.y;
+  FormR<N> x, r;
+  bool ok = fr_load<N>(x, ct + (size_t)y * (2 * N + nc) * nb, nc, nb, idx);
+  int total = (s.nwin - 1) * s.W;
+  for (int t = 0;; t++) {
+    if (t % s.W == 0) {
+      u32 *e = tab + mm_tab_index(s, y, idx, t / s.W, 1) * TE;
+      if (ok) mm_store<N>(e, x); else mm_mark<N>(e, 1);
+    }
+    if (t >= total) break;
+    if (ok) {
+      ok = fq_compose<N, true>(r, x, x, false, dbits);
+      x = r;
+    }
+  }
+}
+
+// 2. one thread per (y, base, window): T[w][d] = B_w^d
+template <int N>
+__global__ void __launch_bounds__(kMMBlock) k_mm_fill(int dbits, MMShape s, u32 *tab) {
+  constexpr int TE = MMLayout<N>::TE;
+  size_t total = (size_t)s.n * s.m * s.nwin;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  unsigned y = blockIdx.y;
+  size_t base = idx / s.nwin;
+  int win = (int)(idx % s.nwin);
+  u32 *e = tab + mm_tab_index(s, y, base, win, 1) * TE;
+  FormR<N> f, x, r;
+  bool ok = mm_kind<N>(e) == 0;
+  fr_unpack<N>(f, e);
+  x = f;
+  int nt = (1 << s.W) - 1;
+  for (int d = 2; d <= nt; d++) {
+    if (ok) {
+      ok = d == 2 ? fq_compose<N, true>(r, x, x, false, dbits) : fq_compose<N, false>(r, x, f, false, dbits);
+      x = r;
+    }
+    if (ok) mm_store<N>(e + (size_t)(d - 1) * TE, x); else mm_mark<N>(e + (size_t)(d - 1) * TE, 1);
+  }
+}
+
+// 3. one thread per (chunk, y, i, k): product over the chunk's j range and all windows; compositions only
+template <int N>
+__global__ void __launch_bounds__(kMMBlock) k_mm_accum(int dbits, MMShape s, const u32 *scal, const u32 *tab, u32 *part) {
+  constexpr int TE = MMLayout<N>::TE;
+  size_t no = (size_t)s.n * s.p;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= no) return;
+  unsigned y = blockIdx.y, c = blockIdx.z;
+  unsigned i = (unsigned)(idx / s.p), k = (unsigned)(idx % s.p);
+  unsigned j0 = c * s.jper, j1 = j0 + s.jper < s.m ? j0 + s.jper : s.m;
+  size_t sstride = (size_t)s.m * s.p;
+  FormR<N> x, t, r;
+  bool ok = true, started = false;
+  for (unsigned j = j0; j < j1 && ok; j++) {
+    const u32 *e = scal + (size_t)j * s.p + k;
+    for (int w = 0; w < s.nwin; w++) {
+      u32 d = exp_digit(e, s.el, sstride, w, s.W);
+      if (!d) continue;
+      const u32 *te = tab + mm_tab_index(s, y, (size_t)i * s.m + j, w, (int)d) * TE;
+      if (mm_kind<N>(te) != 0) { ok = false; break; }
+      fr_unpack<N>(t, te);
+      if (started) {
+        ok = fq_compose<N, false>(r, x, t, false, dbits);
+        if (!ok) break;
+        x = r;
+      } else { x = t; started = true; }
+    }
+  }
+  u32 *o = part + (((size_t)c * 2 + y) * no + idx) * TE;
+  if (!ok) mm_mark<N>(o, 1);
+  else if (!started) mm_mark<N>(o, 0);
+  else mm_store<N>(o, x);
+}
+
+// 4. one thread per (y, i, k): out = init o prod_chunks part
+template <int N>
+__global__ void __launch_bounds__(kMMBlock) k_mm_final(int dbits, int nc, MMShape s, const u32 *init, const u32 *part, u32 *out,
+                                                       u32 *bail, int *nbail) {
+  constexpr int TE = MMLayout<N>::TE;
+  size_t no = (size_t)s.n * s.p;
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= no) return;
+  unsigned y = blockIdx.y;
+  FormR<N> x, t, r;
+  bool ok = fr_load<N>(x, init + (size_t)y * (2 * N + nc), nc, 1, 0);
+  for (unsigned c = 0; c < s.chunks && ok; c++) {
+    const u32 *pe = part + (((size_t)c * 2 + y) * no + idx) * TE;
+    int kind = mm_kind<N>(pe);
+    if (kind == 1) continue;
+    if (kind == 2) { ok = false; break; }
+    fr_unpack<N>(t, pe);
+    ok = fq_compose<N, false>(r, x, t, false, dbits);
+    x = r;
+  }
+  if (ok) fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);
+  else bail[atomicAdd(nbail, 1)] = (u32)(y * no + idx);
+}
+
+// robust path: all outputs (list == nullptr) or the listed ones; clears the next call's counter
+template <int CAP>
+__global__ void __launch_bounds__(kMMBlock) k_mm_robust(const Group<CAP> *G, Shape sh, MMShape s, const u32 *ct, const u32 *scal,
+                                                        const u32 *init, u32 *out, const u32 *bail, const int *nbail,
+                                                        int *nbail_next, int *err) {
+  size_t no = (size_t)s.n * s.p, nb = (size_t)s.n * s.m;
+  size_t cnt = bail ? (size_t)*nbail : 2 * no;
+  if (nbail_next && blockIdx.x == 0 && threadIdx.x == 0) *nbail_next = 0;
+  for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < cnt; q += (size_t)gridDim.x * blockDim.x) {
+    size_t e = bail ? bail[q] : q;
+    size_t y = e / no, idx = e % no;
+    unsigned i = (unsigned)(idx / s.p), k = (unsigned)(idx % s.p);
+    Err er; er.code = 0;
+    Form<CAP> acc, f, t;
+    form_load(er, acc, init + y * form_limbs(sh), sh, 1, 0);
+    for (unsigned j = 0; j < s.m && !er.code; j++) {
+      const u32 *ex = scal + (size_t)j * s.p + k;
+      bool zero = true;
+      for (int l = 0; l < s.el; l++) zero = zero && ex[(size_t)l * s.m * s.p] == 0;
+      if (zero) continue;
+      form_load(er, f, ct + y * form_limbs(sh) * nb, sh, nb, (size_t)i * s.m + j);
+      qf_pow(er, *G, t, f, ex, s.el, (size_t)s.m * s.p, false);
+      qf_compose(er, *G, acc, acc, t, false, false);
+    }
+    form_store(er, acc, out + y * form_limbs(sh) * no, sh, no, idx);
+    if (er.code) atomicMax(err, er.code);
+  }
+}
+#endif
+
+}  // namespace cofhe

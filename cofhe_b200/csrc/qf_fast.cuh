@@ -15,6 +15,12 @@
 #include "fw.cuh"
 #include "lehmer.cuh"
 
+// Test hook: a host build may define QF_NOTE to record which guard declined an element (tests/hostsim).
+#ifndef QF_NOTE
+#define QF_NOTE ((void)0)
+#endif
+#define QF_BAIL do { QF_NOTE; return false; } while (0)
+
 namespace cofhe {
 
 template <int N>
@@ -100,7 +106,7 @@ QF_HD u32 fw_lin_add(u32 *r, u32 x, const u32 *A, u32 y, const u32 *B) {
 template <int N, int NC>
 QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail) {
   int lsh = fw_lead_zero_limbs<N>(R0);
-  if (lsh >= N) { bail = true; return 0; }
+  if (lsh >= N) { { bail = true; QF_NOTE; } return 0; }
   fw_shl_limbs<N>(R0, lsh);
   fw_shl_limbs<N>(R1, lsh);
   int sb = stop_bits + 32 * lsh;
@@ -127,7 +133,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
     if (M.j == 1) {
       // one full-precision division step with a quotient of at most 30 bits
       int b0 = 32 * N - clz32(R0[N - 1]);
-      if (b0 - b1 > 29) { bail = true; break; }
+      if (b0 - b1 > 29) { { bail = true; QF_NOTE; } break; }
       int s2 = clz32(R0[N - 1]);
       u64 A64 = ((u64)R0[N - 1] << 32) | R0[N >= 2 ? N - 2 : 0];
       u64 B64 = ((u64)R1[N - 1] << 32) | R1[N >= 2 ? N - 2 : 0];
@@ -141,18 +147,18 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       u32 t[N];
       fw_copy<N>(t, R0);
       u32 bo = fw_submul1<N>(t, R1, q);
-      if (bo) { bail = true; break; }  // cannot happen: q underestimates
+      if (bo) { { bail = true; QF_NOTE; } break; }  // cannot happen: q underestimates
       int fix = 0;
       while (!fw_lt<N>(t, R1)) {
         fw_sub<N>(t, t, R1);
         q++;
-        if (++fix > 8) { bail = true; break; }
+        if (++fix > 8) { { bail = true; QF_NOTE; } break; }
       }
       if (bail) break;
       u32 cn[NC + 1];
       fw_mul1<NC>(cn, C1, q);
       u32 cy = fw_add<NC>(cn, cn, C0);
-      if (cn[NC] | cy) { bail = true; break; }
+      if (cn[NC] | cy) { { bail = true; QF_NOTE; } break; }
       fw_copy<N>(R0, R1);
       fw_copy<N>(R1, t);
       fw_copy<NC>(C0, C1);
@@ -169,12 +175,12 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       u32 c0[NC], c1[NC];
       u32 o0 = fw_lin_add<NC>(c0, M.S0, C0, M.T0, C1);
       u32 o1 = fw_lin_add<NC>(c1, M.S1, C0, M.T1, C1);
-      if (o0 | o1) { bail = true; break; }
+      if (o0 | o1) { { bail = true; QF_NOTE; } break; }
       fw_copy<NC>(C0, c0);
       fw_copy<NC>(C1, c1);
       steps += M.j - 1;
     }
-    if (guard == 80 * N - 1) bail = true;
+    if (guard == 80 * N - 1) { bail = true; QF_NOTE; }
   }
   fw_shr_limbs<N>(R0, lsh);
   fw_shr_limbs<N>(R1, lsh);
@@ -203,13 +209,13 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
     // ---- normalise: -a < b <= a
     int ba = fw_bits<N>(a);
     // c stays within W limbs only while a is not too small
-    if (ba == 0 || ba < dbits - 32 * W + 3) return false;
+    if (ba == 0 || ba < dbits - 32 * W + 3) QF_BAIL;
     bool bneg = b[W - 1] >> 31;
     u32 bm[W];
     fw_cneg<W>(bm, b, bneg);
     int bb = fw_bits<W>(bm);
     if (bb >= ba) {
-      if (bb - ba > 28) return false;
+      if (bb - ba > 28) QF_BAIL;
       // k = round-ish(b / 2a) from the leading 64 bits, then exact fix-up
       u32 aw[W];
       fw_ext<W, N>(aw, a, false);
@@ -232,7 +238,7 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
       fw_shl_bits<W>(a2, aw, 1);
       u32 r[W];
       fw_copy<W>(r, bm);
-      if (k) { if (fw_submul1<W>(r, a2, k)) return false; }
+      if (k) { if (fw_submul1<W>(r, a2, k)) QF_BAIL; }
       // bring r into (-a, a] for b > 0, [-a, a) for b < 0  (r is treated as signed from here)
       int fix = 0;
       for (;;) {
@@ -243,7 +249,7 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
         if (!over) break;
         fw_sub<W>(r, r, a2);
         k++;
-        if (++fix > 8) return false;
+        if (++fix > 8) QF_BAIL;
       }
       // signed k and new b:  b' = sign * r ; c' = c - ks*(b + b')/2 , with (b + b')/2 = sign*(|b| + r)/2
       u32 hs[W];
@@ -252,7 +258,7 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
       // c' = c - k*hs  (sign*sign = +)
       if (k) {
         u32 bo = fw_submul1<W>(c, hs, k);
-        if (bo) return false;
+        if (bo) QF_BAIL;
       }
       fw_cneg<W>(b, r, bneg);
     }
@@ -264,14 +270,14 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
       if (cmp == 0 && (b[W - 1] >> 31)) fw_neg<W>(b, b);
       return true;
     }
-    if (c[N] != 0) return false;  // cannot be: c < a
+    if (c[N] != 0) QF_BAIL;  // cannot be: c < a
     u32 t[N];
     fw_copy<N>(t, a);
     fw_copy<N>(a, c);
     fw_ext<W, N>(c, t, false);
     fw_neg<W>(b, b);
   }
-  return false;
+  QF_BAIL;
 }
 
 // r = f1 o f2 (neg2: f1 o f2^-1; DUPL: f1^2, f2 ignored).  Returns false (bail) when the element must take the
@@ -280,7 +286,9 @@ template <int N, bool DUPL>
 QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool neg2, int dbits) {
   constexpr int W = N + 1;
   constexpr int M = (N + 1) / 2 + 1;  // half width of the post-Euclid quantities
-  constexpr int L = M + 1;            // numerators carry one extra limb for the 2-adic shift
+  // numerators carry extra limbs for the 2-adic shift: a1 = 2^tz * odd with tz < 32*(L-M).  In these non-maximal
+  // orders (Delta = -2^(2k+5) N) P(2^j | a) decays only like 2^(-j/2), so tz >= 32 does occur (~2^-17 per step).
+  constexpr int L = (M + 2 <= W) ? M + 2 : M + 1;
   bool bail = false;
 
   // ---- operands, larger `a` first
@@ -308,15 +316,15 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     u32 R0[N], R1[N], C0[N], C1[N];
     fw_copy<N>(R0, a1); fw_copy<N>(R1, a2); fw_zero<N>(C0); fw_zero<N>(C1); C1[0] = 1;
     int st = fw_hxgcd<N, N>(R0, R1, C0, C1, 0, bail);
-    if (bail) return false;
-    if (!fw_high_zero<N, 1>(R0)) return false;  // gcd(a1,a2) >= 2^32: robust path
+    if (bail) QF_BAIL;
+    if (!fw_high_zero<N, 1>(R0)) QF_BAIL;  // gcd(a1,a2) >= 2^32: robust path
     u32 F = R0[0];
     bool vneg = (st & 1) == 0;  // sign(C_st) = (-1)^(st+1)
     // t = |v| * |m| mod By, with By = a1/G
     u32 mneg = m[W - 1] >> 31;
     u32 mm[W];
     fw_cneg<W>(mm, m, mneg);
-    if (mm[N] != 0) return false;
+    if (mm[N] != 0) QF_BAIL;
     u32 x0m = 1; bool x0neg = false; u32 y0m = 0; bool y0neg = false;
     u32 x0big[N]; bool x0_is_big = false;
     fw_zero<N>(x0big);
@@ -325,7 +333,7 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
       u32 sneg = s[W - 1] >> 31;
       u32 sm_[W];
       fw_cneg<W>(sm_, s, sneg);
-      if (sm_[N] != 0) return false;
+      if (sm_[N] != 0) QF_BAIL;
       u32 srem = fw_mod1<N>(sm_, F);  // |s| mod F
       if (srem == 0) {
         G = F;
@@ -351,7 +359,7 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
         }
         u32 xq[W];
         fw_divexact1<W>(xq, num, F);
-        if (xq[N] != 0) return false;
+        if (xq[N] != 0) QF_BAIL;
         fw_copy<N>(x0big, xq);
         x0neg = nneg;
         x0_is_big = true;
@@ -362,26 +370,26 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     // t = (|v|*|m|) mod By
     u32 prod[2 * N], t[N];
     fw_mul<N, N>(prod, C0, mm);
-    if (!fw_mod<2 * N, N>(t, prod, By)) return false;
+    if (!fw_mod<2 * N, N>(t, prod, By)) QF_BAIL;
     bool tneg = (vneg != (mneg != 0));
     if (F != 1) {
       // t <- x0 * t (mod By)
       if (x0_is_big) {
         u32 xr[N];
-        if (!fw_mod<N, N>(xr, x0big, By)) return false;
+        if (!fw_mod<N, N>(xr, x0big, By)) QF_BAIL;
         fw_mul<N, N>(prod, xr, t);
-        if (!fw_mod<2 * N, N>(t, prod, By)) return false;
+        if (!fw_mod<2 * N, N>(t, prod, By)) QF_BAIL;
         tneg = tneg != x0neg;
       }
       (void)x0m;
       // u = y0 * (c2 mod By) (mod By)
       if (y0m) {
         u32 cr[N];
-        if (!fw_mod<W, N>(cr, c2, By)) return false;
+        if (!fw_mod<W, N>(cr, c2, By)) QF_BAIL;
         u32 yc[W];
         fw_mul1<N>(yc, cr, y0m);
         u32 u[N];
-        if (!fw_mod<W, N>(u, yc, By)) return false;
+        if (!fw_mod<W, N>(u, yc, By)) QF_BAIL;
         // Bx = (tneg ? -t : t) + (y0neg ? -u : u)  (mod By)
         // fold signs: bring both to [0, By)
         if (tneg && !fw_is_zero<N>(t)) fw_sub<N>(t, By, t);
@@ -398,23 +406,23 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     u32 bneg = b1[W - 1] >> 31;
     u32 bm[W];
     fw_cneg<W>(bm, b1, bneg);
-    if (bm[N] != 0) return false;
+    if (bm[N] != 0) QF_BAIL;
     bool yneg = false;
     u32 ym[N];
     fw_zero<N>(ym);
     if (fw_is_zero<N>(bm)) {
       // b == 0: G = a; By = 1; Bx = 0
-      return false;  // rare (ambiguous forms): robust path
+      QF_BAIL;  // rare (ambiguous forms): robust path
     }
     {
       u32 R0[N], R1[N], C0[N], C1[N];
       fw_copy<N>(R0, a1); fw_copy<N>(R1, bm);
       // |b| <= a for reduced input; an unreduced input may have |b| > a: robust path
-      if (fw_lt<N>(R0, R1)) return false;
+      if (fw_lt<N>(R0, R1)) QF_BAIL;
       fw_zero<N>(C0); fw_zero<N>(C1); C1[0] = 1;
       int st = fw_hxgcd<N, N>(R0, R1, C0, C1, 0, bail);
-      if (bail) return false;
-      if (!fw_high_zero<N, 1>(R0)) return false;
+      if (bail) QF_BAIL;
+      if (!fw_high_zero<N, 1>(R0)) QF_BAIL;
       G = R0[0];
       fw_copy<N>(ym, C0);
       yneg = ((st & 1) == 0) != (bneg != 0);  // y*|b| == G  ->  y*b == G needs the sign of b
@@ -422,10 +430,10 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     if (G == 1) fw_copy<N>(By, a1); else fw_divexact1<N>(By, a1, G);
     // Bx = y * c mod By
     u32 cr[N];
-    if (!fw_mod<W, N>(cr, c2, By)) return false;
+    if (!fw_mod<W, N>(cr, c2, By)) QF_BAIL;
     u32 prod[2 * N], t[N];
     fw_mul<N, N>(prod, ym, cr);
-    if (!fw_mod<2 * N, N>(t, prod, By)) return false;
+    if (!fw_mod<2 * N, N>(t, prod, By)) QF_BAIL;
     if (yneg && !fw_is_zero<N>(t)) fw_sub<N>(t, By, t);
     fw_copy<N>(Bx, t);
   }
@@ -437,18 +445,18 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
   u32 C0[M], C1[M];
   fw_zero<M>(C0); fw_zero<M>(C1); C1[0] = 1;
   int st = fw_hxgcd<N, M>(By, Bx, C0, C1, stop, bail);  // (By, Bx) <- (R_{i-1}, R_i)
-  if (bail) return false;
+  if (bail) QF_BAIL;
   int idx = 1 + st;
   // rows: x' = (Ax, Bxp) with Ax = G*C0 >= 0, Bxp = (-1)^idx R_{i-1};  y' = (Ay, Byp) with Ay = (-1)^(idx+1) G*C1, Byp = R_i
-  if (!fw_high_zero<N, M>(By) || !fw_high_zero<N, M>(Bx)) return false;
-  if ((By[M - 1] | Bx[M - 1]) >> 30) return false;
+  if (!fw_high_zero<N, M>(By) || !fw_high_zero<N, M>(Bx)) QF_BAIL;
+  if ((By[M - 1] | Bx[M - 1]) >> 30) QF_BAIL;
   u32 Ax[M], Ay[M], Rx[M], Ry[M];
   fw_copy<M>(Rx, By);
   fw_copy<M>(Ry, Bx);
   {
     u32 t[M + 1];
-    fw_mul1<M>(t, C0, G); if (t[M] | (t[M - 1] >> 30)) return false; fw_copy<M>(Ax, t);
-    fw_mul1<M>(t, C1, G); if (t[M] | (t[M - 1] >> 30)) return false; fw_copy<M>(Ay, t);
+    fw_mul1<M>(t, C0, G); if (t[M] | (t[M - 1] >> 30)) QF_BAIL; fw_copy<M>(Ax, t);
+    fw_mul1<M>(t, C1, G); if (t[M] | (t[M - 1] >> 30)) QF_BAIL; fw_copy<M>(Ay, t);
   }
   bool ay_neg = (idx & 1) == 0, rx_neg = (idx & 1) != 0;
   // size guards for the quotients (they must fit M limbs signed):
@@ -462,16 +470,19 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     int mx = t1 > t2 ? t1 : t2;
     mx = mx > t3 ? mx : t3;
     mx = mx > t4 ? mx : t4;
-    if (mx + 2 - (ba1 - 1) > lim) return false;
+    if (mx + 2 - (ba1 - 1) > lim) QF_BAIL;
   }
   // 2-adic exact division by a1 = 2^tz * a1o
   int tz = fw_ctz<N>(a1);
-  if (tz > 31) return false;
+  if (tz > 32 * (L - M) - 1) QF_BAIL;
+  int tzl = tz >> 5, tzb = tz & 31;
   u32 a1o[M];
   {
-    u32 t[N];
-    fw_shr_bits<N>(t, a1, tz);
-    fw_copy<M>(a1o, t);
+    u32 t[N], t2[N];
+    fw_copy<N>(t, a1);
+    fw_shr_limbs<N>(t, tzl);
+    fw_shr_bits<N>(t2, t, tzb);
+    fw_copy<M>(a1o, t2);
   }
   u32 a1inv = inv32(a1o[0]);
   // quotient Q = (p*B - q*A)/a1 for (p, q) = (a2, m) -> C and (s, c2) -> D; B, A given as magnitude + sign
@@ -495,7 +506,8 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
       fw_cneg<L>(n2, n2, ANEG);                                                \
       fw_sub<L>(n1, n1, n2);                                                   \
       u32 sh_[L];                                                              \
-      fw_shr_bits<L>(sh_, n1, tz);                                             \
+      fw_shr_limbs<L>(n1, tzl);                                                \
+      fw_shr_bits<L>(sh_, n1, tzb);                                            \
       u32 nm[M];                                                               \
       fw_copy<M>(nm, sh_);                                                     \
       fw_divexact_2adic<M>(QOUT, nm, a1o, a1inv);                              \
@@ -537,24 +549,24 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
   }
   // must fit the working shape: 0 < a3 < 2^(32N-1), 0 < c3 < 2^(32W-1), |b3| < 2^(32W-1)
   static_assert(P >= W, "2M >= N+1");
-  if ((a3[P - 1] >> 31) || (c3[P - 1] >> 31)) return false;
-  if (!fw_high_zero<P, N>(a3) || (a3[N - 1] >> 31) || fw_is_zero<P>(a3)) return false;
-  if (!fw_high_zero<P, W>(c3) || (c3[W - 1] >> 31)) return false;
+  if ((a3[P - 1] >> 31) || (c3[P - 1] >> 31)) QF_BAIL;
+  if (!fw_high_zero<P, N>(a3) || (a3[N - 1] >> 31) || fw_is_zero<P>(a3)) QF_BAIL;
+  if (!fw_high_zero<P, W>(c3) || (c3[W - 1] >> 31)) QF_BAIL;
   {
     u32 fill = (b3[P - 1] >> 31) ? 0xffffffffu : 0u;
     u32 o = 0;
     QF_UNROLL for (int i = W; i < P; i++) o |= b3[i] ^ fill;
-    if (o || ((b3[W - 1] >> 31) != (fill & 1))) return false;
+    if (o || ((b3[W - 1] >> 31) != (fill & 1))) QF_BAIL;
   }
   u32 ra[N], rb[W], rc[W];
   fw_copy<N>(ra, a3);
   fw_copy<W>(rb, b3);
   fw_copy<W>(rc, c3);
-  if (!fw_reduce<N>(ra, rb, rc, dbits)) return false;
+  if (!fw_reduce<N>(ra, rb, rc, dbits)) QF_BAIL;
   // b must fit N limbs signed
   {
     u32 fill = (rb[W - 1] >> 31) ? 0xffffffffu : 0u;
-    if (rb[N] != fill || ((rb[N - 1] >> 31) != (fill & 1))) return false;
+    if (rb[N] != fill || ((rb[N - 1] >> 31) != (fill & 1))) QF_BAIL;
   }
   fw_copy<N>(r.a, ra);
   fw_copy<N>(r.b, rb);

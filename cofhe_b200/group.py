@@ -119,6 +119,23 @@ class ClassGroupB200:
         capi.check(self.lib.cofhe_b200_add_ciphertexts(self.h, n, _ptr(ct1), _ptr(ct2), _ptr(out), _stream()), "add")
         return out
 
+    def scal_matmul(self, ct, scalars, n, m, p, init, ebits=None):
+        """out[i,k] = init o prod_j ct[i,j]^{s[j,k]}: ct device tensor [2, fl, n*m]; scalars: m*p non-negative ints
+        (row-major) or a device tensor [el, m*p]; init: device tensor [2, fl, 1] (the `zero` ciphertext)."""
+        if torch.is_tensor(scalars):
+            sc, el = scalars, scalars.shape[0]
+            eb = 0 if ebits is None else ebits
+        else:
+            if any(x < 0 for x in scalars):
+                raise ValueError("matmul scalars must be non-negative")
+            eb = max([int(x).bit_length() for x in scalars] + [1]) if ebits is None else ebits
+            el = max(1, (max([int(x).bit_length() for x in scalars] + [1]) + 31) // 32)
+            sc = to_device(L.ints_to_limbs(scalars, el), self.device)
+        out = torch.empty((2, self.fl, n * p), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_scal_matmul(self.h, n, m, p, _ptr(ct), _ptr(sc), el, eb, _ptr(init), _ptr(out),
+                                                   _stream()), "scal_matmul")
+        return out
+
     def add_ciphertexts_host(self, ct1, ct2, out):
         """numpy uint32 host buffers [2, fl, n]; transfers happen inside the call."""
         n = ct1.shape[-1]

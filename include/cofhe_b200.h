@@ -81,6 +81,17 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out);
 
+/* Scalar x ciphertext matmul: out[i,k] = init o prod_j ct[i,j]^{s[j,k]}  (i < n, j < m, k < p; row-major).
+ * ct: ciphertext batch of n*m elements, scal: non-negative scalars [el][m*p] (limb-major), init: ONE ciphertext
+ * (the reference's `zero` = encrypt(pk, 0)), out: ciphertext batch of n*p elements.  ebits: an upper bound on the
+ * bit length of the scalars (0 = 32*el); it only sizes the work, not the result.
+ * CPUCryptoSystem::scal_ciphertext_tensors, matmul branch (reference
+ * include/x86_64/cpu_cryptosystem_tensor_ops.inl:346-461; qfi_nupow include/x86_64/qfi.inl:1-135).  Results are those
+ * of ClassGroup::nupow / nucomp, i.e. the mathematically exact ones; the reference's qfi_nupow is wrong for some
+ * scalars >= 2^65 and that defect is not reproduced. */
+int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct, const uint32_t *scal,
+                           uint32_t el, uint32_t ebits, const uint32_t *init, uint32_t *out, void *stream);
+
 /* Measurement helper (no reference counterpart): sustained rate of independent 32x32->64-bit multiply-accumulates
  * (wide != 0: IMAD.WIDE.U32) or 32-bit multiply-adds (wide == 0: IMAD) over all SMs of `device`, in MACs/s.
  * bench.py uses it as the integer-multiply roofline denominator. */

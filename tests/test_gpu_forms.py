@@ -137,3 +137,52 @@ def test_group_law_at_scale(groups):
     assert torch.equal(G.nucomp(g, f), fg)
     assert torch.equal(G.nudupl(f), G.nucomp(f, f))
     G.status()
+
+
+def test_scal_matmul_fixtures(groups, tier):
+    """Matmul branch of scal_ciphertext_tensors against fixtures generated by the compiled reference."""
+    G = groups(int(tier["params"]["Delta"]))
+    for c in tier["scal_matmul"]:
+        n, m, p = c["n"], c["m"], c["p"]
+        ct, init = G.cts(I(c["ct"])), G.cts([I(c["zero"])])
+        got = G.cts_out(G.scal_matmul(ct, [int(x) for x in c["s"]], n, m, p, init))
+        G.status()
+        assert got == list(I(c["res"])), c["label"]
+
+
+@pytest.mark.parametrize("shape,bits", [((3, 5, 4), 13), ((2, 9, 33), 17), ((1, 4, 2), 128), ((4, 1, 3), 40)])
+def test_scal_matmul_vs_oracle(groups, shape, bits):
+    """Ragged shapes, zero scalars, chunked j ranges, wide scalars: GPU multi-exponentiation == oracle matmul."""
+    import os
+    t = load_golden("ref_t0.json")
+    G = groups(int(t["params"]["Delta"]))
+    n, m, p = shape
+    rng = random.Random(n * 100 + m * 10 + p)
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    cts = [(O.power(h, rng.getrandbits(50) + 1), O.power(pk, rng.getrandbits(50) + 1)) for _ in range(n * m)]
+    s = [rng.getrandbits(bits) if rng.random() > 0.15 else 0 for _ in range(m * p)]
+    zero = I(t["scal_matmul"][0]["zero"])
+    want = O.scal_matmul(zero, cts, s, n, m, p)
+    for chunks in ("1", "3", None):
+        if chunks:
+            os.environ["COFHE_B200_MM_CHUNKS"] = chunks
+        else:
+            os.environ.pop("COFHE_B200_MM_CHUNKS", None)
+        got = G.cts_out(G.scal_matmul(G.cts(cts), s, n, m, p, G.cts([zero])))
+        G.status()
+        assert got == want, chunks
+    os.environ.pop("COFHE_B200_MM_CHUNKS", None)
+
+
+def test_scal_matmul_degenerate(groups):
+    """Identical ciphertexts in a row (the fast path declines self-compositions) and all-zero scalars."""
+    t = load_golden("ref_t0.json")
+    G = groups(int(t["params"]["Delta"]))
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    c = (O.power(h, 12345), O.power(pk, 12345))
+    zero = I(t["scal_matmul"][0]["zero"])
+    cts, s = [c] * 4, [3, 3, 3, 3, 0, 0, 0, 0]
+    want = O.scal_matmul(zero, cts, s[:4], 1, 4, 1)
+    assert G.cts_out(G.scal_matmul(G.cts(cts), s[:4], 1, 4, 1, G.cts([zero]))) == want
+    assert G.cts_out(G.scal_matmul(G.cts(cts), s[4:], 1, 4, 1, G.cts([zero]))) == [zero]
+    G.status()
