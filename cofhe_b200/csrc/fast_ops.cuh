@@ -50,6 +50,36 @@ QF_HD void fr_unpack(FormR<N> &f, const u32 *t) {
   QF_UNROLL for (int i = 0; i < N + 1; i++) f.c[i] = t[2 * N + i];
 }
 
+// ---- per-operation fallback -----------------------------------------------------------------------------------
+// What fq_compose declines (about 2e-6 of random compositions: gcd(a1,a2) >= 2^32, a 31+ bit Euclid quotient, ...)
+// is recomputed in place by the robust path through ONE out-of-line call, so a declined step costs its lane one slow
+// composition instead of sending the whole element (a 100+ step exponentiation, a matmul output) to the robust
+// kernels.  x: packed f1 in, packed result out; t: packed f2.  Returns false when the result does not fit the
+// register shape or the robust path reports an error (the element then goes to the bail list).
+template <int N, int CAP>
+QF_HDN bool slow_compose(const Group<CAP> *G, u32 *x, const u32 *t, bool neg2, bool dupl) {
+  Err e; e.code = 0;
+  Form<CAP> f1, f2;
+  z_load(e, f1.a, x, N, 1, false); z_load(e, f1.b, x + N, N, 1, true); z_load(e, f1.c, x + 2 * N, N + 1, 1, false);
+  if (!dupl) { z_load(e, f2.a, t, N, 1, false); z_load(e, f2.b, t + N, N, 1, true); z_load(e, f2.c, t + 2 * N, N + 1, 1, false); }
+  if (dupl) qf_compose(e, *G, f1, f1, f1, false, true);
+  else qf_compose(e, *G, f1, f1, f2, neg2, false);
+  z_store(e, f1.a, x, N, 1, false); z_store(e, f1.b, x + N, N, 1, true); z_store(e, f1.c, x + 2 * N, N + 1, 1, false);
+  return e.code == 0;
+}
+template <int N, int CAP, bool DUPL>
+QF_HD bool hy_compose(const Group<CAP> *G, FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool neg2, int dbits) {
+  bool ok = fq_compose<N, DUPL>(r, f1, f2, neg2, dbits);
+  if (!ok) {
+    u32 xb[3 * N + 1], tb[3 * N + 1];
+    fr_pack<N>(xb, f1);
+    fr_pack<N>(tb, f2);
+    ok = slow_compose<N, CAP>(G, xb, tb, neg2, DUPL);
+    fr_unpack<N>(r, xb);
+  }
+  return ok;
+}
+
 // w-bit digit number `win` (from the least significant end) of an exponent stored with `stride` words between limbs
 QF_HD u32 exp_digit(const u32 *e, int el, size_t stride, int win, int w) {
   int bit = win * w, li = bit >> 5, sh = bit & 31;
@@ -64,9 +94,9 @@ QF_HD u32 exp_digit(const u32 *e, int el, size_t stride, int win, int w) {
 // per use.  Fixed windows keep the op sequence of a warp uniform even when every thread has its own exponent
 // (threads whose leading digits are zero idle until their first non-zero digit).
 // tab = per-thread scratch of (2^W - 1) packed forms f^1 .. f^(2^W-1).
-// Returns false on bail or when e == 0 (the neutral form does not fit the register shape: robust path).
-template <int N, int W>
-QF_HD bool fr_pow(FormR<N> &x, const FormR<N> &f, const u32 *e, int el, size_t stride, int dbits, u32 *tab) {
+// Returns false when a step fails even on the robust path, or when e == 0 (the neutral form does not fit the register shape: robust path).
+template <int N, int CAP, int W>
+QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32 *e, int el, size_t stride, int dbits, u32 *tab) {
   constexpr int TE = 3 * N + 1, NT = (1 << W) - 1;
   int win = (32 * el + W - 1) / W - 1;
   fr_pack<N>(tab, f);
@@ -83,11 +113,11 @@ QF_HD bool fr_pow(FormR<N> &x, const FormR<N> &f, const u32 *e, int el, size_t s
     else op = 0;
     // ---- execute
     FormR<N> r;
-    if (op == 1) ok = fq_compose<N, true>(r, x, x, false, dbits);
+    if (op == 1) ok = hy_compose<N, CAP, true>(G, r, x, x, false, dbits);
     else if (op == 2) {
       FormR<N> t;
       fr_unpack<N>(t, tab + src * TE);
-      ok = fq_compose<N, false>(r, x, t, false, dbits);
+      ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
     } else if (op == 3) { fr_unpack<N>(r, tab + src * TE); started = true; }
     else r = x;
     if (!ok) break;

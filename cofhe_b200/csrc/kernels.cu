@@ -102,8 +102,8 @@ __global__ void __launch_bounds__(kBlock) k_pow(const Group<CAP> *G, Shape s, si
 
 
 // ---- register-resident fast path (fast_ops.cuh) + sparse robust redo of what it declines -------------------------
-template <int N, bool DUPL>
-__global__ void __launch_bounds__(kBlock) k_fast_compose(int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
+template <int N, int CAP, bool DUPL>
+__global__ void __launch_bounds__(kBlock) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
                                                          int neg2, u32 *bail, int *nbail) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
@@ -111,12 +111,12 @@ __global__ void __launch_bounds__(kBlock) k_fast_compose(int dbits, int nc, size
   FormR<N> f1, f2, r;
   bool ok = fr_load<N>(f1, in1 + off, nc, n, idx);
   if (!DUPL) ok = fr_load<N>(f2, in2 + off, nc, n, idx) && ok;
-  ok = ok && fq_compose<N, DUPL>(r, f1, DUPL ? f1 : f2, neg2 != 0, dbits);
+  ok = ok && hy_compose<N, CAP, DUPL>(G, r, f1, DUPL ? f1 : f2, neg2 != 0, dbits);
   if (ok) fr_store<N>(r, out + off, nc, n, idx);
   else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
 }
-template <int N>
-__global__ void __launch_bounds__(kBlock) k_fast_pow(int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
+template <int N, int CAP>
+__global__ void __launch_bounds__(kBlock) k_fast_pow(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
                                                      int per_elem, const unsigned char *expneg, int shared_neg, u32 *bail,
                                                      int *nbail) {
   constexpr int W = 4;
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(kBlock) k_fast_pow(int dbits, int nc, size_t n
   u32 tab[((1 << W) - 1) * (3 * N + 1)];
   FormR<N> f, r;
   bool ok = fr_load<N>(f, in + off, nc, n, idx);
-  ok = ok && (per_elem ? fr_pow<N, W>(r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, W>(r, f, exp, el, 1, dbits, tab));
+  ok = ok && (per_elem ? fr_pow<N, CAP, W>(G, r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, CAP, W>(G, r, f, exp, el, 1, dbits, tab));
   if (ok) {
     if (per_elem ? (expneg && expneg[idx]) : shared_neg != 0) fr_inverse<N>(r);
     fr_store<N>(r, out + off, nc, n, idx);
@@ -151,15 +151,20 @@ __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, s
   }
 }
 
-#define FAST_DISPATCH(fn, ...)                                 \
-  switch (fn) {                                                \
-    case 2: { constexpr int FN = 2; __VA_ARGS__; } break;      \
-    case 4: { constexpr int FN = 4; __VA_ARGS__; } break;      \
-    case 7: { constexpr int FN = 7; __VA_ARGS__; } break;      \
-    case 11: { constexpr int FN = 11; __VA_ARGS__; } break;    \
-    default: return COFHE_B200_EINVAL;                         \
+// (limbs of a and b, capacity class of the robust layer) pairs that exist: cap_for(nd) with nd ~ 2*na - 1
+#define FAST_DISPATCH(fn, ...)                                                        \
+  switch (fn) {                                                                       \
+    case 2: { constexpr int FN = 2, FCAP = 32; __VA_ARGS__; } break;                  \
+    case 4: { constexpr int FN = 4, FCAP = 32; __VA_ARGS__; } break;                  \
+    case 7: { constexpr int FN = 7, FCAP = 32; __VA_ARGS__; } break;                  \
+    case 11: { constexpr int FN = 11, FCAP = 48; __VA_ARGS__; } break;                \
+    default: return COFHE_B200_EINVAL;                                                \
   }
-int fast_n_for(u32 na) { return (na == 2 || na == 4 || na == 7 || na == 11) && !getenv("COFHE_B200_NO_FAST") ? (int)na : 0; }
+int fast_cap(int fn) { return fn == 11 ? 48 : 32; }
+int fast_n_for(u32 na, int cap) {
+  bool have = (na == 2 || na == 4 || na == 7 || na == 11) && fast_cap((int)na) == cap;
+  return have && !getenv("COFHE_B200_NO_FAST") ? (int)na : 0;
+}
 
 int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
   if (entries >> 32) return COFHE_B200_EINVAL;
@@ -206,9 +211,10 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   ctx->flip ^= 1;
   int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
   FAST_DISPATCH(ctx->fastn, {
-    if (op == 0) k_fast_compose<FN, false><<<grid, kBlock, 0, st>>>(dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
-    else if (op == 1) k_fast_compose<FN, true><<<grid, kBlock, 0, st>>>(dbits, nc, n, in1, in1, out, 0, ctx->d_bail, cnt);
-    else k_fast_pow<FN><<<grid, kBlock, 0, st>>>(dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_bail, cnt);
+    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
+    if (op == 0) k_fast_compose<FN, FCAP, false><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+    else if (op == 1) k_fast_compose<FN, FCAP, true><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, in1, out, 0, ctx->d_bail, cnt);
+    else k_fast_pow<FN, FCAP><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_bail, cnt);
   })
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
@@ -256,7 +262,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->nc = n;
   ctx->launches = 0;
   ctx->dbits = (u32)dbits;
-  ctx->fastn = fast_n_for(ctx->na);
+  ctx->fastn = fast_n_for(ctx->na, cap);
   ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
   ctx->d_stage = nullptr; ctx->stage_bytes = 0;
   ctx->d_work = nullptr; ctx->work_bytes = 0;
@@ -416,15 +422,16 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
     if (rc != COFHE_B200_OK) return rc;
     u32 *tab = ctx->d_work, *part = tab + tab_words;
     size_t nb = n * m;
-    k_mm_chain<FN><<<dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(dbits, nc, s, ct, tab);
+    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
+    k_mm_chain<FN, FCAP><<<dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, ct, tab);
     ctx->launches++;
-    k_mm_fill<FN><<<dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(dbits, s, tab);
+    k_mm_fill<FN, FCAP><<<dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, s, tab);
     ctx->launches++;
-    k_mm_accum<FN><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), kMMBlock, 0, st>>>(dbits, s, scal, tab, part);
+    k_mm_accum<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), kMMBlock, 0, st>>>(G, dbits, s, scal, tab, part);
     ctx->launches++;
     int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
     ctx->flip ^= 1;
-    k_mm_final<FN><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(dbits, nc, s, init, part, out, ctx->d_bail, cnt);
+    k_mm_final<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
     ctx->launches++;
     CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<32, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
                                                                    ctx->d_bail, cnt, cnt_next, ctx->d_err))

@@ -57,8 +57,8 @@ QF_HD size_t mm_tab_index(const MMShape &s, unsigned y, size_t base, int win, in
 constexpr int kMMBlock = 128;
 
 // 1. one thread per (y, base): B_w = ct^(2^(W*w)) into T[w][1]
-template <int N>
-__global__ void __launch_bounds__(kMMBlock) k_mm_chain(int dbits, int nc, MMShape s, const u32 *ct, u32 *tab) {
+template <int N, int CAP>
+__global__ void __launch_bounds__(kMMBlock) k_mm_chain(const Group<CAP> *G, int dbits, int nc, MMShape s, const u32 *ct, u32 *tab) {
   constexpr int TE = MMLayout<N>::TE;
   size_t nb = (size_t)s.n * s.m;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -74,15 +74,15 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_chain(int dbits, int nc, MMShap
     }
     if (t >= total) break;
     if (ok) {
-      ok = fq_compose<N, true>(r, x, x, false, dbits);
+      ok = hy_compose<N, CAP, true>(G, r, x, x, false, dbits);
       x = r;
     }
   }
 }
 
 // 2. one thread per (y, base, window): T[w][d] = B_w^d
-template <int N>
-__global__ void __launch_bounds__(kMMBlock) k_mm_fill(int dbits, MMShape s, u32 *tab) {
+template <int N, int CAP>
+__global__ void __launch_bounds__(kMMBlock) k_mm_fill(const Group<CAP> *G, int dbits, MMShape s, u32 *tab) {
   constexpr int TE = MMLayout<N>::TE;
   size_t total = (size_t)s.n * s.m * s.nwin;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_fill(int dbits, MMShape s, u32 
   int nt = (1 << s.W) - 1;
   for (int d = 2; d <= nt; d++) {
     if (ok) {
-      ok = d == 2 ? fq_compose<N, true>(r, x, x, false, dbits) : fq_compose<N, false>(r, x, f, false, dbits);
+      ok = d == 2 ? hy_compose<N, CAP, true>(G, r, x, x, false, dbits) : hy_compose<N, CAP, false>(G, r, x, f, false, dbits);
       x = r;
     }
     if (ok) mm_store<N>(e + (size_t)(d - 1) * TE, x); else mm_mark<N>(e + (size_t)(d - 1) * TE, 1);
@@ -106,8 +106,8 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_fill(int dbits, MMShape s, u32 
 }
 
 // 3. one thread per (chunk, y, i, k): product over the chunk's j range and all windows; compositions only
-template <int N>
-__global__ void __launch_bounds__(kMMBlock) k_mm_accum(int dbits, MMShape s, const u32 *scal, const u32 *tab, u32 *part) {
+template <int N, int CAP>
+__global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int dbits, MMShape s, const u32 *scal, const u32 *tab, u32 *part) {
   constexpr int TE = MMLayout<N>::TE;
   size_t no = (size_t)s.n * s.p;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(int dbits, MMShape s, con
       if (mm_kind<N>(te) != 0) { ok = false; break; }
       fr_unpack<N>(t, te);
       if (started) {
-        ok = fq_compose<N, false>(r, x, t, false, dbits);
+        ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
         if (!ok) break;
         x = r;
       } else { x = t; started = true; }
@@ -140,8 +140,8 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(int dbits, MMShape s, con
 }
 
 // 4. one thread per (y, i, k): out = init o prod_chunks part
-template <int N>
-__global__ void __launch_bounds__(kMMBlock) k_mm_final(int dbits, int nc, MMShape s, const u32 *init, const u32 *part, u32 *out,
+template <int N, int CAP>
+__global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int dbits, int nc, MMShape s, const u32 *init, const u32 *part, u32 *out,
                                                        u32 *bail, int *nbail) {
   constexpr int TE = MMLayout<N>::TE;
   size_t no = (size_t)s.n * s.p;
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_final(int dbits, int nc, MMShap
     if (kind == 1) continue;
     if (kind == 2) { ok = false; break; }
     fr_unpack<N>(t, pe);
-    ok = fq_compose<N, false>(r, x, t, false, dbits);
+    ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
     x = r;
   }
   if (ok) fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);

@@ -19,6 +19,7 @@ class FastSim:
         self.dbits = (-D).bit_length()
         self.na, self.nc, self.nd = L.limb_shape(self.dbits)
         self.lib = HS.load()
+        self.absd = L.ints_to_limbs([-D], self.nd)[:, 0].copy()
 
     def ok(self):
         return self.na in FAST_N
@@ -161,7 +162,7 @@ def test_fast_pow_kat_and_fixtures():
         ex = L.ints_to_limbs([v[1] for v in vs], el)
         out = np.zeros_like(inp)
         bail = np.zeros(n, dtype=np.uint8)
-        S.lib.hs_fast_pow(S.na, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(ex), el, 1, HS.P(bail))
+        S.lib.hs_fast_pow(S.na, HS.P(S.absd), S.nd, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(ex), el, 1, HS.P(bail))
         got = L.limbs_to_forms(out, S.na, S.nc)
         for i, (f, e, r) in enumerate(vs):
             if e == 0:
@@ -173,7 +174,7 @@ def test_fast_pow_kat_and_fixtures():
         # shared exponent
         e = vs[0][1] or 5
         exs = L.ints_to_limbs([e], max(1, (e.bit_length() + 31) // 32))[:, 0].copy()
-        S.lib.hs_fast_pow(S.na, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(exs), len(exs), 0, HS.P(bail))
+        S.lib.hs_fast_pow(S.na, HS.P(S.absd), S.nd, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(exs), len(exs), 0, HS.P(bail))
         got = L.limbs_to_forms(out, S.na, S.nc)
         for i in range(min(n, 6)):
             if not bail[i]:
