@@ -33,6 +33,15 @@ SIGNATURES = {
     "cofhe_b200_add_ciphertexts": (i32, [vp, sz, vp, vp, vp, vp]),
     "cofhe_b200_add_ciphertexts_host": (i32, [vp, sz, vp, vp, vp]),
     "cofhe_b200_scal_matmul": (i32, [vp, sz, sz, sz, vp, vp, u32, u32, vp, vp, vp]),
+    "cofhe_b200_set_scheme": (i32, [vp, u32, vp, u32]),
+    "cofhe_b200_set_bases": (i32, [vp, vp, vp, u32]),
+    "cofhe_b200_fixed_base_pow": (i32, [vp, sz, vp, u32, vp, vp]),
+    "cofhe_b200_power_of_f": (i32, [vp, sz, vp, u32, vp, vp]),
+    "cofhe_b200_dlog": (i32, [vp, sz, vp, vp, u32, vp]),
+    "cofhe_b200_encrypt": (i32, [vp, sz, vp, u32, vp, u32, i32, vp, vp]),
+    "cofhe_b200_part_decrypt": (i32, [vp, sz, vp, vp, u32, i32, vp, vp]),
+    "cofhe_b200_combine": (i32, [vp, sz, u32, vp, vp, vp, u32, vp]),
+    "cofhe_b200_decrypt": (i32, [vp, sz, vp, vp, u32, vp, u32, vp]),
     "cofhe_b200_imad_probe": (i32, [i32, i32, ctypes.POINTER(ctypes.c_double)]),
 }
 

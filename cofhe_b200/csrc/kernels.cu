@@ -11,6 +11,7 @@
 #include "cofhe_b200.h"
 #include "fast_ops.cuh"
 #include "matmul.cuh"
+#include "scheme_ops.cuh"
 
 using namespace cofhe;
 
@@ -18,6 +19,7 @@ struct cofhe_b200_ctx {
   int device;
   int cap;            // capacity class of the generic integer layer
   u32 na, nc, nd, dbits;
+  u32 h_absd[2 * 216];  // |Delta| (host copy)
   void *d_group;      // Group<CAP> in device memory
   int *d_err;         // sticky per-context element status (max of Err codes)
   cudaStream_t xfer;  // internal stream of the _host entry points
@@ -33,6 +35,16 @@ struct cofhe_b200_ctx {
   // scratch of the composite operations (matmul tables and partial products, fixed-base digits, ...)
   u32 *d_work;
   size_t work_bytes;
+  u32 *d_tmp;         // form / ciphertext temporaries of encrypt, combine, decrypt
+  size_t tmp_bytes;
+  // CL_HSM2k scheme (set_scheme) and fixed bases h, pk (set_bases)
+  void *d_scheme;     // Scheme<CAP> in device memory
+  int k, kl;
+  u32 *d_exp;         // one shared exponent (share / secret key) staged from host memory: 64 limbs
+  u32 *d_fb_bases;    // (h, pk) as one ciphertext-shaped element [2][fl][1]
+  u32 *d_fb_tab;      // window tables of h and pk (fast tiers)
+  MMShape fb;
+  int fb_set;
 };
 
 namespace {
@@ -176,10 +188,54 @@ int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
   return COFHE_B200_OK;
 }
 
+// ---- scheme-level kernels (scheme_ops.cuh) ----------------------------------------------------------------------
+template <int KL, int CAP>
+__global__ void __launch_bounds__(kBlock) k_power_of_f(const Group<CAP> *G, const Scheme<CAP> *S, Shape s, size_t n, const u32 *m,
+                                                       int ml, u32 *out, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  int c = op_power_of_f<KL, CAP>(*G, *S, s, n, idx, m, ml, out);
+  if (c) atomicMax(err, c);
+}
+template <int KL, int CAP>
+__global__ void __launch_bounds__(kBlock) k_dlog(const Group<CAP> *G, const Scheme<CAP> *S, Shape s, size_t n, const u32 *in,
+                                                 u32 *out, int ml, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  int c = op_dlog<KL, CAP>(*G, *S, s, n, idx, in, out, ml);
+  if (c) atomicMax(err, c);
+}
+// out[row][idx] = in[row][0] for `rows` limb rows
+__global__ void k_bcast(size_t n, int rows, const u32 *in, u32 *out) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  for (int r = 0; r < rows; r++) out[(size_t)r * n + idx] = in[r];
+}
+
+#define SCHEME_DISPATCH(ctx, ...)                                                                   \
+  CAP_DISPATCH((ctx)->cap, switch ((ctx)->kl) {                                                       \
+    case 1: { constexpr int KL = 1; __VA_ARGS__; } break;                                            \
+    case 4: { constexpr int KL = 4; __VA_ARGS__; } break;                                            \
+    case 8: { constexpr int KL = 8; __VA_ARGS__; } break;                                            \
+    default: return COFHE_B200_ESTATE;                                                              \
+  })
+
+int ensure_tmp(cofhe_b200_ctx *ctx, size_t bytes) {
+  if (bytes <= ctx->tmp_bytes) return COFHE_B200_OK;
+  if (ctx->d_tmp) cudaFree(ctx->d_tmp);
+  ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
+  if (cudaMalloc(&ctx->d_tmp, bytes) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+  ctx->tmp_bytes = bytes;
+  return COFHE_B200_OK;
+}
+
 int ensure_work(cofhe_b200_ctx *ctx, size_t bytes) {
   if (bytes <= ctx->work_bytes) return COFHE_B200_OK;
   if (ctx->d_work) cudaFree(ctx->d_work);  // synchronises with kernels still using the old scratch
   ctx->d_work = nullptr; ctx->work_bytes = 0;
+  ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
+  ctx->d_scheme = nullptr; ctx->k = 0; ctx->kl = 0; ctx->d_exp = nullptr;
+  ctx->d_fb_bases = nullptr; ctx->d_fb_tab = nullptr; ctx->fb_set = 0;
   if (cudaMalloc(&ctx->d_work, bytes) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
   ctx->work_bytes = bytes;
   return COFHE_B200_OK;
@@ -224,6 +280,66 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   return check_launch(ctx);
 }
 
+// ---- matmul / fixed-base machinery (matmul.cuh) ---------------------------------------------------------------
+size_t mm_tab_words(const cofhe_b200_ctx *ctx, const MMShape &s) {
+  int te = ((3 * ctx->fastn + 1) + 3) & ~3;
+  return (size_t)2 * s.n * s.m * s.nwin * ((1u << s.W) - 1) * te;
+}
+size_t mm_part_words(const cofhe_b200_ctx *ctx, const MMShape &s) {
+  int te = ((3 * ctx->fastn + 1) + 3) & ~3;
+  return (size_t)s.chunks * 2 * s.n * s.p * te;
+}
+// window tables of the n*m base ciphertexts `ct` into tab (fast tiers only)
+int mm_tables(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, u32 *tab, cudaStream_t st) {
+  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  size_t nb = (size_t)s.n * s.m;
+  FAST_DISPATCH(ctx->fastn, {
+    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
+    k_mm_chain<FN, FCAP><<<dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, ct, tab);
+    ctx->launches++;
+    k_mm_fill<FN, FCAP><<<dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, s, tab);
+  })
+  return check_launch(ctx);
+}
+// out[i,k] = init o prod_j prod_w tab_{ij}[w][digit_w(scal[j,k])]; declined outputs are redone from ct on the robust path
+int mm_eval(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *scal, const u32 *init, u32 *out, const u32 *tab,
+            u32 *part, cudaStream_t st) {
+  Shape sh{(int)ctx->na, (int)ctx->nc};
+  size_t no = (size_t)s.n * s.p;
+  int rc = ensure_bail(ctx, 2 * no);
+  if (rc != COFHE_B200_OK) return rc;
+  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
+  ctx->flip ^= 1;
+  FAST_DISPATCH(ctx->fastn, {
+    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
+    k_mm_accum<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), kMMBlock, 0, st>>>(G, dbits, s, scal, tab, part);
+    ctx->launches++;
+    k_mm_final<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
+    ctx->launches++;
+    k_mm_robust<FCAP><<<32, kMMBlock, 0, st>>>(G, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err);
+  })
+  return check_launch(ctx);
+}
+int mm_robust_all(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *scal, const u32 *init, u32 *out, cudaStream_t st) {
+  Shape sh{(int)ctx->na, (int)ctx->nc};
+  size_t no = (size_t)s.n * s.p;
+  unsigned blocks = (unsigned)((2 * no + kMMBlock - 1) / kMMBlock);
+  CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
+                                                                     nullptr, nullptr, nullptr, ctx->d_err))
+  return check_launch(ctx);
+}
+
+// (h^e, pk^e) for n exponents into a ciphertext-shaped batch `out`; part: scratch of mm_part_words(fb with p = n)
+int fb_pow(cofhe_b200_ctx *ctx, size_t n, const u32 *exps, u32 el, u32 *out, u32 *part, cudaStream_t st) {
+  MMShape s = ctx->fb;
+  if ((int)el > s.el) return COFHE_B200_EINVAL;  // exponent wider than the tables were built for
+  s.p = (unsigned)n;
+  s.el = (int)el;
+  if (!ctx->fastn) return mm_robust_all(ctx, s, ctx->d_fb_bases, exps, nullptr, out, st);
+  return mm_eval(ctx, s, ctx->d_fb_bases, exps, nullptr, out, ctx->d_fb_tab, part, st);
+}
+
 struct DevGuard {
   int prev;
   bool ok;
@@ -262,10 +378,14 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->nc = n;
   ctx->launches = 0;
   ctx->dbits = (u32)dbits;
+  for (u32 i = 0; i < n; i++) ctx->h_absd[i] = abs_delta[i];
   ctx->fastn = fast_n_for(ctx->na, cap);
   ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
   ctx->d_stage = nullptr; ctx->stage_bytes = 0;
   ctx->d_work = nullptr; ctx->work_bytes = 0;
+  ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
+  ctx->d_scheme = nullptr; ctx->k = 0; ctx->kl = 0; ctx->d_exp = nullptr;
+  ctx->d_fb_bases = nullptr; ctx->d_fb_tab = nullptr; ctx->fb_set = 0;
   ctx->d_group = nullptr;
   ctx->d_err = nullptr;
   ctx->xfer = nullptr;
@@ -285,6 +405,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   if (rc == COFHE_B200_OK && (cudaMalloc(&ctx->d_err, sizeof(int)) != cudaSuccess ||
                               cudaMemset(ctx->d_err, 0, sizeof(int)) != cudaSuccess ||
                               cudaMalloc(&ctx->d_nbail, 2 * sizeof(int)) != cudaSuccess ||
+                              cudaMalloc(&ctx->d_exp, 64 * sizeof(u32)) != cudaSuccess ||
                               cudaMemset(ctx->d_nbail, 0, 2 * sizeof(int)) != cudaSuccess ||
                               cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking) != cudaSuccess))
     rc = COFHE_B200_ECUDA;
@@ -302,6 +423,11 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_nbail) cudaFree(ctx->d_nbail);
   if (ctx->d_stage) cudaFree(ctx->d_stage);
   if (ctx->d_work) cudaFree(ctx->d_work);
+  if (ctx->d_tmp) cudaFree(ctx->d_tmp);
+  if (ctx->d_scheme) cudaFree(ctx->d_scheme);
+  if (ctx->d_exp) cudaFree(ctx->d_exp);
+  if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
+  if (ctx->d_fb_tab) cudaFree(ctx->d_fb_tab);
   if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
   delete ctx;
 }
@@ -387,22 +513,15 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
-  Shape sh{(int)ctx->na, (int)ctx->nc};
   MMShape s;
   s.n = (unsigned)n; s.m = (unsigned)m; s.p = (unsigned)p; s.el = (int)el;
   s.W = 4;
   if (const char *w = getenv("COFHE_B200_MM_W")) { int v = atoi(w); if (v >= 2 && v <= 8) s.W = v; }
   if (ebits == 0 || ebits > 32 * el) ebits = 32 * el;
   s.nwin = (int)((ebits + s.W - 1) / s.W);
+  s.chunks = 1; s.jper = (unsigned)m;
   size_t no = n * p;
-  if (!ctx->fastn || m == 0) {
-    // robust path over every output (tiers without a register-resident instantiation)
-    s.chunks = 1; s.jper = (unsigned)m;
-    unsigned blocks = (unsigned)((2 * no + kMMBlock - 1) / kMMBlock);
-    CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
-                                                                       nullptr, nullptr, nullptr, ctx->d_err))
-    return check_launch(ctx);
-  }
+  if (!ctx->fastn || m == 0) return mm_robust_all(ctx, s, ct, scal, init, out, st);
   // split the j range so that small n*p still fills the machine
   size_t want = (size_t)148 * 4 * kMMBlock;
   size_t ch = (want + 2 * no - 1) / (2 * no);
@@ -411,32 +530,207 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   if (const char *c = getenv("COFHE_B200_MM_CHUNKS")) { int v = atoi(c); if (v >= 1 && (size_t)v <= m) ch = (size_t)v; }
   s.jper = (unsigned)((m + ch - 1) / ch);
   s.chunks = (unsigned)((m + s.jper - 1) / s.jper);
-  int rc = ensure_bail(ctx, 2 * no);
+  size_t tw = mm_tab_words(ctx, s), pw = mm_part_words(ctx, s);
+  int rc = ensure_work(ctx, (tw + pw) * sizeof(u32));
   if (rc != COFHE_B200_OK) return rc;
-  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
-  FAST_DISPATCH(ctx->fastn, {
-    constexpr int TE = MMLayout<FN>::TE;
-    size_t tab_words = (size_t)2 * n * m * s.nwin * ((1u << s.W) - 1) * TE;
-    size_t part_words = (size_t)s.chunks * 2 * no * TE;
-    rc = ensure_work(ctx, (tab_words + part_words) * sizeof(u32));
-    if (rc != COFHE_B200_OK) return rc;
-    u32 *tab = ctx->d_work, *part = tab + tab_words;
-    size_t nb = n * m;
-    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
-    k_mm_chain<FN, FCAP><<<dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, ct, tab);
-    ctx->launches++;
-    k_mm_fill<FN, FCAP><<<dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, s, tab);
-    ctx->launches++;
-    k_mm_accum<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), kMMBlock, 0, st>>>(G, dbits, s, scal, tab, part);
-    ctx->launches++;
-    int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
-    ctx->flip ^= 1;
-    k_mm_final<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
-    ctx->launches++;
-    CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<32, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
-                                                                   ctx->d_bail, cnt, cnt_next, ctx->d_err))
+  u32 *tab = ctx->d_work, *part = tab + tw;
+  rc = mm_tables(ctx, s, ct, tab, st);
+  if (rc != COFHE_B200_OK) return rc;
+  return mm_eval(ctx, s, ct, scal, init, out, tab, part, st);
+}
+
+// ---- CL_HSM2k scheme level ---------------------------------------------------------------------------------------
+int cofhe_b200_set_scheme(cofhe_b200_ctx *ctx, uint32_t k, const uint32_t *N, uint32_t nN) {
+  if (!ctx || !N || nN == 0 || k == 0 || k > 256) return COFHE_B200_EINVAL;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  int n = bn_norm(N, (int)nN);
+  if (n == 0) return COFHE_B200_EINVAL;
+  // |Delta| must be 2^(2k+5) * N  (CL_HSM2k.inl:620-637: DeltaK = -8N, Delta = DeltaK * 2^(2(k+1)))
+  {
+    int nb = bn_bits(N, n);
+    if ((u32)nb + 2 * k + 5 != ctx->dbits) return COFHE_B200_EINVAL;
+    unsigned sh = 2 * k + 5;
+    for (u32 i = 0; i < ctx->nd; i++) {
+      // limb i of N << sh
+      long lo = (long)i - (long)(sh >> 5);
+      u32 v = 0;
+      if (lo >= 0 && lo < n) v = N[lo] << (sh & 31);
+      if ((sh & 31) && lo - 1 >= 0 && lo - 1 < n) v |= N[lo - 1] >> (32 - (sh & 31));
+      if (v != ctx->h_absd[i]) return COFHE_B200_EINVAL;
+    }
+  }
+  ctx->k = (int)k;
+  ctx->kl = k <= 32 ? 1 : (k <= 128 ? 4 : 8);
+  int rc = COFHE_B200_OK;
+  CAP_DISPATCH(ctx->cap, {
+    Scheme<CAP> *S = new (std::nothrow) Scheme<CAP>();
+    if (!S) return COFHE_B200_ENOMEM;
+    memset(S, 0, sizeof(*S));
+    Err e; e.code = 0;
+    S->k = (int)k;
+    S->N.n = n; S->N.neg = 0;
+    for (int i = 0; i < n; i++) S->N.d[i] = N[i];
+    z_shl(e, S->absDK, S->N, 3);
+    Z<CAP> t, one;
+    z_set_u32(one, 1);
+    z_add(e, t, S->absDK, one);
+    S->large = z_bits(t) <= (int)(2 * k) ? 1 : 0;
+    if (e.code) rc = COFHE_B200_EINVAL;
+    if (rc == COFHE_B200_OK && !ctx->d_scheme && cudaMalloc(&ctx->d_scheme, sizeof(*S)) != cudaSuccess) rc = COFHE_B200_ENOMEM;
+    if (rc == COFHE_B200_OK && cudaMemcpy(ctx->d_scheme, S, sizeof(*S), cudaMemcpyHostToDevice) != cudaSuccess) rc = COFHE_B200_ECUDA;
+    delete S;
   })
+  return rc;
+}
+
+int cofhe_b200_power_of_f(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_t ml, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!m || !out)) || ml == 0) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  SCHEME_DISPATCH(ctx, k_power_of_f<KL, CAP><<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(
+                           (const Group<CAP> *)ctx->d_group, (const Scheme<CAP> *)ctx->d_scheme, s, n, m, (int)ml, out, ctx->d_err))
   return check_launch(ctx);
+}
+
+int cofhe_b200_dlog(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *m, uint32_t ml, void *stream) {
+  if (!ctx || (n && (!m || !f)) || ml == 0) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  SCHEME_DISPATCH(ctx, k_dlog<KL, CAP><<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(
+                           (const Group<CAP> *)ctx->d_group, (const Scheme<CAP> *)ctx->d_scheme, s, n, f, m, (int)ml, ctx->d_err))
+  return check_launch(ctx);
+}
+
+int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t *pk, uint32_t ebits) {
+  if (!ctx || !h || ebits == 0) return COFHE_B200_EINVAL;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  size_t fl = 2 * ctx->na + ctx->nc;
+  if (!ctx->d_fb_bases && cudaMalloc(&ctx->d_fb_bases, 2 * fl * sizeof(u32)) != cudaSuccess) return COFHE_B200_ENOMEM;
+  CUDA_TRY(cudaStreamSynchronize(ctx->xfer));
+  CUDA_TRY(cudaMemcpy(ctx->d_fb_bases, h, fl * sizeof(u32), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(ctx->d_fb_bases + fl, pk ? pk : h, fl * sizeof(u32), cudaMemcpyHostToDevice));
+  MMShape s;
+  s.n = 1; s.m = 1; s.p = 0; s.chunks = 1; s.jper = 1;
+  s.W = 8;
+  if (const char *w = getenv("COFHE_B200_FB_W")) { int v = atoi(w); if (v >= 2 && v <= 10) s.W = v; }
+  s.el = (int)((ebits + 31) / 32);
+  s.nwin = (32 * s.el + s.W - 1) / s.W;
+  ctx->fb = s;
+  ctx->fb_set = 1;
+  if (!ctx->fastn) return COFHE_B200_OK;
+  if (ctx->d_fb_tab) { cudaFree(ctx->d_fb_tab); ctx->d_fb_tab = nullptr; }
+  if (cudaMalloc(&ctx->d_fb_tab, mm_tab_words(ctx, s) * sizeof(u32)) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+  int rc = mm_tables(ctx, s, ctx->d_fb_bases, ctx->d_fb_tab, ctx->xfer);
+  if (rc != COFHE_B200_OK) return rc;
+  return cofhe_b200_status(ctx, ctx->xfer);
+}
+
+int cofhe_b200_fixed_base_pow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *exps, uint32_t el, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!exps || !out)) || el == 0 || n >> 30) return COFHE_B200_EINVAL;
+  if (!ctx->fb_set) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  MMShape s = ctx->fb;
+  s.p = (unsigned)n;
+  int rc = ensure_tmp(ctx, (ctx->fastn ? mm_part_words(ctx, s) : 1) * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  return fb_pow(ctx, n, exps, el, out, ctx->d_tmp, (cudaStream_t)stream);
+}
+
+int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_t ml, const uint32_t *r, uint32_t el, int shared_r,
+                       uint32_t *out, void *stream) {
+  if (!ctx || (n && (!m || !out)) || !r || ml == 0 || el == 0 || n >> 30) return COFHE_B200_EINVAL;
+  if (!ctx->fb_set || !ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t fl = 2 * ctx->na + ctx->nc;
+  size_t nr = shared_r ? 1 : n;
+  MMShape s = ctx->fb;
+  s.p = (unsigned)nr;
+  size_t pw = ctx->fastn ? mm_part_words(ctx, s) : 0;
+  // tmp: partial products | f^m forms [fl][n] | the shared (h^r, pk^r) [2][fl][1]
+  int rc = ensure_tmp(ctx, (pw + fl * n + 2 * fl) * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  u32 *part = ctx->d_tmp, *fm = part + pw, *one = fm + fl * n;
+  if (shared_r) {
+    rc = fb_pow(ctx, 1, r, el, one, part, st);
+    if (rc != COFHE_B200_OK) return rc;
+    k_bcast<<<grid_for(n), kBlock, 0, st>>>(n, (int)(2 * fl), one, out);
+    rc = check_launch(ctx);
+  } else {
+    rc = fb_pow(ctx, n, r, el, out, part, st);
+  }
+  if (rc != COFHE_B200_OK) return rc;
+  rc = cofhe_b200_power_of_f(ctx, n, m, ml, fm, stream);
+  if (rc != COFHE_B200_OK) return rc;
+  return launch_op(ctx, 0, 1, n, out + fl * n, fm, out + fl * n, 0, nullptr, 0, 0, nullptr, 0, st);
+}
+
+int cofhe_b200_part_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *share, uint32_t el, int share_neg,
+                            uint32_t *out, void *stream) {
+  if (!ctx || (n && (!ct || !out)) || !share || el == 0 || el > 64) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemcpyAsync(ctx->d_exp, share, el * sizeof(u32), cudaMemcpyHostToDevice, st));
+  return launch_op(ctx, 2, 1, n, ct, ct, out, 0, ctx->d_exp, (int)el, 0, nullptr, share_neg, st);
+}
+
+int cofhe_b200_combine(cofhe_b200_ctx *ctx, size_t n, uint32_t t, const uint32_t *ct, const uint32_t *ds, uint32_t *m, uint32_t ml,
+                       void *stream) {
+  if (!ctx || (n && (!ct || !ds || !m)) || t == 0 || ml == 0) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t fl = 2 * ctx->na + ctx->nc;
+  int rc = ensure_tmp(ctx, 2 * fl * n * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  u32 *d = ctx->d_tmp, *r = d + fl * n;
+  // d = ds_0 o ds_1^-1 o ... o ds_{t-1}^-1   (compute_d, lambda = (1,-1,-1,...): cpu_cryptosystem_distributed.inl:214-242)
+  const u32 *cur = ds;
+  for (uint32_t i = 1; i < t; i++) {
+    rc = launch_op(ctx, 0, 1, n, cur, ds + (size_t)i * fl * n, d, 1, nullptr, 0, 0, nullptr, 0, st);
+    if (rc != COFHE_B200_OK) return rc;
+    cur = d;
+  }
+  // r = c2 o d^-1 ; m = dlog_F(r)   (finalDecrypt :256-270)
+  rc = launch_op(ctx, 0, 1, n, ct + fl * n, cur, r, 1, nullptr, 0, 0, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  return cofhe_b200_dlog(ctx, n, r, m, ml, stream);
+}
+
+int cofhe_b200_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *sk, uint32_t el, uint32_t *m, uint32_t ml,
+                       void *stream) {
+  if (!ctx || (n && (!ct || !m)) || !sk || el == 0 || el > 64 || ml == 0) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t fl = 2 * ctx->na + ctx->nc;
+  int rc = ensure_tmp(ctx, 2 * fl * n * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  u32 *x = ctx->d_tmp, *r = x + fl * n;
+  CUDA_TRY(cudaMemcpyAsync(ctx->d_exp, sk, el * sizeof(u32), cudaMemcpyHostToDevice, st));
+  rc = launch_op(ctx, 2, 1, n, ct, ct, x, 0, ctx->d_exp, (int)el, 0, nullptr, 0, st);   // c1^sk
+  if (rc != COFHE_B200_OK) return rc;
+  rc = launch_op(ctx, 0, 1, n, ct + fl * n, x, r, 1, nullptr, 0, 0, nullptr, 0, st);     // c2 o (c1^sk)^-1
+  if (rc != COFHE_B200_OK) return rc;
+  return cofhe_b200_dlog(ctx, n, r, m, ml, stream);
 }
 
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
@@ -450,8 +744,16 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   if (ctx->stage_bytes < 3 * bytes) {
     if (ctx->d_stage) cudaFree(ctx->d_stage);
   if (ctx->d_work) cudaFree(ctx->d_work);
+  if (ctx->d_tmp) cudaFree(ctx->d_tmp);
+  if (ctx->d_scheme) cudaFree(ctx->d_scheme);
+  if (ctx->d_exp) cudaFree(ctx->d_exp);
+  if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
+  if (ctx->d_fb_tab) cudaFree(ctx->d_fb_tab);
     ctx->d_stage = nullptr; ctx->stage_bytes = 0;
   ctx->d_work = nullptr; ctx->work_bytes = 0;
+  ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
+  ctx->d_scheme = nullptr; ctx->k = 0; ctx->kl = 0; ctx->d_exp = nullptr;
+  ctx->d_fb_bases = nullptr; ctx->d_fb_tab = nullptr; ctx->fb_set = 0;
     if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) rc = COFHE_B200_ENOMEM;
     else ctx->stage_bytes = 3 * bytes;
   }

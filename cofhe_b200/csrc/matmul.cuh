@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int 
   else mm_store<N>(o, x);
 }
 
-// 4. one thread per (y, i, k): out = init o prod_chunks part
+// 4. one thread per (y, i, k): out = init o prod_chunks part   (init == nullptr: plain product)
 template <int N, int CAP>
 __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int dbits, int nc, MMShape s, const u32 *init, const u32 *part, u32 *out,
                                                        u32 *bail, int *nbail) {
@@ -149,16 +149,20 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int 
   if (idx >= no) return;
   unsigned y = blockIdx.y;
   FormR<N> x, t, r;
-  bool ok = fr_load<N>(x, init + (size_t)y * (2 * N + nc), nc, 1, 0);
+  bool started = init != nullptr;
+  bool ok = started ? fr_load<N>(x, init + (size_t)y * (2 * N + nc), nc, 1, 0) : true;
   for (unsigned c = 0; c < s.chunks && ok; c++) {
     const u32 *pe = part + (((size_t)c * 2 + y) * no + idx) * TE;
     int kind = mm_kind<N>(pe);
     if (kind == 1) continue;
     if (kind == 2) { ok = false; break; }
     fr_unpack<N>(t, pe);
-    ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
-    x = r;
+    if (started) {
+      ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
+      x = r;
+    } else { x = t; started = true; }
   }
+  ok = ok && started;  // an empty product without init is the neutral form: robust path
   if (ok) fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);
   else bail[atomicAdd(nbail, 1)] = (u32)(y * no + idx);
 }
@@ -177,7 +181,8 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_robust(const Group<CAP> *G, Sha
     unsigned i = (unsigned)(idx / s.p), k = (unsigned)(idx % s.p);
     Err er; er.code = 0;
     Form<CAP> acc, f, t;
-    form_load(er, acc, init + y * form_limbs(sh), sh, 1, 0);
+    if (init) form_load(er, acc, init + y * form_limbs(sh), sh, 1, 0);
+    else qf_identity(er, *G, acc);
     for (unsigned j = 0; j < s.m && !er.code; j++) {
       const u32 *ex = scal + (size_t)j * s.p + k;
       bool zero = true;

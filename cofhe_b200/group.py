@@ -136,6 +136,86 @@ class ClassGroupB200:
                                                    _stream()), "scal_matmul")
         return out
 
+    # ---- CL_HSM2k scheme level (mirrors CPUCryptoSystem's batched entry points on SoA device tensors) --------------
+    def set_scheme(self, k, N):
+        nN = (int(N).bit_length() + 31) // 32
+        nl = L.ints_to_limbs([N], nN)[:, 0].copy()
+        capi.check(self.lib.cofhe_b200_set_scheme(self.h, k, nl.ctypes.data_as(ctypes.c_void_p), nN), "set_scheme")
+        self.k, self.ml = k, (k + 31) // 32
+
+    def set_bases(self, h, pk, ebits):
+        hl = L.forms_to_limbs([h], self.na, self.nc)[:, 0].copy()
+        pl = None if pk is None else L.forms_to_limbs([pk], self.na, self.nc)[:, 0].copy()
+        vp = ctypes.c_void_p
+        capi.check(self.lib.cofhe_b200_set_bases(self.h, hl.ctypes.data_as(vp), None if pl is None else pl.ctypes.data_as(vp),
+                                                 ebits), "set_bases")
+        self.el_r = (ebits + 31) // 32
+
+    def ints(self, vals, nl):
+        return to_device(L.ints_to_limbs(vals, nl), self.device)
+
+    def fixed_base_pow(self, exps):
+        """exps: list of ints or device tensor [el, n] -> ciphertext-shaped tensor (h^x, pk^x)."""
+        ex = exps if torch.is_tensor(exps) else self.ints(exps, self.el_r)
+        n = ex.shape[-1]
+        out = torch.empty((2, self.fl, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_fixed_base_pow(self.h, n, _ptr(ex), ex.shape[0], _ptr(out), _stream()), "fixed_base_pow")
+        return out
+
+    def power_of_f(self, ms):
+        m = ms if torch.is_tensor(ms) else self.ints([x % (1 << self.k) for x in ms], self.ml)
+        n = m.shape[-1]
+        out = torch.empty((self.fl, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_power_of_f(self.h, n, _ptr(m), m.shape[0], _ptr(out), _stream()), "power_of_f")
+        return out
+
+    def dlog(self, f):
+        n = f.shape[-1]
+        out = torch.empty((self.ml, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_dlog(self.h, n, _ptr(f), _ptr(out), self.ml, _stream()), "dlog")
+        return out
+
+    def encrypt(self, ms, r):
+        """r: one int (shared randomness, reference encrypt_tensor semantics) or a list / device tensor (per element)."""
+        m = ms if torch.is_tensor(ms) else self.ints([x % (1 << self.k) for x in ms], self.ml)
+        n = m.shape[-1]
+        shared = isinstance(r, int)
+        rr = r if torch.is_tensor(r) else self.ints([r] if shared else r, self.el_r)
+        out = torch.empty((2, self.fl, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_encrypt(self.h, n, _ptr(m), m.shape[0], _ptr(rr), rr.shape[0], int(shared), _ptr(out),
+                                               _stream()), "encrypt")
+        return out
+
+    def _host_exp(self, e):
+        el = max(1, (abs(int(e)).bit_length() + 31) // 32)
+        return L.ints_to_limbs([abs(int(e))], el)[:, 0].copy(), el
+
+    def part_decrypt(self, ct, share):
+        n = ct.shape[-1]
+        ex, el = self._host_exp(share)
+        out = torch.empty((self.fl, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_part_decrypt(self.h, n, _ptr(ct), ex.ctypes.data_as(ctypes.c_void_p), el, int(share < 0),
+                                                    _ptr(out), _stream()), "part_decrypt")
+        return out
+
+    def combine(self, ct, ds):
+        """ds: device tensor [t, fl, n] of partial decryptions (party order as the reference's lambda = (1,-1,-1,...))."""
+        n, t = ct.shape[-1], ds.shape[0]
+        out = torch.empty((self.ml, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_combine(self.h, n, t, _ptr(ct), _ptr(ds), _ptr(out), self.ml, _stream()), "combine")
+        return out
+
+    def decrypt(self, ct, sk):
+        n = ct.shape[-1]
+        ex, el = self._host_exp(sk)
+        out = torch.empty((self.ml, n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_decrypt(self.h, n, _ptr(ct), ex.ctypes.data_as(ctypes.c_void_p), el, _ptr(out), self.ml,
+                                               _stream()), "decrypt")
+        return out
+
+    def ints_out(self, t):
+        return L.limbs_to_ints(to_host(t))
+
     def add_ciphertexts_host(self, ct1, ct2, out):
         """numpy uint32 host buffers [2, fl, n]; transfers happen inside the call."""
         n = ct1.shape[-1]

@@ -92,6 +92,48 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
 int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct, const uint32_t *scal,
                            uint32_t el, uint32_t ebits, const uint32_t *init, uint32_t *out, void *stream);
 
+/* ---- CL_HSM2k scheme level --------------------------------------------------------------------------------------
+ * The context becomes a CL_HSM2k instance once the scheme constants are known: message space Z/2^k and the modulus N
+ * with DeltaK = -8N, Delta = -2^(2k+5) N (reference thirdparty/bicycl/src/bicycl/CL_HSM2k.inl:31-103, 620-637; setup
+ * itself -- random N, class-number bound, h -- stays on the host with the reference's RandGen).
+ * Fails with COFHE_B200_EINVAL when 2^(2k+5) N is not the context's |Delta|.  Host pointers. */
+int cofhe_b200_set_scheme(cofhe_b200_ctx *ctx, uint32_t k, const uint32_t *N, uint32_t nN);
+/* Fixed bases for encryption: the generator h and the public key pk (host pointers to one form each, context shape;
+ * pk may be NULL).  Builds their window tables on the device for exponents below 2^ebits.  Replaces the
+ * precomputation of CL_HSM2k (CL_HSM2k.inl:92-102: h^(2^e), h^(2^d), h^(2^(d+e))) and of CL_HSM_PublicKey
+ * (CL_HSM_utils.inl:43-80).  Synchronous. */
+int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t *pk, uint32_t ebits);
+/* out[e] = (h^x[e], pk^x[e]) as a ciphertext-shaped batch, x = exps[.][e] (el limb rows, x < 2^ebits).
+ * CL_HSM2k::power_of_h (CL_HSM2k.inl:318-322 -> QFI::nupow with 3 precomputed powers, qfi.inl:1162-1251) and
+ * CL_HSM_PublicKey::exponentiation (CL_HSM_utils.inl:89-95). */
+int cofhe_b200_fixed_base_pow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *exps, uint32_t el, uint32_t *out, void *stream);
+/* out[e] = the REDUCED form of f^m[e], m = m[.][e] (ml limb rows, taken modulo 2^k).  CL_HSM2k::power_of_f
+ * (CL_HSM2k.inl:326-405) returns the unreduced triple; every consumer composes it, which reduces it. */
+int cofhe_b200_power_of_f(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_t ml, uint32_t *out, void *stream);
+/* m[.][e] = dlog_F(f[e]) in [0, 2^k), ml limb rows (CL_HSM2k::dlog_in_F, CL_HSM2k.inl:408-455; both the
+ * large-message branch through QFI::kernel_representative_2exp, qfi.inl:396-435, and the small-message branch). */
+int cofhe_b200_dlog(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *m, uint32_t ml, void *stream);
+/* out[e] = (h^r, pk^r o f^m[e]).  shared_r != 0: ONE exponent r[0..el) for the whole batch, as
+ * CPUCryptoSystem::encrypt_tensor / encrypt_vector do (reference include/x86_64/cpu_cryptosystem_tensor_ops.inl:1-19,
+ * CL_HSM_utils.inl:248-255); shared_r == 0: r[.][e] per element, as N calls of CPUCryptoSystem::encrypt
+ * (cpu_cryptosystem.inl:11-14 -> CL_HSM_utils.inl:161-185).  r is drawn by the caller (host RandGen). */
+int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_t ml, const uint32_t *r, uint32_t el, int shared_r,
+                       uint32_t *out, void *stream);
+/* out[e] = c1[e]^share  (threshold partial decryption, one share for the whole batch; share: HOST pointer, el limbs).
+ * CPUCryptoSystem::part_decrypt_tensor (cpu_cryptosystem_tensor_ops.inl:35-47 -> partDecrypt,
+ * cpu_cryptosystem_distributed.inl:244-254). */
+int cofhe_b200_part_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *share, uint32_t el, int share_neg,
+                            uint32_t *out, void *stream);
+/* m[.][e] = dlog_F( c2[e] o (d_0[e] o d_1[e]^-1 o ... o d_{t-1}[e]^-1)^-1 ), ds = [t][form batch].
+ * CPUCryptoSystem::combine_part_decryption_results_tensor (cpu_cryptosystem_tensor_ops.inl:49-73 -> finalDecrypt,
+ * compute_d, compute_lambda: cpu_cryptosystem_distributed.inl:214-270). */
+int cofhe_b200_combine(cofhe_b200_ctx *ctx, size_t n, uint32_t t, const uint32_t *ct, const uint32_t *ds, uint32_t *m, uint32_t ml,
+                       void *stream);
+/* m[.][e] = dlog_F( c2[e] o (c1[e]^sk)^-1 )  (sk: HOST pointer).  CPUCryptoSystem::decrypt_tensor
+ * (cpu_cryptosystem_tensor_ops.inl:21-33 -> CL_HSM_ClearText, CL_HSM_utils.inl:124-138). */
+int cofhe_b200_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *sk, uint32_t el, uint32_t *m, uint32_t ml,
+                       void *stream);
+
 /* Measurement helper (no reference counterpart): sustained rate of independent 32x32->64-bit multiply-accumulates
  * (wide != 0: IMAD.WIDE.U32) or 32-bit multiply-adds (wide == 0: IMAD) over all SMs of `device`, in MACs/s.
  * bench.py uses it as the integer-multiply roofline denominator. */
