@@ -42,6 +42,14 @@ SIGNATURES = {
     "cofhe_b200_part_decrypt": (i32, [vp, sz, vp, vp, u32, i32, vp, vp]),
     "cofhe_b200_combine": (i32, [vp, sz, u32, vp, vp, vp, u32, vp]),
     "cofhe_b200_decrypt": (i32, [vp, sz, vp, vp, u32, vp, u32, vp]),
+    "cofhe_b200_device_count": (i32, []),
+    "cofhe_b200_dev_alloc": (i32, [vp, sz, ctypes.POINTER(vp)]),
+    "cofhe_b200_dev_free": (None, [vp, vp]),
+    "cofhe_b200_host_alloc": (i32, [sz, ctypes.POINTER(vp)]),
+    "cofhe_b200_host_free": (None, [vp]),
+    "cofhe_b200_stream": (vp, [vp]),
+    "cofhe_b200_upload": (i32, [vp, vp, vp, sz, vp]),
+    "cofhe_b200_download": (i32, [vp, vp, vp, sz, vp]),
     "cofhe_b200_imad_probe": (i32, [i32, i32, ctypes.POINTER(ctypes.c_double)]),
 }
 

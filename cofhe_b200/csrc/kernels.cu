@@ -733,6 +733,52 @@ int cofhe_b200_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const 
   return cofhe_b200_dlog(ctx, n, r, m, ml, stream);
 }
 
+// ---- device memory helpers for callers that do not link the CUDA runtime (the header class) -----------------------
+int cofhe_b200_dev_alloc(cofhe_b200_ctx *ctx, size_t bytes, void **ptr) {
+  if (!ctx || !ptr) return COFHE_B200_EINVAL;
+  *ptr = nullptr;
+  if (bytes == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  if (cudaMalloc(ptr, bytes) != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return COFHE_B200_ENOMEM; }
+  return COFHE_B200_OK;
+}
+void cofhe_b200_dev_free(cofhe_b200_ctx *ctx, void *ptr) {
+  if (!ctx || !ptr) return;
+  DevGuard g(ctx->device);
+  cudaFree(ptr);
+}
+int cofhe_b200_host_alloc(size_t bytes, void **ptr) {
+  if (!ptr) return COFHE_B200_EINVAL;
+  *ptr = nullptr;
+  if (bytes == 0) return COFHE_B200_OK;
+  if (cudaMallocHost(ptr, bytes) != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return COFHE_B200_ENOMEM; }
+  return COFHE_B200_OK;
+}
+void cofhe_b200_host_free(void *ptr) { if (ptr) cudaFreeHost(ptr); }
+void *cofhe_b200_stream(cofhe_b200_ctx *ctx) { return ctx ? (void *)ctx->xfer : nullptr; }
+int cofhe_b200_upload(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream) {
+  if (!ctx || (bytes && (!dst || !src))) return COFHE_B200_EINVAL;
+  if (bytes == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return COFHE_B200_OK;
+}
+int cofhe_b200_download(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream) {
+  if (!ctx || (bytes && (!dst || !src))) return COFHE_B200_EINVAL;
+  if (bytes == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return COFHE_B200_OK;
+}
+int cofhe_b200_device_count(void) {
+  int c = 0;
+  if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return c;
+}
+
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out) {
   if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;

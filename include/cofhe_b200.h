@@ -134,6 +134,18 @@ int cofhe_b200_combine(cofhe_b200_ctx *ctx, size_t n, uint32_t t, const uint32_t
 int cofhe_b200_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *sk, uint32_t el, uint32_t *m, uint32_t ml,
                        void *stream);
 
+/* ---- memory helpers, so that a caller (the header class include/cuda/cuda_cryptosystem.hpp) needs nothing but this
+ * header: device buffers on the context's device, pinned host buffers, copies ordered on a stream, and the
+ * context's own non-blocking stream (cofhe_b200_status(ctx, stream) synchronises it and reports element errors). */
+int cofhe_b200_device_count(void);
+int cofhe_b200_dev_alloc(cofhe_b200_ctx *ctx, size_t bytes, void **ptr);
+void cofhe_b200_dev_free(cofhe_b200_ctx *ctx, void *ptr);
+int cofhe_b200_host_alloc(size_t bytes, void **ptr);
+void cofhe_b200_host_free(void *ptr);
+void *cofhe_b200_stream(cofhe_b200_ctx *ctx);
+int cofhe_b200_upload(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream);
+int cofhe_b200_download(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream);
+
 /* Measurement helper (no reference counterpart): sustained rate of independent 32x32->64-bit multiply-accumulates
  * (wide != 0: IMAD.WIDE.U32) or 32-bit multiply-adds (wide == 0: IMAD) over all SMs of `device`, in MACs/s.
  * bench.py uses it as the integer-multiply roofline denominator. */

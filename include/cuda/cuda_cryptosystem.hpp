@@ -1,0 +1,695 @@
+// cofhe_b200 -- B200CryptoSystem: the drop-in for CoFHE's CryptoSystem template argument on NVIDIA B200.
+//
+// This file takes the place of the reference's stub of the same path (reference include/cuda/cuda_cryptosystem.hpp:1-4,
+// `#error "Not implemented"`).  It exposes every public member of CoFHE::CPUCryptoSystem (reference
+// include/x86_64/cpu_cryptosystem.hpp:23-139) with the same names, argument meaning, ownership (batched calls return
+// containers of `new`-allocated BICYCL objects) and exceptions, so ComputeRequestHandler<CryptoSystem>,
+// SMPCClient<CryptoSystem>, benchmarks/local.cpp ... compile unchanged with CryptoSystem = B200CryptoSystem
+// (define COFHE_B200 to make the name CPUCryptoSystem mean this class: see INTEGRATION.md).
+//
+// Split of work:
+//   * batched tensor / vector entry points (encrypt, decrypt, part_decrypt, combine, add, scal incl. matmul, negate)
+//     marshal Tensor<T*> into structure-of-arrays limb buffers and call the C ABI of libcofhe_b200.so
+//     (include/cofhe_b200.h) -- hand-written sm_100a kernels, no CPU fallback;
+//   * everything that is not data parallel stays on the host through an embedded reference CPUCryptoSystem: setup,
+//     key generation, share generation, the RandGen (draw ORDER is part of the contract: SURVEY.md section 8b),
+//     single-element calls, the float codec and the 20 (de)serialisers.
+// Needs the reference headers on the include path (BICYCL types cross this boundary) and -lcofhe_b200.
+#ifndef COFHE_B200_CUDA_CRYPTO_SYSTEM_HPP_INCLUDED
+#define COFHE_B200_CUDA_CRYPTO_SYSTEM_HPP_INCLUDED
+
+#include <cstdint>
+#include <cstring>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "x86_64/cpu_cryptosystem.hpp"
+#include "cofhe_b200.h"
+
+namespace CoFHE
+{
+    namespace b200_detail
+    {
+        // status codes of the C ABI back into the exceptions the reference throws (std::invalid_argument for bad
+        // shapes/arguments, std::runtime_error otherwise; node handlers catch std::exception)
+        inline void check(int rc, const char *what)
+        {
+            if (rc == COFHE_B200_OK)
+                return;
+            std::string msg = std::string("cofhe_b200: ") + what + " failed (" + std::to_string(rc) + ")";
+            if (rc == COFHE_B200_EINVAL)
+                throw std::invalid_argument(msg);
+            throw std::runtime_error(msg);
+        }
+
+        // limb i of element idx lives at dst[i*stride + idx]; signed values are two's complement over nl limbs
+        inline void put_mpz(const BICYCL::Mpz &z, uint32_t *dst, size_t nl, size_t stride, bool twos)
+        {
+            if (z.nbits() > 32 * nl - (twos ? 1 : 0))
+                throw std::range_error("cofhe_b200: integer does not fit the limb shape");
+            uint32_t tmp[2 * 216 + 4];
+            size_t cnt = 0;
+            std::memset(tmp, 0, (nl + 1) * sizeof(uint32_t));
+            mpz_export(tmp, &cnt, -1, 4, 0, 0, (mpz_srcptr)z);
+            if (z.sgn() < 0)
+            {
+                if (!twos)
+                    throw std::range_error("cofhe_b200: negative value where an unsigned one is required");
+                uint64_t c = 1;
+                for (size_t i = 0; i < nl; i++)
+                {
+                    uint64_t v = (uint64_t)(uint32_t)~tmp[i] + c;
+                    tmp[i] = (uint32_t)v;
+                    c = v >> 32;
+                }
+            }
+            for (size_t i = 0; i < nl; i++)
+                dst[i * stride] = tmp[i];
+        }
+        inline BICYCL::Mpz get_mpz(const uint32_t *src, size_t nl, size_t stride, bool twos)
+        {
+            uint32_t tmp[2 * 216 + 4];
+            for (size_t i = 0; i < nl; i++)
+                tmp[i] = src[i * stride];
+            bool neg = twos && (tmp[nl - 1] >> 31);
+            if (neg)
+            {
+                uint64_t c = 1;
+                for (size_t i = 0; i < nl; i++)
+                {
+                    uint64_t v = (uint64_t)(uint32_t)~tmp[i] + c;
+                    tmp[i] = (uint32_t)v;
+                    c = v >> 32;
+                }
+            }
+            mpz_t t;
+            mpz_init(t);
+            mpz_import(t, nl, -1, 4, 0, 0, tmp);
+            if (neg)
+                mpz_neg(t, t);
+            return BICYCL::Mpz(std::move(t)); // takes ownership of the limbs (gmp_extras.inl:256-261)
+        }
+    } // namespace b200_detail
+
+    class B200CryptoSystem
+    {
+    public:
+        using SecretKey = CPUCryptoSystem::SecretKey;
+        using SecretKeyShare = CPUCryptoSystem::SecretKeyShare;
+        using PublicKey = CPUCryptoSystem::PublicKey;
+        using PlainText = CPUCryptoSystem::PlainText;
+        using CipherText = CPUCryptoSystem::CipherText;
+        using PartDecryptionResult = CPUCryptoSystem::PartDecryptionResult;
+
+        // (N_bits a.k.a. security_level, k, compact): same meaning as CPUCryptoSystem (cpu_cryptosystem.hpp:33).
+        // The compact variant keeps c1 in Cl(DeltaK); the device path covers the non-compact scheme every caller
+        // of the reference uses, so compact == true is refused here instead of silently running on the host.
+        B200CryptoSystem(uint32_t security_level, uint32_t k, bool compact = false, int device = 0)
+            : host_(security_level, k, compact), device_(device)
+        {
+            if (compact)
+                throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
+            open();
+        }
+        // copies re-create the RandGen exactly as the reference does (cpu_cryptosystem.hpp:37-68) and own a fresh
+        // device context (contexts are not shared between objects: each serialises its own calls)
+        B200CryptoSystem(const B200CryptoSystem &o) : host_(o.host_), device_(o.device_) { open(); }
+        B200CryptoSystem(B200CryptoSystem &&o) : host_(std::move(o.host_)), device_(o.device_) { open(); }
+        B200CryptoSystem &operator=(const B200CryptoSystem &o)
+        {
+            if (this != &o)
+            {
+                close();
+                host_ = o.host_;
+                device_ = o.device_;
+                open();
+            }
+            return *this;
+        }
+        B200CryptoSystem &operator=(B200CryptoSystem &&o)
+        {
+            if (this != &o)
+            {
+                close();
+                host_ = std::move(o.host_);
+                device_ = o.device_;
+                open();
+            }
+            return *this;
+        }
+        ~B200CryptoSystem() { close(); }
+
+        // ---- host side: forwarded to the embedded reference object (same RandGen draws, same results) ----------
+        SecretKey keygen() const { return host_.keygen(); }
+        PublicKey keygen(const SecretKey &sk) const { return host_.keygen(sk); }
+        Vector<Vector<SecretKeyShare>> keygen(const SecretKey &sk, size_t threshold, size_t num_parties) const { return host_.keygen(sk, threshold, num_parties); }
+        CipherText encrypt(const PublicKey &pk, const PlainText &pt) const { return host_.encrypt(pk, pt); }
+        PlainText decrypt(const SecretKey &sk, const CipherText &ct) const { return host_.decrypt(sk, ct); }
+        PartDecryptionResult part_decrypt(const SecretKeyShare &sks, const CipherText &ct) const { return host_.part_decrypt(sks, ct); }
+        PlainText combine_part_decryption_results(const CipherText &ct, const Vector<PartDecryptionResult> &pdrs) const { return host_.combine_part_decryption_results(ct, pdrs); }
+        CipherText add_ciphertexts(const PublicKey &pk, const CipherText &ct1, const CipherText &ct2) const { return host_.add_ciphertexts(pk, ct1, ct2); }
+        CipherText scal_ciphertext(const PublicKey &pk, const PlainText &s, const CipherText &ct) const { return host_.scal_ciphertext(pk, s, ct); }
+        CipherText negate_ciphertext(const PublicKey &pk, const CipherText &ct) const { return host_.negate_ciphertext(pk, ct); }
+        PlainText generate_random_plaintext() const { return host_.generate_random_plaintext(); }
+        Vector<PlainText> generate_random_beavers_triplet() const { return host_.generate_random_beavers_triplet(); }
+        PlainText add_plaintexts(const PlainText &a, const PlainText &b) const { return host_.add_plaintexts(a, b); }
+        PlainText multiply_plaintexts(const PlainText &a, const PlainText &b) const { return host_.multiply_plaintexts(a, b); }
+        Tensor<PlainText *> add_plaintext_tensors(const Tensor<PlainText *> &a, const Tensor<PlainText *> &b) const { return host_.add_plaintext_tensors(a, b); }
+        Tensor<PlainText *> multiply_plaintext_tensors(const Tensor<PlainText *> &a, const Tensor<PlainText *> &b) const { return host_.multiply_plaintext_tensors(a, b); }
+        PlainText negate_plaintext(const PlainText &s) const { return host_.negate_plaintext(s); }
+        Tensor<PlainText *> negate_plaintext_tensor(const Tensor<PlainText *> &pt) const { return host_.negate_plaintext_tensor(pt); }
+        PlainText make_plaintext(float value) const { return host_.make_plaintext(value); }
+        float get_float_from_plaintext(const PlainText &pt) const { return host_.get_float_from_plaintext(pt); }
+
+        String serialize() const { return host_.serialize(); }
+        String serialize_secret_key(const SecretKey &sk) const { return host_.serialize_secret_key(sk); }
+        String serialize_secret_key_share(const SecretKeyShare &sks) const { return host_.serialize_secret_key_share(sks); }
+        String serialize_public_key(const PublicKey &pk) const { return host_.serialize_public_key(pk); }
+        String serialize_plaintext(const PlainText &pt) const { return host_.serialize_plaintext(pt); }
+        String serialize_ciphertext(const CipherText &ct) const { return host_.serialize_ciphertext(ct); }
+        String serialize_part_decryption_result(const PartDecryptionResult &pdr) const { return host_.serialize_part_decryption_result(pdr); }
+        String serialize_plaintext_tensor(const Tensor<PlainText *> &t) const { return host_.serialize_plaintext_tensor(t); }
+        String serialize_ciphertext_tensor(const Tensor<CipherText *> &t) const { return host_.serialize_ciphertext_tensor(t); }
+        String serialize_part_decryption_result_tensor(const Tensor<PartDecryptionResult *> &t) const { return host_.serialize_part_decryption_result_tensor(t); }
+        static B200CryptoSystem deserialize(const String &data) { return B200CryptoSystem(CPUCryptoSystem::deserialize(data)); }
+        SecretKey deserialize_secret_key(const String &d) const { return host_.deserialize_secret_key(d); }
+        SecretKeyShare deserialize_secret_key_share(const String &d) const { return host_.deserialize_secret_key_share(d); }
+        PublicKey deserialize_public_key(const String &d) const { return host_.deserialize_public_key(d); }
+        PlainText deserialize_plaintext(const String &d) const { return host_.deserialize_plaintext(d); }
+        CipherText deserialize_ciphertext(const String &d) const { return host_.deserialize_ciphertext(d); }
+        PartDecryptionResult deserialize_part_decryption_result(const String &d) const { return host_.deserialize_part_decryption_result(d); }
+        Tensor<PlainText *> deserialize_plaintext_tensor(const String &d) const { return host_.deserialize_plaintext_tensor(d); }
+        Tensor<CipherText *> deserialize_ciphertext_tensor(const String &d) const { return host_.deserialize_ciphertext_tensor(d); }
+        Tensor<PartDecryptionResult *> deserialize_part_decryption_result_tensor(const String &d) const { return host_.deserialize_part_decryption_result_tensor(d); }
+
+        BICYCL::RandGen &get_rand_gen() { return host_.get_rand_gen(); }
+        const BICYCL::CL_HSM2k &get_hsm2k() const { return host_.get_hsm2k(); }
+        // launches issued by this object's device context so far
+        uint64_t gpu_launches() const { return cofhe_b200_launch_count(ctx_); }
+
+        // ---- device side: the batched entry points (definitions below) --------------------------------------------
+        Vector<CipherText *> encrypt_vector(const PublicKey &pk, const Vector<PlainText *> &pt) const;
+        Tensor<CipherText *> encrypt_tensor(const PublicKey &pk, const Tensor<PlainText *> &pt) const;
+        Vector<PlainText *> decrypt_vector(const SecretKey &sk, const Vector<CipherText *> &ct) const;
+        Tensor<PlainText *> decrypt_tensor(const SecretKey &sk, const Tensor<CipherText *> &ct) const;
+        Vector<PartDecryptionResult *> part_decrypt_vector(const SecretKeyShare &sks, const Vector<CipherText *> &ct) const;
+        Tensor<PartDecryptionResult *> part_decrypt_tensor(const SecretKeyShare &sks, const Tensor<CipherText *> &ct) const;
+        Vector<PlainText *> combine_part_decryption_results_vector(const CipherText &ct, const Vector<PartDecryptionResult *> &pdrs) const;
+        Tensor<PlainText *> combine_part_decryption_results_tensor(const Tensor<CipherText *> &ct, const Vector<Tensor<PartDecryptionResult *>> &pdrs) const;
+        Vector<CipherText *> add_ciphertext_vectors(const PublicKey &pk, const Vector<CipherText *> &ct1, const Vector<CipherText *> &ct2) const;
+        Vector<CipherText *> scal_ciphertext_vector(const PublicKey &pk, const PlainText &s, const Vector<CipherText *> &ct) const;
+        Vector<CipherText *> scal_ciphertext_vector(const PublicKey &pk, const Vector<PlainText *> &s, const Vector<CipherText *> &ct) const;
+        Tensor<CipherText *> add_ciphertext_tensors(const PublicKey &pk, const Tensor<CipherText *> &ct1, const Tensor<CipherText *> &ct2) const;
+        Tensor<CipherText *> scal_ciphertext_tensors(const PublicKey &pk, const Tensor<PlainText *> &s, const Tensor<CipherText *> &ct) const;
+        Tensor<CipherText *> negate_ciphertext_tensor(const PublicKey &pk, const Tensor<CipherText *> &ct) const;
+
+        // wrap an existing reference object (used by deserialize)
+        explicit B200CryptoSystem(CPUCryptoSystem host, int device = 0) : host_(std::move(host)), device_(device)
+        {
+            if (host_.get_hsm2k().compact_variant())
+                throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
+            open();
+        }
+
+    private:
+        mutable CPUCryptoSystem host_; // RandGen lives here; draws happen in the reference's call order
+        int device_;
+        cofhe_b200_ctx *ctx_ = nullptr;
+        uint32_t na_ = 0, nc_ = 0, nd_ = 0, ml_ = 0, el_r_ = 0;
+        mutable std::mutex mu_;        // one call at a time per context (the reference's methods are const and are
+                                       // called from 8 server threads: node/server.hpp:16,187-196)
+        mutable bool pk_set_ = false;
+        mutable BICYCL::QFI pk_cached_;
+        // staging arena: pinned host memory + device memory of the same size, grown on demand
+        mutable uint32_t *h_arena_ = nullptr;
+        mutable uint32_t *d_arena_ = nullptr;
+        mutable size_t arena_words_ = 0;
+
+        size_t fl() const { return 2 * (size_t)na_ + nc_; }
+
+        void open()
+        {
+            using namespace b200_detail;
+            const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
+            BICYCL::Mpz absd(H.Delta());
+            absd.neg();
+            std::vector<uint32_t> dl((absd.nbits() + 31) / 32);
+            put_mpz(absd, dl.data(), dl.size(), 1, false);
+            check(cofhe_b200_create(&ctx_, device_, dl.data(), (uint32_t)dl.size()), "create");
+            check(cofhe_b200_shape(ctx_, &na_, &nc_, &nd_), "shape");
+            std::vector<uint32_t> nl((H.N().nbits() + 31) / 32);
+            put_mpz(H.N(), nl.data(), nl.size(), 1, false);
+            check(cofhe_b200_set_scheme(ctx_, (uint32_t)H.k(), nl.data(), (uint32_t)nl.size()), "set_scheme");
+            ml_ = ((uint32_t)H.k() + 31) / 32;
+            el_r_ = (uint32_t)((H.encrypt_randomness_bound().nbits() + 31) / 32);
+            pk_set_ = false;
+        }
+        void close()
+        {
+            if (ctx_)
+            {
+                if (d_arena_)
+                    cofhe_b200_dev_free(ctx_, d_arena_);
+                if (h_arena_)
+                    cofhe_b200_host_free(h_arena_);
+                cofhe_b200_destroy(ctx_);
+            }
+            ctx_ = nullptr;
+            d_arena_ = h_arena_ = nullptr;
+            arena_words_ = 0;
+        }
+        void reserve(size_t words) const
+        {
+            using namespace b200_detail;
+            if (words <= arena_words_)
+                return;
+            if (d_arena_)
+                cofhe_b200_dev_free(ctx_, d_arena_);
+            if (h_arena_)
+                cofhe_b200_host_free(h_arena_);
+            d_arena_ = h_arena_ = nullptr;
+            arena_words_ = 0;
+            void *h = nullptr, *d = nullptr;
+            check(cofhe_b200_host_alloc(words * 4, &h), "host_alloc");
+            h_arena_ = (uint32_t *)h;
+            check(cofhe_b200_dev_alloc(ctx_, words * 4, &d), "dev_alloc");
+            d_arena_ = (uint32_t *)d;
+            arena_words_ = words;
+        }
+        // fixed-base tables follow the public key the caller passes (rebuilt only when it changes)
+        void ensure_pk(const PublicKey &pk) const
+        {
+            using namespace b200_detail;
+            if (pk_set_ && pk.elt() == pk_cached_)
+                return;
+            const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
+            std::vector<uint32_t> hb(fl()), pb(fl());
+            put_form(H.h(), hb.data(), 0, 1);
+            put_form(pk.elt(), pb.data(), 0, 1);
+            check(cofhe_b200_set_bases(ctx_, hb.data(), pb.data(), (uint32_t)H.encrypt_randomness_bound().nbits()), "set_bases");
+            pk_cached_ = pk.elt();
+            pk_set_ = true;
+        }
+
+        // ---- marshalling between BICYCL objects and the SoA limb layout (include/cofhe_b200.h "Layout") -----------
+        void put_form(const BICYCL::QFI &f, uint32_t *buf, size_t idx, size_t n) const
+        {
+            b200_detail::put_mpz(f.a(), buf + idx, na_, n, false);
+            b200_detail::put_mpz(f.b(), buf + (size_t)na_ * n + idx, na_, n, true);
+            b200_detail::put_mpz(f.c(), buf + (size_t)2 * na_ * n + idx, nc_, n, false);
+        }
+        BICYCL::QFI get_form(const uint32_t *buf, size_t idx, size_t n) const
+        {
+            return BICYCL::QFI(b200_detail::get_mpz(buf + idx, na_, n, false), b200_detail::get_mpz(buf + (size_t)na_ * n + idx, na_, n, true),
+                               b200_detail::get_mpz(buf + (size_t)2 * na_ * n + idx, nc_, n, false), true);
+        }
+        template <class Cts> // anything indexable yielding CipherText*
+        void put_cts(const Cts &cts, size_t n, uint32_t *buf) const
+        {
+            CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++)
+            {
+                put_form(cts[i]->c1(), buf, i, n);
+                put_form(cts[i]->c2(), buf + fl() * n, i, n);
+            }
+        }
+        CipherText *get_ct(const uint32_t *buf, size_t i, size_t n) const
+        {
+            return new CipherText(get_form(buf, i, n), get_form(buf + fl() * n, i, n));
+        }
+        void up(const uint32_t *h, size_t words) const
+        {
+            b200_detail::check(cofhe_b200_upload(ctx_, d_arena_ + (h - h_arena_), h, words * 4, cofhe_b200_stream(ctx_)), "upload");
+        }
+        // download + synchronise + report element errors
+        void down(uint32_t *h, size_t words) const
+        {
+            b200_detail::check(cofhe_b200_download(ctx_, h, d_arena_ + (h - h_arena_), words * 4, cofhe_b200_stream(ctx_)), "download");
+            b200_detail::check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "device arithmetic");
+        }
+        uint32_t *dev(const uint32_t *h) const { return d_arena_ + (h - h_arena_); }
+        static uint32_t limbs_of(const BICYCL::Mpz &z) { return z.nbits() ? (uint32_t)((z.nbits() + 31) / 32) : 1; }
+
+        // shared bodies (flat index ranges; the tensor / vector entry points only differ in their containers)
+        template <class Pts, class Out>
+        void encrypt_flat(const PublicKey &pk, const Pts &pts, size_t n, Out &out) const;
+        template <class Cts, class Out>
+        void decrypt_flat(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const;
+        template <class Cts, class Out>
+        void part_decrypt_flat(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const;
+        template <class Cts, class Out>
+        void add_flat(const Cts &a, const Cts &b, size_t n, Out &out) const;
+        template <class Cts, class Exps, class Out>
+        void pow_flat(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const;
+    };
+
+    // =================================================================================================================
+    // flat bodies
+    // =================================================================================================================
+    // encrypt_tensor / encrypt_vector: ONE r per call, c1 = h^r shared, c2_i = pk^r o f^{m_i}
+    // (reference cpu_cryptosystem_tensor_ops.inl:1-19, cpu_cryptosystem_vector_ops.inl:4-18)
+    template <class Pts, class Out>
+    inline void B200CryptoSystem::encrypt_flat(const PublicKey &pk, const Pts &pts, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
+        BICYCL::Mpz r = host_.get_rand_gen().random_mpz(H.encrypt_randomness_bound()); // the call's single draw
+        if (n == 0)
+            return;
+        ensure_pk(pk);
+        size_t mw = (size_t)ml_ * n, rw = el_r_, cw = 2 * fl() * n;
+        reserve(mw + rw + cw);
+        uint32_t *hm = h_arena_, *hr = hm + mw, *hc = hr + rw;
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++)
+        {
+            BICYCL::Mpz m;
+            BICYCL::Mpz::mod(m, *pts[i], H.cleartext_bound()); // f has order 2^k: only m mod 2^k matters
+            put_mpz(m, hm + i, ml_, n, false);
+        }
+        put_mpz(r, hr, el_r_, 1, false);
+        up(hm, mw + rw);
+        check(cofhe_b200_encrypt(ctx_, n, dev(hm), ml_, dev(hr), el_r_, 1, dev(hc), cofhe_b200_stream(ctx_)), "encrypt");
+        down(hc, cw);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = get_ct(hc, i, n);
+    }
+
+    // decrypt_tensor / decrypt_vector (cpu_cryptosystem_tensor_ops.inl:21-33)
+    template <class Cts, class Out>
+    inline void B200CryptoSystem::decrypt_flat(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        if (n == 0)
+            return;
+        size_t cw = 2 * fl() * n, mw = (size_t)ml_ * n;
+        reserve(cw + mw);
+        uint32_t *hc = h_arena_, *hm = hc + cw;
+        put_cts(cts, n, hc);
+        up(hc, cw);
+        uint32_t el = limbs_of(sk);
+        std::vector<uint32_t> e(el);
+        put_mpz(sk, e.data(), el, 1, false);
+        check(cofhe_b200_decrypt(ctx_, n, dev(hc), e.data(), el, dev(hm), ml_, cofhe_b200_stream(ctx_)), "decrypt");
+        down(hm, mw);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = new PlainText(get_mpz(hm + i, ml_, n, false));
+    }
+
+    // part_decrypt_tensor / part_decrypt_vector: d_i = c1_i^share (cpu_cryptosystem_tensor_ops.inl:35-47)
+    template <class Cts, class Out>
+    inline void B200CryptoSystem::part_decrypt_flat(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        if (n == 0)
+            return;
+        size_t cw = 2 * fl() * n, dw = fl() * n;
+        reserve(cw + dw);
+        uint32_t *hc = h_arena_, *hd = hc + cw;
+        put_cts(cts, n, hc);
+        up(hc, cw);
+        BICYCL::Mpz mag(sks);
+        BICYCL::Mpz::abs(mag, mag);
+        uint32_t el = limbs_of(mag);
+        std::vector<uint32_t> e(el);
+        put_mpz(mag, e.data(), el, 1, false);
+        check(cofhe_b200_part_decrypt(ctx_, n, dev(hc), e.data(), el, sks.sgn() < 0, dev(hd), cofhe_b200_stream(ctx_)), "part_decrypt");
+        down(hd, dw);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = new PartDecryptionResult(get_form(hd, i, n));
+    }
+
+    // add_ciphertext_tensors / add_ciphertext_vectors: no randomness (cpu_cryptosystem_tensor_ops.inl:242-264)
+    template <class Cts, class Out>
+    inline void B200CryptoSystem::add_flat(const Cts &a, const Cts &b, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        if (n == 0)
+            return;
+        size_t cw = 2 * fl() * n;
+        reserve(3 * cw);
+        uint32_t *h1 = h_arena_, *h2 = h1 + cw, *h3 = h2 + cw;
+        put_cts(a, n, h1);
+        put_cts(b, n, h2);
+        up(h1, 2 * cw);
+        check(cofhe_b200_add_ciphertexts(ctx_, n, dev(h1), dev(h2), dev(h3), cofhe_b200_stream(ctx_)), "add_ciphertexts");
+        down(h3, cw);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = get_ct(h3, i, n);
+    }
+
+    // (c1^s, c2^s) with one shared scalar or one scalar per element; no randomness in the batched reference paths
+    // (cpu_cryptosystem_tensor_ops.inl:135-195 negate, :280-340 1-D scal; cpu_cryptosystem_vector_ops.inl:122-242)
+    template <class Cts, class Exps, class Out>
+    inline void B200CryptoSystem::pow_flat(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        if (n == 0)
+            return;
+        uint32_t el = 1;
+        if (per_elem)
+            for (size_t i = 0; i < n; i++)
+                el = std::max(el, limbs_of(*(*per_elem)[i]));
+        else
+            el = limbs_of(*shared);
+        size_t cw = 2 * fl() * n, ew = per_elem ? (size_t)el * n : el, sw = per_elem ? (n + 3) / 4 : 0;
+        reserve(2 * cw + ew + sw);
+        uint32_t *hc = h_arena_, *he = hc + cw, *hs = he + ew, *ho = hs + sw;
+        put_cts(cts, n, hc);
+        int shared_neg = 0;
+        if (per_elem)
+        {
+            unsigned char *sg = (unsigned char *)hs;
+            for (size_t i = 0; i < n; i++)
+            {
+                BICYCL::Mpz mag(*(*per_elem)[i]);
+                sg[i] = mag.sgn() < 0;
+                BICYCL::Mpz::abs(mag, mag);
+                put_mpz(mag, he + i, el, n, false);
+            }
+        }
+        else
+        {
+            BICYCL::Mpz mag(*shared);
+            shared_neg = mag.sgn() < 0;
+            BICYCL::Mpz::abs(mag, mag);
+            put_mpz(mag, he, el, 1, false);
+        }
+        up(hc, cw + ew + sw);
+        void *st = cofhe_b200_stream(ctx_);
+        for (int y = 0; y < 2; y++) // c1 block, c2 block
+            check(cofhe_b200_nupow(ctx_, n, dev(hc) + y * fl() * n, dev(he), el, per_elem ? 1 : 0, per_elem ? (const uint8_t *)dev(hs) : nullptr,
+                                   shared_neg, dev(ho) + y * fl() * n, st), "nupow");
+        down(ho, cw);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = get_ct(ho, i, n);
+    }
+
+    // =================================================================================================================
+    // public batched entry points: containers, shapes and exceptions as the reference's
+    // =================================================================================================================
+    inline Vector<B200CryptoSystem::CipherText *> B200CryptoSystem::encrypt_vector(const PublicKey &pk, const Vector<PlainText *> &pt) const
+    {
+        Vector<CipherText *> res(pt.size());
+        encrypt_flat(pk, pt, pt.size(), res);
+        return res;
+    }
+    inline Tensor<B200CryptoSystem::CipherText *> B200CryptoSystem::encrypt_tensor(const PublicKey &pk, const Tensor<PlainText *> &pt) const
+    {
+        Tensor<CipherText *> ct(pt.shape(), nullptr);
+        auto flat = pt;
+        flat.flatten();
+        ct.flatten();
+        encrypt_flat(pk, flat, pt.num_elements(), ct);
+        ct.reshape(pt.shape());
+        return ct;
+    }
+    inline Vector<B200CryptoSystem::PlainText *> B200CryptoSystem::decrypt_vector(const SecretKey &sk, const Vector<CipherText *> &ct) const
+    {
+        Vector<PlainText *> res(ct.size());
+        decrypt_flat(sk, ct, ct.size(), res);
+        return res;
+    }
+    inline Tensor<B200CryptoSystem::PlainText *> B200CryptoSystem::decrypt_tensor(const SecretKey &sk, const Tensor<CipherText *> &ct) const
+    {
+        Tensor<PlainText *> pt(ct.shape(), nullptr);
+        auto flat = ct;
+        flat.flatten();
+        pt.flatten();
+        decrypt_flat(sk, flat, ct.num_elements(), pt);
+        pt.reshape(ct.shape());
+        return pt;
+    }
+    inline Vector<B200CryptoSystem::PartDecryptionResult *> B200CryptoSystem::part_decrypt_vector(const SecretKeyShare &sks, const Vector<CipherText *> &ct) const
+    {
+        Vector<PartDecryptionResult *> res(ct.size());
+        part_decrypt_flat(sks, ct, ct.size(), res);
+        return res;
+    }
+    inline Tensor<B200CryptoSystem::PartDecryptionResult *> B200CryptoSystem::part_decrypt_tensor(const SecretKeyShare &sks, const Tensor<CipherText *> &ct) const
+    {
+        Tensor<PartDecryptionResult *> pdr(ct.shape(), nullptr);
+        auto flat = ct;
+        flat.flatten();
+        pdr.flatten();
+        part_decrypt_flat(sks, flat, ct.num_elements(), pdr);
+        pdr.reshape(ct.shape());
+        return pdr;
+    }
+    // the reference's vector variant indexes `pdrs` both as parties and as results (cpu_cryptosystem_vector_ops.inl:42-56);
+    // that quirk is kept by forwarding
+    inline Vector<B200CryptoSystem::PlainText *> B200CryptoSystem::combine_part_decryption_results_vector(const CipherText &ct, const Vector<PartDecryptionResult *> &pdrs) const
+    {
+        return host_.combine_part_decryption_results_vector(ct, pdrs);
+    }
+    // m_i = dlog_F(c2_i o (d_0i o d_1i^-1 o ...)^-1)  (cpu_cryptosystem_tensor_ops.inl:49-73 -> finalDecrypt)
+    inline Tensor<B200CryptoSystem::PlainText *> B200CryptoSystem::combine_part_decryption_results_tensor(const Tensor<CipherText *> &ct, const Vector<Tensor<PartDecryptionResult *>> &pdrs) const
+    {
+        using namespace b200_detail;
+        if (pdrs.empty())
+            throw std::invalid_argument("No partial decryption results");
+        Tensor<PlainText *> pt(pdrs[0].shape(), nullptr);
+        auto cflat = ct;
+        cflat.flatten();
+        size_t n = ct.num_elements(), t = pdrs.size();
+        pt.flatten();
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            size_t cw = 2 * fl() * n, dw = fl() * n * t, mw = (size_t)ml_ * n;
+            if (n)
+            {
+                reserve(cw + dw + mw);
+                uint32_t *hc = h_arena_, *hd = hc + cw, *hm = hd + dw;
+                put_cts(cflat, n, hc);
+                for (size_t j = 0; j < t; j++)
+                {
+                    auto dflat = pdrs[j];
+                    dflat.flatten();
+                    if (dflat.num_elements() != n)
+                        throw std::invalid_argument("Tensor shapes must be equal");
+                    CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) put_form(*dflat[i], hd + j * fl() * n, i, n);
+                }
+                up(hc, cw + dw);
+                check(cofhe_b200_combine(ctx_, n, (uint32_t)t, dev(hc), dev(hd), dev(hm), ml_, cofhe_b200_stream(ctx_)), "combine");
+                down(hm, mw);
+                CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) pt[i] = new PlainText(get_mpz(hm + i, ml_, n, false));
+            }
+        }
+        pt.reshape(pdrs[0].shape());
+        return pt;
+    }
+    inline Vector<B200CryptoSystem::CipherText *> B200CryptoSystem::add_ciphertext_vectors(const PublicKey &, const Vector<CipherText *> &ct1, const Vector<CipherText *> &ct2) const
+    {
+        if (ct1.size() != ct2.size())
+            throw std::invalid_argument("Vector sizes must be equal");
+        Vector<CipherText *> res(ct1.size());
+        add_flat(ct1, ct2, ct1.size(), res);
+        return res;
+    }
+    inline Vector<B200CryptoSystem::CipherText *> B200CryptoSystem::scal_ciphertext_vector(const PublicKey &, const PlainText &s, const Vector<CipherText *> &ct) const
+    {
+        if (s.sgn() < 0)
+            throw std::invalid_argument("CPUCryptoSystem::PlainText must be non-negative");
+        Vector<CipherText *> res(ct.size());
+        pow_flat<Vector<CipherText *>, Vector<PlainText *>>(ct, ct.size(), nullptr, &s, res);
+        return res;
+    }
+    inline Vector<B200CryptoSystem::CipherText *> B200CryptoSystem::scal_ciphertext_vector(const PublicKey &, const Vector<PlainText *> &s, const Vector<CipherText *> &ct) const
+    {
+        if (s.size() != ct.size())
+            throw std::invalid_argument("Vector sizes must be equal");
+        Vector<CipherText *> res(ct.size());
+        pow_flat(ct, ct.size(), &s, nullptr, res);
+        return res;
+    }
+    inline Tensor<B200CryptoSystem::CipherText *> B200CryptoSystem::add_ciphertext_tensors(const PublicKey &pk, const Tensor<CipherText *> &ct1_, const Tensor<CipherText *> &ct2_) const
+    {
+        if (ct1_.is_zero_degree() && ct2_.is_zero_degree())
+            return Tensor<CipherText *>(new CipherText(this->add_ciphertexts(pk, *ct1_.get_value(), *ct2_.get_value())));
+        if (ct1_.shape() != ct2_.shape())
+            throw std::invalid_argument("Tensor shapes must be equal");
+        auto ct1 = ct1_, ct2 = ct2_;
+        auto shape = ct1.shape();
+        ct1.flatten();
+        ct2.flatten();
+        Tensor<CipherText *> res({ct1.num_elements()}, nullptr);
+        add_flat(ct1, ct2, ct1.num_elements(), res);
+        res.reshape(shape);
+        return res;
+    }
+    // ct^(2^k - 1) elementwise, no randomness (cpu_cryptosystem_tensor_ops.inl:135-195; make_plaintext(-1) = 2^k - 1)
+    inline Tensor<B200CryptoSystem::CipherText *> B200CryptoSystem::negate_ciphertext_tensor(const PublicKey &, const Tensor<CipherText *> &ct) const
+    {
+        PlainText s = this->make_plaintext(-1);
+        auto flat = ct;
+        flat.flatten();
+        Tensor<CipherText *> res(ct.shape(), nullptr);
+        res.flatten();
+        pow_flat<Tensor<CipherText *>, Vector<PlainText *>>(flat, ct.num_elements(), nullptr, &s, res);
+        res.reshape(ct.shape());
+        return res;
+    }
+    // 0-D: single re-randomising scal on the host (1 draw); 1-D: elementwise (c1^s_i, c2^s_i), no randomness;
+    // 2-D: res[i,k] = zero o prod_j ct[i,j]^{s[j,k]} with zero = encrypt(pk, 0) (1 draw)
+    // (cpu_cryptosystem_tensor_ops.inl:269-462).  Matmul scalars must be non-negative (they are residues mod 2^k).
+    inline Tensor<B200CryptoSystem::CipherText *> B200CryptoSystem::scal_ciphertext_tensors(const PublicKey &pk, const Tensor<PlainText *> &s, const Tensor<CipherText *> &cts) const
+    {
+        using namespace b200_detail;
+        if (s.ndim() > 2 || cts.ndim() > 2)
+            throw std::invalid_argument("Tensors must be 0D, 1D or 2D for now");
+        if (s.is_zero_degree() && cts.is_zero_degree())
+            return Tensor<CipherText *>(new CipherText(this->scal_ciphertext(pk, *s.get_value(), *cts.get_value())));
+        if (s.is_column_vector() && cts.is_column_vector())
+        {
+            if (s.shape()[0] != cts.shape()[0])
+                throw std::invalid_argument("Vector sizes must be equal");
+            Tensor<CipherText *> res(cts.shape(), nullptr);
+            pow_flat(cts, cts.size(), &s, nullptr, res);
+            return res;
+        }
+        auto sflat = s;
+        auto cflat = cts;
+        sflat.flatten();
+        cflat.flatten();
+        size_t n = cts.shape()[0], m = cts.shape()[1], p = s.shape()[1];
+        if (s.shape()[0] != m)
+            throw std::invalid_argument("Tensor shapes must be compatible for matrix multiplication");
+        Tensor<CipherText *> res({n, p}, nullptr);
+        res.flatten();
+        CipherText zero = this->encrypt(pk, this->make_plaintext(0)); // the call's single draw, as the reference
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            uint32_t el = 1;
+            size_t ebits = 1;
+            for (size_t i = 0; i < m * p; i++)
+            {
+                if (sflat[i]->sgn() < 0)
+                    throw std::invalid_argument("matmul scalars must be non-negative");
+                ebits = std::max(ebits, (size_t)sflat[i]->nbits());
+            }
+            el = (uint32_t)((ebits + 31) / 32);
+            size_t cw = 2 * fl() * n * m, sw = (size_t)el * m * p, zw = 2 * fl(), ow = 2 * fl() * n * p;
+            reserve(cw + sw + zw + ow);
+            uint32_t *hc = h_arena_, *hs = hc + cw, *hz = hs + sw, *ho = hz + zw;
+            put_cts(cflat, n * m, hc);
+            CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < m * p; i++) put_mpz(*sflat[i], hs + i, el, m * p, false);
+            put_form(zero.c1(), hz, 0, 1);
+            put_form(zero.c2(), hz + fl(), 0, 1);
+            up(hc, cw + sw + zw);
+            check(cofhe_b200_scal_matmul(ctx_, n, m, p, dev(hc), dev(hs), el, (uint32_t)ebits, dev(hz), dev(ho), cofhe_b200_stream(ctx_)), "scal_matmul");
+            down(ho, ow);
+            CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n * p; i++) res[i] = get_ct(ho, i, n * p);
+        }
+        res.reshape({n, p});
+        return res;
+    }
+
+    // ---- factory: honours Device::GPU, which the reference's make_cryptosystem ignores (cofhe.hpp:96-121) ----------
+    inline B200CryptoSystem make_b200_cryptosystem(uint32_t security_level, uint32_t k, int device = 0)
+    {
+        return B200CryptoSystem{security_level, k, false, device};
+    }
+
+} // namespace CoFHE
+
+#endif
