@@ -233,9 +233,6 @@ int ensure_work(cofhe_b200_ctx *ctx, size_t bytes) {
   if (bytes <= ctx->work_bytes) return COFHE_B200_OK;
   if (ctx->d_work) cudaFree(ctx->d_work);  // synchronises with kernels still using the old scratch
   ctx->d_work = nullptr; ctx->work_bytes = 0;
-  ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
-  ctx->d_scheme = nullptr; ctx->k = 0; ctx->kl = 0; ctx->d_exp = nullptr;
-  ctx->d_fb_bases = nullptr; ctx->d_fb_tab = nullptr; ctx->fb_set = 0;
   if (cudaMalloc(&ctx->d_work, bytes) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
   ctx->work_bytes = bytes;
   return COFHE_B200_OK;
@@ -789,17 +786,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   int rc = COFHE_B200_OK;
   if (ctx->stage_bytes < 3 * bytes) {
     if (ctx->d_stage) cudaFree(ctx->d_stage);
-  if (ctx->d_work) cudaFree(ctx->d_work);
-  if (ctx->d_tmp) cudaFree(ctx->d_tmp);
-  if (ctx->d_scheme) cudaFree(ctx->d_scheme);
-  if (ctx->d_exp) cudaFree(ctx->d_exp);
-  if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
-  if (ctx->d_fb_tab) cudaFree(ctx->d_fb_tab);
     ctx->d_stage = nullptr; ctx->stage_bytes = 0;
-  ctx->d_work = nullptr; ctx->work_bytes = 0;
-  ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
-  ctx->d_scheme = nullptr; ctx->k = 0; ctx->kl = 0; ctx->d_exp = nullptr;
-  ctx->d_fb_bases = nullptr; ctx->d_fb_tab = nullptr; ctx->fb_set = 0;
     if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) rc = COFHE_B200_ENOMEM;
     else ctx->stage_bytes = 3 * bytes;
   }

@@ -102,3 +102,19 @@ def test_threshold(systems, tier):
     m = G.ints_out(G.combine(ct, torch.stack(ds)))
     assert m == [int(v["m"]) for v in vs]
     G.status()
+
+
+def test_mixed_sequence_keeps_state(systems):
+    """encrypt -> add -> matmul -> decrypt on ONE context (scratch growth must not disturb scheme state)."""
+    tier = load_golden("ref_t0.json")
+    G = systems(tier)
+    ct = G.encrypt(list(range(1, 13)), 12345)
+    s2 = G.add_ciphertexts(ct, ct)
+    zero = G.cts([I(tier["scal_matmul"][0]["zero"])])
+    sc = [7 * i + 3 for i in range(6)]
+    mm = G.scal_matmul(s2, sc, 4, 3, 2, zero)
+    got = G.ints_out(G.decrypt(mm, int(tier["sk"])))
+    G.status()
+    m = [2 * (i + 1) for i in range(12)]
+    want = [sum(m[i * 3 + j] * sc[j * 2 + k] for j in range(3)) % (1 << G.k) for i in range(4) for k in range(2)]
+    assert got == want
