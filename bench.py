@@ -31,7 +31,7 @@ def fixture(tier):
     with open(os.path.join(ROOT, "tests", "golden", TIERS[tier][0])) as fh:
         t = json.load(fh)
     conv = lambda x: tuple(int(y) for y in x)
-    return {"Delta": int(t["params"]["Delta"]), "h": conv(t["params"]["h"]), "pk": conv(t["pk"]),
+    return {"tier": tier, "N": int(t["params"]["N"]), "Delta": int(t["params"]["Delta"]), "h": conv(t["params"]["h"]), "pk": conv(t["pk"]),
             "bound": int(t["params"]["exponent_bound"]), "sk": int(t["sk"]), "k": int(t["params"]["k"])}
 
 
@@ -233,8 +233,11 @@ def run_product(args):
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     kern_ms, e2e_ms = times.tolist()
+    imad = ctypes.c_double()
+    G.lib.cofhe_b200_imad_probe(G.device.index, 1, ctypes.byref(imad))
+    extra = None if args.no_extra else extras(G, fx, s, world, rank, imad.value)
     if rank == 0:
-        emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks, h1.nbytes)
+        emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks, h1.nbytes, imad.value, extra)
     if world > 1:
         dist.destroy_process_group()
 
@@ -247,33 +250,97 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def extra_exponentiation(G, fx, s, n=1 << 14):
-    """Shared-exponent variable-base exponentiation (threshold part_decrypt shape, reference
-    cpu_cryptosystem_distributed.inl:244-254): form exponentiations/s on n forms, CUDA events."""
+def _timed(fn, world, reps=2):
+    """best-of-reps device time of fn() in seconds: CUDA events on the current stream, max over ranks."""
     import torch
-    f = synth_cts(G, fx, n, 77)[0].contiguous()
-    e = fx["sk"]
-    G.nupow(f, shared=e)
+    import torch.distributed as dist
+    fn()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    G.nupow(f, shared=e)
-    e1.record()
-    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(reps):
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) * 1e-3], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        best = min(best, float(t.item()))
+    return best
+
+
+def extras(G, fx, s, world, rank, imad_peak):
+    """The other BASELINE.json configs, weak-scaled (fixed work per GPU, results gathered over NCCL where the config
+    says so): scal_matmul rows (config 5: 256x256 . 256x256 at 8 GPUs = 32 ct rows per GPU), threshold part_decrypt +
+    combine (config 4), per-element-r encryption (config 3).  Every rank runs them; times are max over ranks."""
+    import torch
+    from conftest_free import golden_zero
+    from cofhe_b200 import shard as S
+    out = {}
+    k = fx["k"]
+    G.set_scheme(k, fx["N"])
+    G.set_bases(fx["h"], fx["pk"], fx["bound"].bit_length())
+    rng = random.Random(4242)
+    # ---- config 5: scalar x ciphertext matmul, row-sharded, one all-gather of the result rows
+    rows, m, p = 32, 256, 256
+    ct = synth_cts(G, fx, rows * m, 31 + rank)
+    zero = G.cts([golden_zero(fx["tier"])])
+    for label, sc in (("pattern i+1 (<= 17 bit, as benchmarks/local.cpp)", [i + 1 for i in range(m * p)]),
+                      ("uniform %d-bit" % k, [rng.getrandbits(k) for _ in range(m * p)])):
+        ebits = max(x.bit_length() for x in sc)
+        scd = G.ints(sc, (ebits + 31) // 32)
+        parts = [(r * rows, (r + 1) * rows) for r in range(world)]
+
+        def run():
+            local = G.scal_matmul(ct, scd, rows, m, p, zero, ebits=ebits)
+            return S.gather_last(local, [rows * p] * world)
+        dt = _timed(run, world)
+        G.status()
+        units = 2 * world * rows * m * p
+        macs = units * (w_exp(s, ebits) + w_comp(s)) / dt
+        out.setdefault("scal_matmul", []).append({
+            "workload": "%dx%d . %dx%d, %s, row-sharded %d rows/GPU + NCCL gather" % (world * rows, m, m, p, label, rows),
+            "form_exps_per_s": units / dt, "seconds": dt, "imad_frac_nominal": macs / imad_peak})
+    # ---- config 4: threshold decryption, element-sharded; config 3: encryption with per-element randomness
+    n = 1 << 13
+    ms = G.ints([rng.getrandbits(k) for _ in range(n)], G.ml)
+    rs = G.ints([rng.randrange(1, fx["bound"]) for _ in range(n)], G.el_r)
+    holder = {}
+
+    def enc():
+        holder["ct"] = G.encrypt(ms, rs)
+    dt = _timed(enc, world)
+    out["encrypt"] = {"workload": "%d ciphertexts/GPU, own r per ciphertext (2 fixed-base exps + f^m + 1 comp each)" % n,
+                      "encryptions_per_s": world * n / dt, "fixed_base_form_exps_per_s": 2 * world * n / dt,
+                      "imad_frac_nominal": 2 * world * n * w_exp(s, fx["bound"].bit_length()) / dt / imad_peak}
+    share = fx["sk"]
+
+    def pdec():
+        holder["d"] = G.part_decrypt(holder["ct"], share)
+    dt = _timed(pdec, world)
+    out["part_decrypt"] = {"workload": "%d ciphertexts/GPU, shared %d-bit exponent" % (n, share.bit_length()),
+                           "form_exps_per_s": world * n / dt,
+                           "imad_frac_nominal": world * n * w_exp(s, share.bit_length()) / dt / imad_peak}
+
+    def dec():
+        holder["m"] = G.decrypt(holder["ct"], share)
+    dt = _timed(dec, world, reps=1)
+    out["decrypt"] = {"workload": "%d ciphertexts/GPU (c1^sk, nucompinv, dlog_F)" % n, "decryptions_per_s": world * n / dt,
+                      "roundtrip_ok": bool(torch.equal(holder["m"], ms))}
     G.status()
-    dt = e0.elapsed_time(e1) * 1e-3
-    return {"workload": "part_decrypt-shaped nupow, %d forms, shared %d-bit exponent" % (n, e.bit_length()),
-            "form_exps_per_s": n / dt, "imad_macs_per_s": n * w_exp(s, e.bit_length()) / dt}
+    return out
 
 
-def emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks, ct_bytes):
+def emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks, ct_bytes, imad_peak, extra):
     peak_gbs, peak_src = measured_peaks()
     ms_step = kern_ms / args.steps
     value = world * n * args.steps / (kern_ms * 1e-3)
     alg_bytes = 3 * ct_bytes                       # read ct1, ct2; write res -- in this build's limb layout
     achieved = alg_bytes / (ms_step * 1e-3) / 1e9
-    imad = ctypes.c_double()
-    G.lib.cofhe_b200_imad_probe(G.device.index, 1, ctypes.byref(imad))
+    imad = ctypes.c_double(imad_peak)
     macs = 2 * n * w_comp(s) / (ms_step * 1e-3)
     line = {"metric": "ciphertext adds/sec (ciphertext_matadd 128x128)", "value": value, "unit": "ct_adds/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -297,8 +364,8 @@ def emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks,
             line["cpu_baseline"] = cpu_baseline_matadd(args.tier, G)
         else:
             line["cpu_baseline"] = {"value": None, "unit": "ct_adds/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not loadable"}
-    if not args.no_extra:
-        line["extra"] = extra_exponentiation(G, fx, s)
+    if extra is not None:
+        line["extra"] = extra
     print(json.dumps(line))
 
 
