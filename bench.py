@@ -303,7 +303,7 @@ def extras(G, fx, s, world, rank, imad_peak):
         macs = units * (w_exp(s, ebits) + w_comp(s)) / dt
         out.setdefault("scal_matmul", []).append({
             "workload": "%dx%d . %dx%d, %s, row-sharded %d rows/GPU + NCCL gather" % (world * rows, m, m, p, label, rows),
-            "form_exps_per_s": units / dt, "seconds": dt, "imad_frac_nominal": macs / imad_peak})
+            "form_exps_per_s": units / dt, "seconds": dt, "imad_frac_nominal": macs / imad_peak / world})
     # ---- config 4: threshold decryption, element-sharded; config 3: encryption with per-element randomness
     n = 1 << 13
     ms = G.ints([rng.getrandbits(k) for _ in range(n)], G.ml)
@@ -315,7 +315,7 @@ def extras(G, fx, s, world, rank, imad_peak):
     dt = _timed(enc, world)
     out["encrypt"] = {"workload": "%d ciphertexts/GPU, own r per ciphertext (2 fixed-base exps + f^m + 1 comp each)" % n,
                       "encryptions_per_s": world * n / dt, "fixed_base_form_exps_per_s": 2 * world * n / dt,
-                      "imad_frac_nominal": 2 * world * n * w_exp(s, fx["bound"].bit_length()) / dt / imad_peak}
+                      "imad_frac_nominal": 2 * world * n * w_exp(s, fx["bound"].bit_length()) / dt / imad_peak / world}
     share = fx["sk"]
 
     def pdec():
@@ -323,7 +323,7 @@ def extras(G, fx, s, world, rank, imad_peak):
     dt = _timed(pdec, world)
     out["part_decrypt"] = {"workload": "%d ciphertexts/GPU, shared %d-bit exponent" % (n, share.bit_length()),
                            "form_exps_per_s": world * n / dt,
-                           "imad_frac_nominal": world * n * w_exp(s, share.bit_length()) / dt / imad_peak}
+                           "imad_frac_nominal": world * n * w_exp(s, share.bit_length()) / dt / imad_peak / world}
 
     def dec():
         holder["m"] = G.decrypt(holder["ct"], share)

@@ -20,6 +20,10 @@
 #define QF_NOTE ((void)0)
 #endif
 #define QF_BAIL do { QF_NOTE; return false; } while (0)
+// Test hook: event counters of a host build (rounds, fallback steps, ...)
+#ifndef QF_STAT
+#define QF_STAT(k) ((void)0)
+#endif
 
 namespace cofhe {
 
@@ -51,28 +55,62 @@ QF_HD u32 divmod32(u32 a, u32 b, u32 *rem) {
   return q;
 }
 
+QF_HD float rcp_approx(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / x;
+#endif
+}
+
 // Single-precision Lehmer step: as hgcd2 (lehmer.cuh) on 32-bit leading parts; cofactors stay below 2^30.
+//
+// This loop is where a composition spends most of its instructions, so it is written for the SM: the quotient comes
+// from one reciprocal (float estimate biased low by 2^-20: for q < 2^19 it is q or q-1, one conditional fix-up), the
+// float of the divisor is reused as the next dividend, and two Euclid steps are unrolled so that the (previous,
+// current) pairs swap roles instead of moving through registers and the parity of Jebelean's test is static.
+// A quotient of 2^19 or more ends the run; the caller then takes one full-precision step.
 QF_HD Mat2 hgcd32(u32 ah, u32 bh, bool exact, u32 min_r) {
-  u32 r0 = ah, r1 = bh;
-  u32 S0 = 1, T0 = 0, S1 = 0, T1 = 1;
+  u32 rp = ah, rc = bh;
+  u32 Sp = 1, Tp = 0, Sc = 0, Tc = 1;
+  const u32 lim = min_r ? min_r : 1u;
+  float fprev = (float)rp;
   int j = 1;
-  for (;;) {
-    if (r1 == 0 || r1 < min_r) break;
-    u32 r2;
-    u32 q = divmod32(r0, r1, &r2);
-    u64 S2 = (u64)q * S1 + S0, T2 = (u64)q * T1 + T0;
-    if ((S2 | T2) >> 30) break;
-    if (!exact) {
-      bool ok;
-      if (j & 1) ok = r2 >= T2 && (u64)(r1 - r2) >= S2 + S1;
-      else ok = r2 >= S2 && (u64)(r1 - r2) >= T2 + T1;
-      if (!ok) break;
-    }
-    r0 = r1; r1 = r2; S0 = S1; S1 = (u32)S2; T0 = T1; T1 = (u32)T2;
-    j++;
+  bool swapped = false;
+  // one Euclid step: (P*) previous, (C*) current; on success the new remainder and cofactors replace the P set
+#define QF_HG_STEP(RP, SP, TP, RC, SC, TC, ODD)                                                        \
+  {                                                                                                    \
+    if (RC < lim) break;                                                                               \
+    float fcur = (float)RC;                                                                            \
+    float qf = fprev * rcp_approx(fcur) * 0.99999905f;                                                 \
+    if (!(qf < 524288.0f)) break;                                                                      \
+    u32 q = (u32)qf;                                                                                   \
+    u32 rn = RP - q * RC;                                                                              \
+    if (rn >= RC) { q++; rn -= RC; }                                                                   \
+    u64 Sn = (u64)q * SC + SP, Tn = (u64)q * TC + TP;                                                  \
+    if ((Sn | Tn) >> 30) break;                                                                        \
+    if (!exact) {                                                                                      \
+      bool ok = ODD ? (rn >= (u32)Tn && RC - rn >= (u32)Sn + SC) : (rn >= (u32)Sn && RC - rn >= (u32)Tn + TC); \
+      if (!ok) break;                                                                                  \
+    }                                                                                                  \
+    RP = rn; SP = (u32)Sn; TP = (u32)Tn;                                                               \
+    fprev = fcur;                                                                                      \
+    j++;                                                                                               \
   }
+  for (;;) {
+    swapped = false;
+    QF_HG_STEP(rp, Sp, Tp, rc, Sc, Tc, true)   // index j odd -> even
+    swapped = true;
+    QF_HG_STEP(rc, Sc, Tc, rp, Sp, Tp, false)  // index j even -> odd
+  }
+#undef QF_HG_STEP
   Mat2 m;
-  m.S0 = S0; m.T0 = T0; m.S1 = S1; m.T1 = T1; m.j = j;
+  // after an odd number of accepted steps the sets have swapped roles
+  m.S0 = swapped ? Sc : Sp; m.T0 = swapped ? Tc : Tp;
+  m.S1 = swapped ? Sp : Sc; m.T1 = swapped ? Tp : Tc;
+  m.j = j;
   return m;
 }
 
@@ -116,6 +154,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       QF_UNROLL for (int i = N - 1; i > 0; i--) { R0[i] = R0[i - 1]; R1[i] = R1[i - 1]; }
       R0[0] = 0; R1[0] = 0;
       lsh++; sb += 32;
+      QF_STAT(2);
       continue;
     }
     int b1 = fw_bits<N>(R1);
@@ -130,7 +169,9 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
     int h = 32 * (N - 1) - sh;
     u32 min_r = sb > h ? (1u << (sb - h)) : 0u;
     Mat2 M = hgcd32(ah, bh, exact, min_r);
+    QF_STAT(0);
     if (M.j == 1) {
+      QF_STAT(1);
       // one full-precision division step with a quotient of at most 30 bits
       int b0 = 32 * N - clz32(R0[N - 1]);
       if (b0 - b1 > 29) { { bail = true; QF_NOTE; } break; }
@@ -179,6 +220,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       fw_copy<NC>(C0, c0);
       fw_copy<NC>(C1, c1);
       steps += M.j - 1;
+      QF_STAT(3 + (M.j - 1 > 28 ? 28 : M.j - 1));
     }
     if (guard == 80 * N - 1) { bail = true; QF_NOTE; }
   }
