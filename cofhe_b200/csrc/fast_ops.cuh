@@ -80,6 +80,25 @@ QF_HD bool hy_compose(const Group<CAP> *G, FormR<N> &r, const FormR<N> &f1, cons
   return ok;
 }
 
+// Out-of-line composition on packed forms, for the kernels that compose in a loop (exponentiation, matmul): one copy
+// of the (large) composition body per (N, DUPL) in the whole library instead of one per call site, a kernel register
+// budget that does not have to hold the loop state across it, and an instruction footprint the SM can cache.
+// x: packed f1 in, packed result out (thread-local); t: packed f2 (any address space).
+template <int N, int CAP, bool DUPL>
+QF_HDN bool cc_compose(const Group<CAP> *G, u32 *x, const u32 *t, bool neg2, int dbits) {
+  FormR<N> f1, f2, r;
+  fr_unpack<N>(f1, x);
+  if (!DUPL) fr_unpack<N>(f2, t);
+  bool ok = fq_compose<N, DUPL>(r, f1, DUPL ? f1 : f2, neg2, dbits);
+  if (ok) fr_pack<N>(x, r);
+  else {
+    u32 tb[3 * N + 1];
+    QF_UNROLL for (int i = 0; i < 3 * N + 1; i++) tb[i] = DUPL ? 0u : t[i];
+    ok = slow_compose<N, CAP>(G, x, tb, neg2, DUPL);
+  }
+  return ok;
+}
+
 // w-bit digit number `win` (from the least significant end) of an exponent stored with `stride` words between limbs
 QF_HD u32 exp_digit(const u32 *e, int el, size_t stride, int win, int w) {
   int bit = win * w, li = bit >> 5, sh = bit & 31;
@@ -99,8 +118,9 @@ template <int N, int CAP, int W>
 QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32 *e, int el, size_t stride, int dbits, u32 *tab) {
   constexpr int TE = 3 * N + 1, NT = (1 << W) - 1;
   int win = (32 * el + W - 1) / W - 1;
+  u32 xb[TE];  // the accumulator, packed (thread-local memory: it crosses the out-of-line composition)
   fr_pack<N>(tab, f);
-  x = f;
+  fr_pack<N>(xb, f);
   bool ok = true, started = false;
   int built = 1, sq_left = 0;
   u32 d = exp_digit(e, el, stride, win, W);
@@ -112,19 +132,16 @@ QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32
     else if (d) { op = started ? 2 : 3; src = (int)d - 1; }
     else op = 0;
     // ---- execute
-    FormR<N> r;
-    if (op == 1) ok = hy_compose<N, CAP, true>(G, r, x, x, false, dbits);
-    else if (op == 2) {
-      FormR<N> t;
-      fr_unpack<N>(t, tab + src * TE);
-      ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
-    } else if (op == 3) { fr_unpack<N>(r, tab + src * TE); started = true; }
-    else r = x;
+    if (op == 1) ok = cc_compose<N, CAP, true>(G, xb, xb, false, dbits);
+    else if (op == 2) ok = cc_compose<N, CAP, false>(G, xb, tab + src * TE, false, dbits);
+    else if (op == 3) {
+      QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = tab[src * TE + i];
+      started = true;
+    }
     if (!ok) break;
-    x = r;
     // ---- advance
     if (built < NT) {
-      fr_pack<N>(tab + built * TE, x);
+      QF_UNROLL for (int i = 0; i < TE; i++) tab[built * TE + i] = xb[i];
       built++;
     } else if (sq_left > 0) {
       sq_left--;
@@ -135,6 +152,7 @@ QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32
       d = exp_digit(e, el, stride, win, W);
     }
   }
+  fr_unpack<N>(x, xb);
   return ok && started;
 }
 

@@ -64,19 +64,19 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_chain(const Group<CAP> *G, int 
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= nb) return;
   unsigned y = blockIdx.y;
-  FormR<N> x, r;
+  FormR<N> x;
+  u32 xb[TE];
   bool ok = fr_load<N>(x, ct + (size_t)y * (2 * N + nc) * nb, nc, nb, idx);
+  mm_store<N>(xb, x);
   int total = (s.nwin - 1) * s.W;
   for (int t = 0;; t++) {
     if (t % s.W == 0) {
       u32 *e = tab + mm_tab_index(s, y, idx, t / s.W, 1) * TE;
-      if (ok) mm_store<N>(e, x); else mm_mark<N>(e, 1);
+      if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) e[i] = xb[i]; }
+      else mm_mark<N>(e, 1);
     }
     if (t >= total) break;
-    if (ok) {
-      ok = hy_compose<N, CAP, true>(G, r, x, x, false, dbits);
-      x = r;
-    }
+    if (ok) ok = cc_compose<N, CAP, true>(G, xb, xb, false, dbits);
   }
 }
 
@@ -91,17 +91,15 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_fill(const Group<CAP> *G, int d
   size_t base = idx / s.nwin;
   int win = (int)(idx % s.nwin);
   u32 *e = tab + mm_tab_index(s, y, base, win, 1) * TE;
-  FormR<N> f, x, r;
+  u32 xb[TE];
   bool ok = mm_kind<N>(e) == 0;
-  fr_unpack<N>(f, e);
-  x = f;
+  QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = e[i];
   int nt = (1 << s.W) - 1;
   for (int d = 2; d <= nt; d++) {
-    if (ok) {
-      ok = d == 2 ? hy_compose<N, CAP, true>(G, r, x, x, false, dbits) : hy_compose<N, CAP, false>(G, r, x, f, false, dbits);
-      x = r;
-    }
-    if (ok) mm_store<N>(e + (size_t)(d - 1) * TE, x); else mm_mark<N>(e + (size_t)(d - 1) * TE, 1);
+    if (ok) ok = d == 2 ? cc_compose<N, CAP, true>(G, xb, xb, false, dbits) : cc_compose<N, CAP, false>(G, xb, e, false, dbits);
+    u32 *o = e + (size_t)(d - 1) * TE;
+    if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) o[i] = xb[i]; }
+    else mm_mark<N>(o, 1);
   }
 }
 
@@ -116,7 +114,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int 
   unsigned i = (unsigned)(idx / s.p), k = (unsigned)(idx % s.p);
   unsigned j0 = c * s.jper, j1 = j0 + s.jper < s.m ? j0 + s.jper : s.m;
   size_t sstride = (size_t)s.m * s.p;
-  FormR<N> x, t, r;
+  u32 xb[TE];
   bool ok = true, started = false;
   for (unsigned j = j0; j < j1 && ok; j++) {
     const u32 *e = scal + (size_t)j * s.p + k;
@@ -125,18 +123,19 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int 
       if (!d) continue;
       const u32 *te = tab + mm_tab_index(s, y, (size_t)i * s.m + j, w, (int)d) * TE;
       if (mm_kind<N>(te) != 0) { ok = false; break; }
-      fr_unpack<N>(t, te);
       if (started) {
-        ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
+        ok = cc_compose<N, CAP, false>(G, xb, te, false, dbits);
         if (!ok) break;
-        x = r;
-      } else { x = t; started = true; }
+      } else {
+        QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = te[i];
+        started = true;
+      }
     }
   }
   u32 *o = part + (((size_t)c * 2 + y) * no + idx) * TE;
   if (!ok) mm_mark<N>(o, 1);
   else if (!started) mm_mark<N>(o, 0);
-  else mm_store<N>(o, x);
+  else { QF_UNROLL for (int i = 0; i < TE; i++) o[i] = xb[i]; }
 }
 
 // 4. one thread per (y, i, k): out = init o prod_chunks part   (init == nullptr: plain product)
@@ -148,22 +147,27 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int 
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= no) return;
   unsigned y = blockIdx.y;
-  FormR<N> x, t, r;
+  FormR<N> x;
+  u32 xb[TE];
   bool started = init != nullptr;
   bool ok = started ? fr_load<N>(x, init + (size_t)y * (2 * N + nc), nc, 1, 0) : true;
+  if (started) mm_store<N>(xb, x);
   for (unsigned c = 0; c < s.chunks && ok; c++) {
     const u32 *pe = part + (((size_t)c * 2 + y) * no + idx) * TE;
     int kind = mm_kind<N>(pe);
     if (kind == 1) continue;
     if (kind == 2) { ok = false; break; }
-    fr_unpack<N>(t, pe);
-    if (started) {
-      ok = hy_compose<N, CAP, false>(G, r, x, t, false, dbits);
-      x = r;
-    } else { x = t; started = true; }
+    if (started) ok = cc_compose<N, CAP, false>(G, xb, pe, false, dbits);
+    else {
+      QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = pe[i];
+      started = true;
+    }
   }
   ok = ok && started;  // an empty product without init is the neutral form: robust path
-  if (ok) fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);
+  if (ok) {
+    fr_unpack<N>(x, xb);
+    fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);
+  }
   else bail[atomicAdd(nbail, 1)] = (u32)(y * no + idx);
 }
 
