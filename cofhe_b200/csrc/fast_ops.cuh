@@ -7,6 +7,12 @@
 #include "ops.cuh"
 #include "qf_fast.cuh"
 
+#if defined(__CUDA_ARCH__)
+#define QF_BLOCK_ALIGN() __syncthreads()
+#else
+#define QF_BLOCK_ALIGN() ((void)0)
+#endif
+
 namespace cofhe {
 
 // SoA buffer (shape s, n elements per limb row) -> registers.  Returns false when the element does not fit the
@@ -131,17 +137,19 @@ QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32
     else if (sq_left > 0) { op = started ? 1 : 0; }
     else if (d) { op = started ? 2 : 3; src = (int)d - 1; }
     else op = 0;
-    // ---- execute
+    if (!ok) op = 0;  // a failed element idles: every thread of the block runs the same number of rounds
+    // ---- execute.  The barrier keeps the warps of a block in the same region of the (large) composition code, so
+    // that the SM's instruction cache serves them together; without it they drift apart and refetch from L2.
+    QF_BLOCK_ALIGN();
     if (op == 1) ok = cc_compose<N, CAP, true>(G, xb, xb, false, dbits);
     else if (op == 2) ok = cc_compose<N, CAP, false>(G, xb, tab + src * TE, false, dbits);
     else if (op == 3) {
       QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = tab[src * TE + i];
       started = true;
     }
-    if (!ok) break;
     // ---- advance
     if (built < NT) {
-      QF_UNROLL for (int i = 0; i < TE; i++) tab[built * TE + i] = xb[i];
+      if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) tab[built * TE + i] = xb[i]; }
       built++;
     } else if (sq_left > 0) {
       sq_left--;

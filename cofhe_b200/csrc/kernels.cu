@@ -50,6 +50,7 @@ struct cofhe_b200_ctx {
 namespace {
 
 constexpr int kBlock = 128;
+constexpr int kPowBlock = 384;  // exponentiation kernel: its warps are kept aligned by block barriers
 
 #define CUDA_TRY(x)                                   \
   do {                                                \
@@ -128,21 +129,26 @@ __global__ void __launch_bounds__(kBlock) k_fast_compose(const Group<CAP> *G, in
   else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
 }
 template <int N, int CAP>
-__global__ void __launch_bounds__(kBlock) k_fast_pow(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
-                                                     int per_elem, const unsigned char *expneg, int shared_neg, u32 *bail,
-                                                     int *nbail) {
+__global__ void __launch_bounds__(kPowBlock) k_fast_pow(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in, u32 *out,
+                                                        const u32 *exp, int el, int per_elem, const unsigned char *expneg,
+                                                        int shared_neg, u32 *bail, int *nbail) {
   constexpr int W = 4;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
+  // threads past the end stay in the kernel (fr_pow contains block barriers); they redo the last element and store nothing
+  bool live = idx < n;
+  if (!live) idx = n - 1;
   size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
   u32 tab[((1 << W) - 1) * (3 * N + 1)];
   FormR<N> f, r;
   bool ok = fr_load<N>(f, in + off, nc, n, idx);
-  ok = ok && (per_elem ? fr_pow<N, CAP, W>(G, r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, CAP, W>(G, r, f, exp, el, 1, dbits, tab));
-  if (ok) {
-    if (per_elem ? (expneg && expneg[idx]) : shared_neg != 0) fr_inverse<N>(r);
-    fr_store<N>(r, out + off, nc, n, idx);
-  } else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
+  bool pok = per_elem ? fr_pow<N, CAP, W>(G, r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, CAP, W>(G, r, f, exp, el, 1, dbits, tab);
+  ok = ok && pok;
+  if (live) {
+    if (ok) {
+      if (per_elem ? (expneg && expneg[idx]) : shared_neg != 0) fr_inverse<N>(r);
+      fr_store<N>(r, out + off, nc, n, idx);
+    } else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
+  }
 }
 // op: 0 compose, 1 square, 2 pow.  Grid-stride over the bail list; clears the counter of the next call.
 template <int CAP>
@@ -267,7 +273,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
     const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
     if (op == 0) k_fast_compose<FN, FCAP, false><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
     else if (op == 1) k_fast_compose<FN, FCAP, true><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, in1, out, 0, ctx->d_bail, cnt);
-    else k_fast_pow<FN, FCAP><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_bail, cnt);
+    else k_fast_pow<FN, FCAP><<<dim3((unsigned)((n + kPowBlock - 1) / kPowBlock), ny), kPowBlock, 0, st>>>(G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_bail, cnt);
   })
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
@@ -520,7 +526,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   size_t no = n * p;
   if (!ctx->fastn || m == 0) return mm_robust_all(ctx, s, ct, scal, init, out, st);
   // split the j range so that small n*p still fills the machine
-  size_t want = (size_t)148 * 4 * kMMBlock;
+  size_t want = (size_t)148 * kMMBlock;
   size_t ch = (want + 2 * no - 1) / (2 * no);
   if (ch > m / 2) ch = m / 2;
   if (ch < 1) ch = 1;

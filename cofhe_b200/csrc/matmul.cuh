@@ -54,7 +54,7 @@ QF_HD size_t mm_tab_index(const MMShape &s, unsigned y, size_t base, int win, in
 
 
 #if defined(__CUDACC__)
-constexpr int kMMBlock = 128;
+constexpr int kMMBlock = 384;  // one block per SM at 168 registers: all resident warps share the barrier
 
 // 1. one thread per (y, base): B_w = ct^(2^(W*w)) into T[w][1]
 template <int N, int CAP>
@@ -62,7 +62,8 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_chain(const Group<CAP> *G, int 
   constexpr int TE = MMLayout<N>::TE;
   size_t nb = (size_t)s.n * s.m;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= nb) return;
+  bool live = idx < nb;  // threads past the end idle inside the loop (block barriers)
+  if (!live) idx = nb - 1;
   unsigned y = blockIdx.y;
   FormR<N> x;
   u32 xb[TE];
@@ -70,13 +71,14 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_chain(const Group<CAP> *G, int 
   mm_store<N>(xb, x);
   int total = (s.nwin - 1) * s.W;
   for (int t = 0;; t++) {
-    if (t % s.W == 0) {
+    if (live && t % s.W == 0) {
       u32 *e = tab + mm_tab_index(s, y, idx, t / s.W, 1) * TE;
       if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) e[i] = xb[i]; }
       else mm_mark<N>(e, 1);
     }
     if (t >= total) break;
-    if (ok) ok = cc_compose<N, CAP, true>(G, xb, xb, false, dbits);
+    QF_BLOCK_ALIGN();
+    if (ok && live) ok = cc_compose<N, CAP, true>(G, xb, xb, false, dbits);
   }
 }
 
@@ -86,7 +88,8 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_fill(const Group<CAP> *G, int d
   constexpr int TE = MMLayout<N>::TE;
   size_t total = (size_t)s.n * s.m * s.nwin;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
+  bool live = idx < total;
+  if (!live) idx = total - 1;
   unsigned y = blockIdx.y;
   size_t base = idx / s.nwin;
   int win = (int)(idx % s.nwin);
@@ -96,10 +99,13 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_fill(const Group<CAP> *G, int d
   QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = e[i];
   int nt = (1 << s.W) - 1;
   for (int d = 2; d <= nt; d++) {
-    if (ok) ok = d == 2 ? cc_compose<N, CAP, true>(G, xb, xb, false, dbits) : cc_compose<N, CAP, false>(G, xb, e, false, dbits);
-    u32 *o = e + (size_t)(d - 1) * TE;
-    if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) o[i] = xb[i]; }
-    else mm_mark<N>(o, 1);
+    QF_BLOCK_ALIGN();
+    if (ok && live) ok = d == 2 ? cc_compose<N, CAP, true>(G, xb, xb, false, dbits) : cc_compose<N, CAP, false>(G, xb, e, false, dbits);
+    if (live) {
+      u32 *o = e + (size_t)(d - 1) * TE;
+      if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) o[i] = xb[i]; }
+      else mm_mark<N>(o, 1);
+    }
   }
 }
 
@@ -109,33 +115,37 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int 
   constexpr int TE = MMLayout<N>::TE;
   size_t no = (size_t)s.n * s.p;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= no) return;
+  bool live = idx < no;
+  if (!live) idx = no - 1;
   unsigned y = blockIdx.y, c = blockIdx.z;
   unsigned i = (unsigned)(idx / s.p), k = (unsigned)(idx % s.p);
   unsigned j0 = c * s.jper, j1 = j0 + s.jper < s.m ? j0 + s.jper : s.m;
   size_t sstride = (size_t)s.m * s.p;
   u32 xb[TE];
   bool ok = true, started = false;
-  for (unsigned j = j0; j < j1 && ok; j++) {
+  // the trip counts are the same for every thread of the block (block barriers inside)
+  for (unsigned j = j0; j < j1; j++) {
     const u32 *e = scal + (size_t)j * s.p + k;
     for (int w = 0; w < s.nwin; w++) {
-      u32 d = exp_digit(e, s.el, sstride, w, s.W);
-      if (!d) continue;
-      const u32 *te = tab + mm_tab_index(s, y, (size_t)i * s.m + j, w, (int)d) * TE;
-      if (mm_kind<N>(te) != 0) { ok = false; break; }
-      if (started) {
-        ok = cc_compose<N, CAP, false>(G, xb, te, false, dbits);
-        if (!ok) break;
-      } else {
-        QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = te[i];
-        started = true;
+      u32 d = (ok && live) ? exp_digit(e, s.el, sstride, w, s.W) : 0u;
+      const u32 *te = tab + mm_tab_index(s, y, (size_t)i * s.m + j, w, d ? (int)d : 1) * TE;
+      if (d && mm_kind<N>(te) != 0) { ok = false; d = 0; }
+      QF_BLOCK_ALIGN();
+      if (d) {
+        if (started) ok = cc_compose<N, CAP, false>(G, xb, te, false, dbits);
+        else {
+          QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = te[i];
+          started = true;
+        }
       }
     }
   }
-  u32 *o = part + (((size_t)c * 2 + y) * no + idx) * TE;
-  if (!ok) mm_mark<N>(o, 1);
-  else if (!started) mm_mark<N>(o, 0);
-  else { QF_UNROLL for (int i = 0; i < TE; i++) o[i] = xb[i]; }
+  if (live) {
+    u32 *o = part + (((size_t)c * 2 + y) * no + idx) * TE;
+    if (!ok) mm_mark<N>(o, 1);
+    else if (!started) mm_mark<N>(o, 0);
+    else { QF_UNROLL for (int i = 0; i < TE; i++) o[i] = xb[i]; }
+  }
 }
 
 // 4. one thread per (y, i, k): out = init o prod_chunks part   (init == nullptr: plain product)
@@ -145,30 +155,34 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int 
   constexpr int TE = MMLayout<N>::TE;
   size_t no = (size_t)s.n * s.p;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= no) return;
+  bool live = idx < no;
+  if (!live) idx = no - 1;
   unsigned y = blockIdx.y;
   FormR<N> x;
   u32 xb[TE];
   bool started = init != nullptr;
   bool ok = started ? fr_load<N>(x, init + (size_t)y * (2 * N + nc), nc, 1, 0) : true;
   if (started) mm_store<N>(xb, x);
-  for (unsigned c = 0; c < s.chunks && ok; c++) {
+  for (unsigned c = 0; c < s.chunks; c++) {
     const u32 *pe = part + (((size_t)c * 2 + y) * no + idx) * TE;
-    int kind = mm_kind<N>(pe);
-    if (kind == 1) continue;
-    if (kind == 2) { ok = false; break; }
-    if (started) ok = cc_compose<N, CAP, false>(G, xb, pe, false, dbits);
-    else {
-      QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = pe[i];
-      started = true;
+    int kind = (ok && live) ? mm_kind<N>(pe) : 1;
+    if (kind == 2) ok = false;
+    QF_BLOCK_ALIGN();
+    if (kind == 0) {
+      if (started) ok = cc_compose<N, CAP, false>(G, xb, pe, false, dbits);
+      else {
+        QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = pe[i];
+        started = true;
+      }
     }
   }
   ok = ok && started;  // an empty product without init is the neutral form: robust path
-  if (ok) {
-    fr_unpack<N>(x, xb);
-    fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);
+  if (live) {
+    if (ok) {
+      fr_unpack<N>(x, xb);
+      fr_store<N>(x, out + (size_t)y * (2 * N + nc) * no, nc, no, idx);
+    } else bail[atomicAdd(nbail, 1)] = (u32)(y * no + idx);
   }
-  else bail[atomicAdd(nbail, 1)] = (u32)(y * no + idx);
 }
 
 // robust path: all outputs (list == nullptr) or the listed ones; clears the next call's counter
