@@ -29,7 +29,8 @@ def stale():
 def build(force=False, verbose=False):
     if not force and not stale():
         return LIB
-    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
+    extra = os.environ.get("COFHE_B200_NVCC_EXTRA", "").split()  # e.g. -DCOFHE_B200_DEV_N7 while iterating
+    cmd = [NVCC] + FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
     subprocess.check_call(cmd)
     return LIB
 

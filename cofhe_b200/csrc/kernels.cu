@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <new>
+#include <utility>
 
 #include "cofhe_b200.h"
 #include "fast_ops.cuh"
@@ -17,6 +18,7 @@ using namespace cofhe;
 
 struct cofhe_b200_ctx {
   int device;
+  int sms;            // multiprocessors of the device (grid sizing)
   int cap;            // capacity class of the generic integer layer
   u32 na, nc, nd, dbits;
   u32 h_absd[2 * 216];  // |Delta| (host copy)
@@ -29,6 +31,9 @@ struct cofhe_b200_ctx {
   int *d_nbail;       // two counters used alternately (the sparse kernel of call k clears the one of call k+1)
   size_t bail_cap;
   int flip;
+  // pipeline lanes of the _host entry points: own stream and own bail list, so that the chunks of one call overlap
+  // (H2D of chunk i+1 | kernels of chunk i | D2H of chunk i-1)
+  struct Lane { cudaStream_t st; u32 *d_bail; int *d_nbail; size_t bail_cap; int flip; } lane[4];
   // staging of the _host entry points (grown on demand, reused across calls)
   u32 *d_stage;
   size_t stage_bytes;
@@ -170,6 +175,14 @@ __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, s
 }
 
 // (limbs of a and b, capacity class of the robust layer) pairs that exist: cap_for(nd) with nd ~ 2*na - 1
+#ifdef COFHE_B200_DEV_N7  /* development builds: only the T0 instantiation (compiles in a quarter of the time) */
+#define FAST_DISPATCH(fn, ...)                                                        \
+  switch (fn) {                                                                       \
+    case 7: { constexpr int FN = 7, FCAP = 32; __VA_ARGS__; } break;                  \
+    default: return COFHE_B200_EINVAL;                                                \
+  }
+#define FAST_HAVE(na) ((na) == 7)
+#else
 #define FAST_DISPATCH(fn, ...)                                                        \
   switch (fn) {                                                                       \
     case 2: { constexpr int FN = 2, FCAP = 32; __VA_ARGS__; } break;                  \
@@ -178,9 +191,11 @@ __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, s
     case 11: { constexpr int FN = 11, FCAP = 48; __VA_ARGS__; } break;                \
     default: return COFHE_B200_EINVAL;                                                \
   }
+#define FAST_HAVE(na) ((na) == 2 || (na) == 4 || (na) == 7 || (na) == 11)
+#endif
 int fast_cap(int fn) { return fn == 11 ? 48 : 32; }
 int fast_n_for(u32 na, int cap) {
-  bool have = (na == 2 || na == 4 || na == 7 || na == 11) && fast_cap((int)na) == cap;
+  bool have = FAST_HAVE(na) && fast_cap((int)na) == cap;
   return have && !getenv("COFHE_B200_NO_FAST") ? (int)na : 0;
 }
 
@@ -374,6 +389,8 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   cofhe_b200_ctx *ctx = new (std::nothrow) cofhe_b200_ctx();
   if (!ctx) return COFHE_B200_ENOMEM;
   ctx->device = device;
+  ctx->sms = 0;
+  if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); ctx->sms = 0; }
   ctx->cap = cap;
   ctx->nd = n;
   int dbits = bn_bits(abs_delta, (int)n);
@@ -384,6 +401,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   for (u32 i = 0; i < n; i++) ctx->h_absd[i] = abs_delta[i];
   ctx->fastn = fast_n_for(ctx->na, cap);
   ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
+  memset(ctx->lane, 0, sizeof(ctx->lane));
   ctx->d_stage = nullptr; ctx->stage_bytes = 0;
   ctx->d_work = nullptr; ctx->work_bytes = 0;
   ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
@@ -432,6 +450,11 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
   if (ctx->d_fb_tab) cudaFree(ctx->d_fb_tab);
   if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
+  for (auto &L : ctx->lane) {
+    if (L.d_bail) cudaFree(L.d_bail);
+    if (L.d_nbail) cudaFree(L.d_nbail);
+    if (L.st) cudaStreamDestroy(L.st);
+  }
   delete ctx;
 }
 
@@ -526,10 +549,23 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   size_t no = n * p;
   if (!ctx->fastn || m == 0) return mm_robust_all(ctx, s, ct, scal, init, out, st);
   // split the j range so that small n*p still fills the machine
-  size_t want = (size_t)148 * kMMBlock;
-  size_t ch = (want + 2 * no - 1) / (2 * no);
-  if (ch > m / 2) ch = m / 2;
-  if (ch < 1) ch = 1;
+  // k_mm_accum runs one kMMBlock-thread block per SM (register budget), all blocks of equal length: pick the chunk
+  // count whose grid is closest to a whole number of waves (rounds * columns-per-chunk = the time of the launch); each
+  // extra chunk costs one more composition per output in k_mm_final
+  size_t ch = 1;
+  {
+    const size_t sms = (size_t)(ctx->sms > 0 ? ctx->sms : 148);
+    const size_t bpc = 2 * ((no + kMMBlock - 1) / kMMBlock);  // blocks per chunk
+    size_t chmax = m / 2 < 1 ? 1 : m / 2;
+    if (chmax > 64) chmax = 64;
+    double best = 0;
+    for (size_t c = 1; c <= chmax; c++) {
+      size_t jper = (m + c - 1) / c, cc = (m + jper - 1) / jper;
+      size_t rounds = (bpc * cc + sms - 1) / sms;
+      double cost = (double)rounds * (double)jper * (double)(s.nwin) + (double)cc;
+      if (c == 1 || cost < best) { best = cost; ch = c; }
+    }
+  }
   if (const char *c = getenv("COFHE_B200_MM_CHUNKS")) { int v = atoi(c); if (v >= 1 && (size_t)v <= m) ch = (size_t)v; }
   s.jper = (unsigned)((m + ch - 1) / ch);
   s.chunks = (unsigned)((m + s.jper - 1) / s.jper);
@@ -782,29 +818,79 @@ int cofhe_b200_device_count(void) {
   return c;
 }
 
+}  // extern "C"
+
+// Lazily created pipeline lane (stream + bail counters).
+static int lane_ready(cofhe_b200_ctx *ctx, int l) {
+  cofhe_b200_ctx::Lane &L = ctx->lane[l];
+  if (L.st) return COFHE_B200_OK;
+  if (cudaStreamCreateWithFlags(&L.st, cudaStreamNonBlocking) != cudaSuccess) { L.st = nullptr; return COFHE_B200_ECUDA; }
+  if (cudaMalloc(&L.d_nbail, 2 * sizeof(int)) != cudaSuccess || cudaMemset(L.d_nbail, 0, 2 * sizeof(int)) != cudaSuccess)
+    return COFHE_B200_ENOMEM;
+  return COFHE_B200_OK;
+}
+// run `fn` with the lane's bail state installed in the context (launch_op reads it from there)
+template <class F>
+static int with_lane(cofhe_b200_ctx *ctx, int l, F fn) {
+  cofhe_b200_ctx::Lane &L = ctx->lane[l];
+  std::swap(ctx->d_bail, L.d_bail); std::swap(ctx->d_nbail, L.d_nbail);
+  std::swap(ctx->bail_cap, L.bail_cap); std::swap(ctx->flip, L.flip);
+  int rc = fn(L.st);
+  std::swap(ctx->d_bail, L.d_bail); std::swap(ctx->d_nbail, L.d_nbail);
+  std::swap(ctx->bail_cap, L.bail_cap); std::swap(ctx->flip, L.flip);
+  return rc;
+}
+
+extern "C" {
+
+/* Host-pointer ciphertext add: the batch is cut into element ranges that travel through up to 4 lanes, so the upload
+ * of one range overlaps the kernels of the previous one and the download of the one before.  Host buffers are the
+ * same SoA rows as everywhere ([rows][n]); a range is a strided 2-D copy into a dense [rows][cn] staging batch. */
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out) {
   if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
-  size_t bytes = (size_t)2 * (2 * ctx->na + ctx->nc) * n * sizeof(u32);
+  const size_t rows = (size_t)2 * (2 * ctx->na + ctx->nc);
+  size_t bytes = rows * n * sizeof(u32);
   int rc = COFHE_B200_OK;
   if (ctx->stage_bytes < 3 * bytes) {
+    cudaDeviceSynchronize();
     if (ctx->d_stage) cudaFree(ctx->d_stage);
     ctx->d_stage = nullptr; ctx->stage_bytes = 0;
-    if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) rc = COFHE_B200_ENOMEM;
-    else ctx->stage_bytes = 3 * bytes;
+    if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+    ctx->stage_bytes = 3 * bytes;
   }
-  u32 *d1 = ctx->d_stage, *d2 = d1 + bytes / 4, *d3 = d2 + bytes / 4;
-  if (rc == COFHE_B200_OK && (cudaMemcpyAsync(d1, ct1, bytes, cudaMemcpyHostToDevice, ctx->xfer) != cudaSuccess ||
-                              cudaMemcpyAsync(d2, ct2, bytes, cudaMemcpyHostToDevice, ctx->xfer) != cudaSuccess))
-    rc = COFHE_B200_ECUDA;
-  if (rc == COFHE_B200_OK) rc = cofhe_b200_add_ciphertexts(ctx, n, d1, d2, d3, ctx->xfer);
-  if (rc == COFHE_B200_OK && cudaMemcpyAsync(out, d3, bytes, cudaMemcpyDeviceToHost, ctx->xfer) != cudaSuccess)
-    rc = COFHE_B200_ECUDA;
-  if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->xfer);
-  else cudaStreamSynchronize(ctx->xfer);
+  size_t chunks = 4;
+  if (const char *c = getenv("COFHE_B200_HOST_CHUNKS")) { int v = atoi(c); if (v >= 1 && v <= 64) chunks = (size_t)v; }
+  if (chunks > (n + 1023) / 1024) chunks = (n + 1023) / 1024;  // ranges below ~1k elements only add launch overhead
+  size_t per = (((n + chunks - 1) / chunks) + 31) & ~(size_t)31;
+  int used = 0;
+  size_t c = 0;
+  for (size_t e0 = 0; e0 < n && rc == COFHE_B200_OK; e0 += per, c++) {
+    size_t cn = n - e0 < per ? n - e0 : per;
+    int l = (int)(c % 4);
+    rc = lane_ready(ctx, l);
+    if (rc != COFHE_B200_OK) break;
+    if (l + 1 > used) used = l + 1;
+    u32 *d1 = ctx->d_stage + 3 * rows * e0, *d2 = d1 + rows * cn, *d3 = d2 + rows * cn;
+    cudaStream_t st = ctx->lane[l].st;
+    if (cudaMemcpy2DAsync(d1, cn * 4, ct1 + e0, n * 4, cn * 4, rows, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaMemcpy2DAsync(d2, cn * 4, ct2 + e0, n * 4, cn * 4, rows, cudaMemcpyHostToDevice, st) != cudaSuccess) {
+      rc = COFHE_B200_ECUDA;
+      break;
+    }
+    rc = with_lane(ctx, l, [&](cudaStream_t s2) { return cofhe_b200_add_ciphertexts(ctx, cn, d1, d2, d3, s2); });
+    if (rc == COFHE_B200_OK &&
+        cudaMemcpy2DAsync(out + e0, n * 4, d3, cn * 4, cn * 4, rows, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+      rc = COFHE_B200_ECUDA;
+  }
+  for (int l = 0; l < used; l++) {
+    if (l + 1 < used) { if (cudaStreamSynchronize(ctx->lane[l].st) != cudaSuccess && rc == COFHE_B200_OK) rc = COFHE_B200_ECUDA; }
+    else if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->lane[l].st);  // last lane: sync + sticky element status
+    else cudaStreamSynchronize(ctx->lane[l].st);
+  }
   return rc;
 }
 
