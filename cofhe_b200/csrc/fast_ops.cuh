@@ -73,9 +73,9 @@ QF_HDN bool slow_compose(const Group<CAP> *G, u32 *x, const u32 *t, bool neg2, b
   z_store(e, f1.a, x, N, 1, false); z_store(e, f1.b, x + N, N, 1, true); z_store(e, f1.c, x + 2 * N, N + 1, 1, false);
   return e.code == 0;
 }
-template <int N, int CAP, bool DUPL>
+template <int N, int CAP, bool DUPL, bool SYNC = false>
 QF_HD bool hy_compose(const Group<CAP> *G, FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool neg2, int dbits) {
-  bool ok = fq_compose<N, DUPL>(r, f1, f2, neg2, dbits);
+  bool ok = fq_compose<N, DUPL, SYNC>(r, f1, f2, neg2, dbits);
   if (!ok) {
     u32 xb[3 * N + 1], tb[3 * N + 1];
     fr_pack<N>(xb, f1);

@@ -124,13 +124,25 @@ template <int N, int CAP, bool DUPL>
 __global__ void __launch_bounds__(kBlock) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
                                                          int neg2, u32 *bail, int *nbail) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
+  // threads past the end stay in the kernel (the composition contains block barriers); they redo the last element
+  bool live = idx < n;
+  if (!live) idx = n - 1;
   size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
   FormR<N> f1, f2, r;
   bool ok = fr_load<N>(f1, in1 + off, nc, n, idx);
   if (!DUPL) ok = fr_load<N>(f2, in2 + off, nc, n, idx) && ok;
-  ok = ok && hy_compose<N, CAP, DUPL>(G, r, f1, DUPL ? f1 : f2, neg2 != 0, dbits);
-  if (ok) fr_store<N>(r, out + off, nc, n, idx);
+  // an element that does not fit the register shape still walks through the composition (on its truncated limbs: every
+  // loop in there is bounded) so that the block's barriers see all threads; its result is discarded
+  bool cok = fq_compose<N, DUPL, true>(r, f1, DUPL ? f1 : f2, neg2 != 0, dbits);
+  if (!live) return;
+  if (ok && !cok) {  // declined by the register path: one robust composition for this lane
+    u32 xb[3 * N + 1], tb[3 * N + 1];
+    fr_pack<N>(xb, f1);
+    fr_pack<N>(tb, DUPL ? f1 : f2);
+    cok = slow_compose<N, CAP>(G, xb, tb, neg2 != 0, DUPL);
+    fr_unpack<N>(r, xb);
+  }
+  if (ok && cok) fr_store<N>(r, out + off, nc, n, idx);
   else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
 }
 template <int N, int CAP>

@@ -79,14 +79,23 @@ QF_HD float rcp_approx(float x) {
 //
 // This loop is where a composition spends most of its instructions, so it is written for the SM: the quotient comes
 // from one reciprocal (float estimate biased low by 2^-20: for q < 2^19 it is q or q-1, one conditional fix-up), the
-// float of the divisor is reused as the next dividend, and two Euclid steps are unrolled so that the (previous,
-// current) pairs swap roles instead of moving through registers and the parity of Jebelean's test is static.
-// A quotient of 2^19 or more ends the run; the caller then takes one full-precision step.
-QF_HD Mat2 hgcd32(u32 ah, u32 bh, bool exact, u32 min_r) {
+// float of the divisor is reused (pre-scaled, off the dependency chain) as the next dividend, and two Euclid steps are
+// unrolled so that the (previous, current) pairs swap roles instead of moving through registers and the parity of
+// Jebelean's test is static.  A quotient of 2^19 or more ends the run; the caller then takes one full-precision step.
+//
+// EXACT == false (the leading parts are truncations): every accepted step passes Jebelean's test, and the cofactors
+// need no overflow check at all -- for the Euclidean sequence of (ah, bh), T_{j+1} r_j + T_j r_{j+1} = ah (same for S
+// with bh <= ah), so with the divisor r_j >= 2 the new cofactors are below 2^31 (32-bit arithmetic cannot wrap), and
+// an accepted step has T_{j+1} <= r_{j+1} < r_j, hence T_{j+1}^2 < 2^32: accepted cofactors are below 2^16.
+// EXACT == true (the operands fit the leading limb: last rounds of a full gcd): no test, cofactors may grow up to
+// ah / r_j, so they are formed in 64 bits and the run stops before one reaches 2^30.
+template <bool EXACT>
+QF_HD Mat2 hgcd32(u32 ah, u32 bh, u32 min_r) {
   u32 rp = ah, rc = bh;
   u32 Sp = 1, Tp = 0, Sc = 0, Tc = 1;
-  const u32 lim = min_r ? min_r : 1u;
-  float fprev = (float)rp;
+  const u32 lim = EXACT ? (min_r ? min_r : 1u) : (min_r > 2u ? min_r : 2u);
+  const float kLow = 0.99999905f;
+  float fprev = (float)rp * kLow;  // dividend estimate, already biased low
   int j = 1;
   bool swapped = false;
   // one Euclid step: (P*) previous, (C*) current; on success the new remainder and cofactors replace the P set
@@ -94,19 +103,23 @@ QF_HD Mat2 hgcd32(u32 ah, u32 bh, bool exact, u32 min_r) {
   {                                                                                                    \
     if (RC < lim) break;                                                                               \
     float fcur = (float)RC;                                                                            \
-    float qf = fprev * rcp_approx(fcur) * 0.99999905f;                                                 \
+    float qf = fprev * rcp_approx(fcur);                                                               \
     if (!(qf < 524288.0f)) break;                                                                      \
     u32 q = (u32)qf;                                                                                   \
     u32 rn = RP - q * RC;                                                                              \
     if (rn >= RC) { q++; rn -= RC; }                                                                   \
-    u64 Sn = (u64)q * SC + SP, Tn = (u64)q * TC + TP;                                                  \
-    if ((Sn | Tn) >> 30) break;                                                                        \
-    if (!exact) {                                                                                      \
-      bool ok = ODD ? (rn >= (u32)Tn && RC - rn >= (u32)Sn + SC) : (rn >= (u32)Sn && RC - rn >= (u32)Tn + TC); \
+    u32 Sn, Tn;                                                                                        \
+    if (EXACT) {                                                                                       \
+      u64 S64 = (u64)q * SC + SP, T64 = (u64)q * TC + TP;                                              \
+      if ((S64 | T64) >> 30) break;                                                                    \
+      Sn = (u32)S64; Tn = (u32)T64;                                                                    \
+    } else {                                                                                           \
+      Sn = q * SC + SP; Tn = q * TC + TP;                                                              \
+      bool ok = ODD ? (rn >= Tn && RC - rn >= Sn + SC) : (rn >= Sn && RC - rn >= Tn + TC);             \
       if (!ok) break;                                                                                  \
     }                                                                                                  \
-    RP = rn; SP = (u32)Sn; TP = (u32)Tn;                                                               \
-    fprev = fcur;                                                                                      \
+    RP = rn; SP = Sn; TP = Tn;                                                                         \
+    fprev = fcur * kLow;                                                                               \
     j++;                                                                                               \
   }
   for (;;) {
@@ -125,27 +138,35 @@ QF_HD Mat2 hgcd32(u32 ah, u32 bh, bool exact, u32 min_r) {
 }
 
 // r = |x*A - y*B| where the sign is known: neg == true means the combination is <= 0.  x, y < 2^30.
+// Both products run as carry chains of 32x32+64 multiply-adds (one IMAD.WIDE per limb), then one borrow chain.
 template <int N>
 QF_HD void fw_lin_sub(u32 *r, u32 x, const u32 *A, u32 y, const u32 *B, bool neg) {
-  i64 c = 0;
+  u32 U[N], V[N];
+  u64 cu = 0, cv = 0;
   QF_UNROLL for (int i = 0; i < N; i++) {
-    i64 d = (i64)((u64)x * A[i]) - (i64)((u64)y * B[i]) + c;
-    r[i] = (u32)d;
-    c = d >> 32;
+    cu = (u64)x * A[i] + (cu >> 32);
+    cv = (u64)y * B[i] + (cv >> 32);
+    U[i] = (u32)cu;
+    V[i] = (u32)cv;
   }
-  fw_cneg<N>(r, r, neg);
+  // the limbs above N cancel (|x*A - y*B| < 2^(32N)); subtract in the order that gives the magnitude
+  u32 bo = 0;
+  QF_UNROLL for (int i = 0; i < N; i++) {
+    u32 p = neg ? V[i] : U[i], q = neg ? U[i] : V[i];
+    u64 d = (u64)p - q - bo;
+    r[i] = (u32)d;
+    bo = (u32)(d >> 63);
+  }
 }
-// r = x*A + y*B, returns the carry-out limb
+// r = x*A + y*B, returns the carry-out limb.  x, y < 2^30 (each partial sum fits 64 bits)
 template <int N>
 QF_HD u32 fw_lin_add(u32 *r, u32 x, const u32 *A, u32 y, const u32 *B) {
   u64 c = 0;
   QF_UNROLL for (int i = 0; i < N; i++) {
-    u64 p = (u64)x * A[i] + (c & 0xffffffffu);
-    u64 q = (u64)y * B[i] + (u32)p;
-    r[i] = (u32)q;
-    c = (c >> 32) + (p >> 32) + (q >> 32);
+    c = (u64)x * A[i] + (u64)y * B[i] + (c >> 32);
+    r[i] = (u32)c;
   }
-  return (u32)c | (u32)(c >> 32);
+  return (u32)(c >> 32);
 }
 
 // Half-extended Euclid on fixed-width magnitudes, same contract as z_hxgcd (lehmer.cuh): in (R0 >= R1, C0, C1),
@@ -187,7 +208,8 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       }
       int h = 32 * (N - 1) - sh;
       u32 min_r = sb > h ? (1u << (sb - h)) : 0u;
-      M = hgcd32(ah, bh, exact, min_r);
+      if (exact) M = hgcd32<true>(ah, bh, min_r);
+      else M = hgcd32<false>(ah, bh, min_r);
       QF_STAT(0);
     }
     QF_CONVERGE(lanes);
@@ -357,14 +379,25 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
 
 // r = f1 o f2 (neg2: f1 o f2^-1; DUPL: f1^2, f2 ignored).  Returns false (bail) when the element must take the
 // robust path; r is unspecified then.  dbits = bit length of |Delta|.
-template <int N, bool DUPL>
+//
+// The body is a sequence of phases; a phase that declines returns false and the later ones are skipped.  With SYNC the
+// warps of a block meet at a block barrier between phases (every thread of the block must then call this function,
+// whatever its data): the two Euclid loops are small and cache-resident, but the straight-line multi-limb code between
+// them is ~250 KB of SASS that each warp executes once per composition, and the SM's instruction cache serves it to
+// all resident warps together only while they stay in step.
+#if defined(__CUDA_ARCH__)
+#define QF_PHASE() do { if (SYNC) __syncthreads(); } while (0)
+#else
+#define QF_PHASE() ((void)0)
+#endif
+template <int N, bool DUPL, bool SYNC = false>
 QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool neg2, int dbits) {
   constexpr int W = N + 1;
   constexpr int M = (N + 1) / 2 + 1;  // half width of the post-Euclid quantities
   // numerators carry extra limbs for the 2-adic shift: a1 = 2^tz * odd with tz < 32*(L-M).  In these non-maximal
   // orders (Delta = -2^(2k+5) N) P(2^j | a) decays only like 2^(-j/2), so tz >= 32 does occur (~2^-17 per step).
   constexpr int L = (M + 2 <= W) ? M + 2 : M + 1;
-  bool bail = false;
+  bool bail = false, ok = true;
 
   // ---- operands, larger `a` first
   u32 a1[N], a2[N], b1[W], b2[W], c2[W];
@@ -384,17 +417,38 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
   fw_shr_bits<W>(s, s, 1, s[W - 1] >> 31);
   fw_sub<W>(m, b2, s);
 
-  // ---- F = gcd(a1, a2) with v*a2 == F (mod a1)   [DUPL: F = a, G = gcd(a, b)]
+  // ---- phase 1: F = gcd(a1, a2) with v*a2 == F (mod a1)   [DUPL: F = a, G = gcd(a, b) = . + y*|b|]
   u32 By[N], Bx[N];
   u32 G = 1;
-  if (!DUPL) {
-    u32 R0[N], R1[N], C0[N], C1[N];
-    fw_copy<N>(R0, a1); fw_copy<N>(R1, a2); fw_zero<N>(C0); fw_zero<N>(C1); C1[0] = 1;
-    int st = fw_hxgcd<N, N>(R0, R1, C0, C1, 0, bail);
+  u32 R0[N], Cv[N];  // gcd and cofactor of the first Euclid
+  int st1 = 0;
+  u32 bneg = b1[W - 1] >> 31;
+  ok = [&]() -> bool {
+    u32 R1[N], C1[N];
+    if (!DUPL) {
+      fw_copy<N>(R0, a1); fw_copy<N>(R1, a2);
+    } else {
+      u32 bm[W];
+      fw_cneg<W>(bm, b1, bneg);
+      if (bm[N] != 0) QF_BAIL;
+      if (fw_is_zero<N>(bm)) QF_BAIL;  // b == 0 (ambiguous forms): robust path
+      fw_copy<N>(R0, a1); fw_copy<N>(R1, bm);
+      // |b| <= a for reduced input; an unreduced input may have |b| > a: robust path
+      if (fw_lt<N>(R0, R1)) QF_BAIL;
+    }
+    fw_zero<N>(Cv); fw_zero<N>(C1); C1[0] = 1;
+    st1 = fw_hxgcd<N, N>(R0, R1, Cv, C1, 0, bail);
     if (bail) QF_BAIL;
-    if (!fw_high_zero<N, 1>(R0)) QF_BAIL;  // gcd(a1,a2) >= 2^32: robust path
+    if (!fw_high_zero<N, 1>(R0)) QF_BAIL;  // gcd >= 2^32: robust path
+    return true;
+  }();
+  QF_PHASE();
+
+  // ---- phase 2: By = a1/G and Bx
+  if (ok) ok = [&]() -> bool {
+  if (!DUPL) {
     u32 F = R0[0];
-    bool vneg = (st & 1) == 0;  // sign(C_st) = (-1)^(st+1)
+    bool vneg = (st1 & 1) == 0;  // sign(C_st) = (-1)^(st+1)
     // t = |v| * |m| mod By, with By = a1/G
     u32 mneg = m[W - 1] >> 31;
     u32 mm[W];
@@ -444,7 +498,7 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     if (G == 1) fw_copy<N>(By, a1); else fw_divexact1<N>(By, a1, G);
     // t = (|v|*|m|) mod By
     u32 prod[2 * N], t[N];
-    fw_mul<N, N>(prod, C0, mm);
+    fw_mul<N, N>(prod, Cv, mm);
     if (!fw_mod<2 * N, N>(t, prod, By)) QF_BAIL;
     bool tneg = (vneg != (mneg != 0));
     if (F != 1) {
@@ -478,54 +532,44 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     fw_copy<N>(Bx, t);
   } else {
     // NUDUPL: s = b, m = 0, F = a.  G = gcd(a, b) = . + y*b ; Bx = y*c mod (a/G)
-    u32 bneg = b1[W - 1] >> 31;
-    u32 bm[W];
-    fw_cneg<W>(bm, b1, bneg);
-    if (bm[N] != 0) QF_BAIL;
-    bool yneg = false;
-    u32 ym[N];
-    fw_zero<N>(ym);
-    if (fw_is_zero<N>(bm)) {
-      // b == 0: G = a; By = 1; Bx = 0
-      QF_BAIL;  // rare (ambiguous forms): robust path
-    }
-    {
-      u32 R0[N], R1[N], C0[N], C1[N];
-      fw_copy<N>(R0, a1); fw_copy<N>(R1, bm);
-      // |b| <= a for reduced input; an unreduced input may have |b| > a: robust path
-      if (fw_lt<N>(R0, R1)) QF_BAIL;
-      fw_zero<N>(C0); fw_zero<N>(C1); C1[0] = 1;
-      int st = fw_hxgcd<N, N>(R0, R1, C0, C1, 0, bail);
-      if (bail) QF_BAIL;
-      if (!fw_high_zero<N, 1>(R0)) QF_BAIL;
-      G = R0[0];
-      fw_copy<N>(ym, C0);
-      yneg = ((st & 1) == 0) != (bneg != 0);  // y*|b| == G  ->  y*b == G needs the sign of b
-    }
+    G = R0[0];
+    bool yneg = ((st1 & 1) == 0) != (bneg != 0);  // y*|b| == G  ->  y*b == G needs the sign of b
     if (G == 1) fw_copy<N>(By, a1); else fw_divexact1<N>(By, a1, G);
     // Bx = y * c mod By
     u32 cr[N];
     if (!fw_mod<W, N>(cr, c2, By)) QF_BAIL;
     u32 prod[2 * N], t[N];
-    fw_mul<N, N>(prod, ym, cr);
+    fw_mul<N, N>(prod, Cv, cr);
     if (!fw_mod<2 * N, N>(t, prod, By)) QF_BAIL;
     if (yneg && !fw_is_zero<N>(t)) fw_sub<N>(t, By, t);
     fw_copy<N>(Bx, t);
   }
+  return true;
+  }();
+  QF_PHASE();
 
-  // ---- partial Euclid on (By, Bx) down to about sqrt(a1/a2) * |D|^(1/4)
+  // ---- phase 3: partial Euclid on (By, Bx) down to about sqrt(a1/a2) * |D|^(1/4)
   int ba1 = fw_bits<N>(a1), ba2 = fw_bits<N>(a2);
-  int stop = (ba1 - ba2) / 2 + dbits / 4;
-  if (stop < 1) stop = 1;
   u32 C0[M], C1[M];
-  fw_zero<M>(C0); fw_zero<M>(C1); C1[0] = 1;
-  int st = fw_hxgcd<N, M>(By, Bx, C0, C1, stop, bail);  // (By, Bx) <- (R_{i-1}, R_i)
-  if (bail) QF_BAIL;
-  int idx = 1 + st;
+  int st = 0;
+  if (ok) {
+    int stop = (ba1 - ba2) / 2 + dbits / 4;
+    if (stop < 1) stop = 1;
+    fw_zero<M>(C0); fw_zero<M>(C1); C1[0] = 1;
+    st = fw_hxgcd<N, M>(By, Bx, C0, C1, stop, bail);  // (By, Bx) <- (R_{i-1}, R_i)
+    if (bail) { QF_NOTE; ok = false; }
+  }
+  QF_PHASE();
+
+  // ---- phase 4: the C and D columns from the orthogonality relations
   // rows: x' = (Ax, Bxp) with Ax = G*C0 >= 0, Bxp = (-1)^idx R_{i-1};  y' = (Ay, Byp) with Ay = (-1)^(idx+1) G*C1, Byp = R_i
+  const int idx = 1 + st;
+  const bool ay_neg = (idx & 1) == 0, rx_neg = (idx & 1) != 0;
+  u32 Ax[M], Ay[M], Rx[M], Ry[M];
+  u32 Cx[M], Cy[M], Dx[M], Dy[M];
+  if (ok) ok = [&]() -> bool {
   if (!fw_high_zero<N, M>(By) || !fw_high_zero<N, M>(Bx)) QF_BAIL;
   if ((By[M - 1] | Bx[M - 1]) >> 30) QF_BAIL;
-  u32 Ax[M], Ay[M], Rx[M], Ry[M];
   fw_copy<M>(Rx, By);
   fw_copy<M>(Ry, Bx);
   {
@@ -533,7 +577,6 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     fw_mul1<M>(t, C0, G); if (t[M] | (t[M - 1] >> 30)) QF_BAIL; fw_copy<M>(Ax, t);
     fw_mul1<M>(t, C1, G); if (t[M] | (t[M - 1] >> 30)) QF_BAIL; fw_copy<M>(Ay, t);
   }
-  bool ay_neg = (idx & 1) == 0, rx_neg = (idx & 1) != 0;
   // size guards for the quotients (they must fit M limbs signed):
   //   |C| <= (a2*|B| + |m|*|A|)/a1 ,  |D| <= (|s|*|B| + c2*|A|)/a1
   {
@@ -561,7 +604,6 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
   }
   u32 a1inv = inv32(a1o[0]);
   // quotient Q = (p*B - q*A)/a1 for (p, q) = (a2, m) -> C and (s, c2) -> D; B, A given as magnitude + sign
-  u32 Cx[M], Cy[M], Dx[M], Dy[M];
   {
     u32 a2l[L], ml[L], sl[L], c2l[L];
     QF_UNROLL for (int i = 0; i < L; i++) {
@@ -571,7 +613,6 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
       c2l[i] = i < W ? c2[i] : 0;
     }
     static_assert(L <= W, "half width must not exceed the operand width");
-    // helper lambda-free: compute into q[M]
 #define QF_ORTHO(QOUT, PL, QL, BMAG, BNEG, AMAG, ANEG)                         \
     {                                                                          \
       u32 n1[L], n2[L];                                                        \
@@ -587,9 +628,9 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
       fw_copy<M>(nm, sh_);                                                     \
       fw_divexact_2adic<M>(QOUT, nm, a1o, a1inv);                              \
     }
-    QF_ORTHO(Cy, a2l, ml, Ry, false, Ay, ay_neg)
+    if (!DUPL) QF_ORTHO(Cy, a2l, ml, Ry, false, Ay, ay_neg)
     QF_ORTHO(Dy, sl, c2l, Ry, false, Ay, ay_neg)
-    QF_ORTHO(Cx, a2l, ml, Rx, rx_neg, Ax, false)
+    if (!DUPL) QF_ORTHO(Cx, a2l, ml, Rx, rx_neg, Ax, false)
     QF_ORTHO(Dx, sl, c2l, Rx, rx_neg, Ax, false)
 #undef QF_ORTHO
   }
@@ -598,9 +639,16 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     fw_cneg<M>(Cy, Ry, false);
     fw_cneg<M>(Cx, Rx, rx_neg);
   }
-  // ---- the composed form (two's complement, 2M limbs):
+  return true;
+  }();
+  QF_PHASE();
+
+  // ---- phase 5: the composed form (two's complement, 2M limbs):
   //   a3 = By*Cy - Ay*Dy ; c3 = Bx*Cx - Ax*Dx ; b3 = (Ax*Dy + Ay*Dx) - (Bx*Cy + By*Cx)
   constexpr int P = 2 * M;
+  static_assert(P >= W, "2M >= N+1");
+  u32 ra[N], rb[W], rc[W];
+  if (ok) ok = [&]() -> bool {
   u32 a3[P], b3[P], c3[P];
   {
     // sign-magnitude of the quotients
@@ -623,7 +671,6 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     fw_sub<P>(b3, b3, p);
   }
   // must fit the working shape: 0 < a3 < 2^(32N-1), 0 < c3 < 2^(32W-1), |b3| < 2^(32W-1)
-  static_assert(P >= W, "2M >= N+1");
   if ((a3[P - 1] >> 31) || (c3[P - 1] >> 31)) QF_BAIL;
   if (!fw_high_zero<P, N>(a3) || (a3[N - 1] >> 31) || fw_is_zero<P>(a3)) QF_BAIL;
   if (!fw_high_zero<P, W>(c3) || (c3[W - 1] >> 31)) QF_BAIL;
@@ -633,10 +680,15 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     QF_UNROLL for (int i = W; i < P; i++) o |= b3[i] ^ fill;
     if (o || ((b3[W - 1] >> 31) != (fill & 1))) QF_BAIL;
   }
-  u32 ra[N], rb[W], rc[W];
   fw_copy<N>(ra, a3);
   fw_copy<W>(rb, b3);
   fw_copy<W>(rc, c3);
+  return true;
+  }();
+  QF_PHASE();
+
+  // ---- phase 6: canonical reduction
+  if (ok) ok = [&]() -> bool {
   if (!fw_reduce<N>(ra, rb, rc, dbits)) QF_BAIL;
   // b must fit N limbs signed
   {
@@ -647,6 +699,9 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
   fw_copy<N>(r.b, rb);
   fw_copy<W>(r.c, rc);
   return true;
+  }();
+  return ok;
 }
+#undef QF_PHASE
 
 }  // namespace cofhe
