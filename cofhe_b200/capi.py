@@ -26,6 +26,7 @@ SIGNATURES = {
     "cofhe_b200_shape": (i32, [vp, ctypes.POINTER(u32), ctypes.POINTER(u32), ctypes.POINTER(u32)]),
     "cofhe_b200_status": (i32, [vp, vp]),
     "cofhe_b200_launch_count": (u64, [vp]),
+    "cofhe_b200_fast_limbs": (ctypes.c_int, [vp]),
     "cofhe_b200_nucomp": (i32, [vp, sz, vp, vp, vp, i32, vp]),
     "cofhe_b200_nudupl": (i32, [vp, sz, vp, vp, vp]),
     "cofhe_b200_reduce": (i32, [vp, sz, vp, u32, u32, vp, vp]),

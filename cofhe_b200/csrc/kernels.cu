@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include <new>
 #include <utility>
 
@@ -129,17 +130,27 @@ __global__ void __launch_bounds__(kBlock) k_fast_compose(const Group<CAP> *G, in
   if (!live) idx = n - 1;
   size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
   FormR<N> f1, f2, r;
-  bool ok = fr_load<N>(f1, in1 + off, nc, n, idx);
-  if (!DUPL) ok = fr_load<N>(f2, in2 + off, nc, n, idx) && ok;
+  bool ok;
+  if (neg2 & 2) {
+    // operands without their c rows (host-pointer entry: the kernel reads pinned host memory directly and c is
+    // redundant): c of the operand the composition needs is recomputed from (a, b, Delta)
+    fr_load_ab<N>(f1, in1 + off, n, idx);
+    if (!DUPL) fr_load_ab<N>(f2, in2 + off, n, idx);
+    bool second = !DUPL && !fw_lt<N>(f1.a, f2.a);  // fq_compose reads the c of the form with the smaller a
+    ok = fr_fill_c<N, CAP>(second ? f2 : f1, G);
+  } else {
+    ok = fr_load<N>(f1, in1 + off, nc, n, idx);
+    if (!DUPL) ok = fr_load<N>(f2, in2 + off, nc, n, idx) && ok;
+  }
   // an element that does not fit the register shape still walks through the composition (on its truncated limbs: every
   // loop in there is bounded) so that the block's barriers see all threads; its result is discarded
-  bool cok = fq_compose<N, DUPL, true>(r, f1, DUPL ? f1 : f2, neg2 != 0, dbits);
+  bool cok = fq_compose<N, DUPL, true>(r, f1, DUPL ? f1 : f2, (neg2 & 1) != 0, dbits);
   if (!live) return;
-  if (ok && !cok) {  // declined by the register path: one robust composition for this lane
+  if (ok && !cok && !(neg2 & 2)) {  // declined by the register path: one robust composition for this lane
     u32 xb[3 * N + 1], tb[3 * N + 1];
     fr_pack<N>(xb, f1);
     fr_pack<N>(tb, DUPL ? f1 : f2);
-    cok = slow_compose<N, CAP>(G, xb, tb, neg2 != 0, DUPL);
+    cok = slow_compose<N, CAP>(G, xb, tb, (neg2 & 1) != 0, DUPL);
     fr_unpack<N>(r, xb);
   }
   if (ok && cok) fr_store<N>(r, out + off, nc, n, idx);
@@ -285,7 +296,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   if (!ctx->fastn) {
     CAP_DISPATCH(ctx->cap, {
       const Group<CAP> *G = (const Group<CAP> *)ctx->d_group;
-      if (op == 0) k_compose<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, in2, out, neg2, ctx->d_err);
+      if (op == 0) k_compose<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, in2, out, neg2 & 1, ctx->d_err);
       else if (op == 1) k_square<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, ctx->d_err);
       else k_pow<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_err);
     })
@@ -305,7 +316,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
   unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
-  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, op, in1, in2, out, neg2, exp, el,
+  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, op, in1, in2, out, neg2 & 1, exp, el,
                                                           per_elem, expneg, shared_neg, ctx->d_bail, cnt, cnt_next, ctx->d_err))
   return check_launch(ctx);
 }
@@ -495,6 +506,7 @@ int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream) {
 }
 
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx) { return ctx ? ctx->fastn : 0; }
 
 int cofhe_b200_nucomp(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f1, const uint32_t *f2, uint32_t *out, int negf2,
                       void *stream) {
@@ -832,6 +844,12 @@ int cofhe_b200_device_count(void) {
 
 }  // extern "C"
 
+static double now_ms() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+
 // Lazily created pipeline lane (stream + bail counters).
 static int lane_ready(cofhe_b200_ctx *ctx, int l) {
   cofhe_b200_ctx::Lane &L = ctx->lane[l];
@@ -867,6 +885,31 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   const size_t rows = (size_t)2 * (2 * ctx->na + ctx->nc);
   size_t bytes = rows * n * sizeof(u32);
   int rc = COFHE_B200_OK;
+  // Page-locked (cudaHostAlloc / cudaHostRegister) buffers: no staging at all.  The composition kernel reads the a and
+  // b rows straight from host memory over PCIe (coalesced 128-byte requests; the c rows, 48 % of the bytes, are
+  // redundant and recomputed on the device) and writes the result rows straight back, so the transfer of one warp
+  // overlaps the arithmetic of the others inside a single launch.  Measured on B200 against copy-engine staging,
+  // which pays a slow start after every idle gap: 0.29 ms vs 0.37-0.58 ms per 128x128 add.
+  if (ctx->fastn && !getenv("COFHE_B200_HOST_STAGED")) {
+    cudaPointerAttributes a1, a2, a3;
+    bool pinned = cudaPointerGetAttributes(&a1, ct1) == cudaSuccess && cudaPointerGetAttributes(&a2, ct2) == cudaSuccess &&
+                  cudaPointerGetAttributes(&a3, out) == cudaSuccess && a1.type == cudaMemoryTypeHost &&
+                  a2.type == cudaMemoryTypeHost && a3.type == cudaMemoryTypeHost && a1.devicePointer && a2.devicePointer &&
+                  a3.devicePointer;
+    cudaGetLastError();
+    if (pinned) {
+      rc = lane_ready(ctx, 0);
+      if (rc != COFHE_B200_OK) return rc;
+      int flags = getenv("COFHE_B200_HOST_LOADC") ? 0 : 2;  // 2: operands without c rows
+      rc = with_lane(ctx, 0, [&](cudaStream_t s2) {
+        return launch_op(ctx, 0, 2, n, (const u32 *)a1.devicePointer, (const u32 *)a2.devicePointer, (u32 *)a3.devicePointer, flags,
+                         nullptr, 0, 0, nullptr, 0, s2);
+      });
+      if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->lane[0].st);
+      else cudaStreamSynchronize(ctx->lane[0].st);
+      return rc;
+    }
+  }
   if (ctx->stage_bytes < 3 * bytes) {
     cudaDeviceSynchronize();
     if (ctx->d_stage) cudaFree(ctx->d_stage);
@@ -874,12 +917,38 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
     if (cudaMalloc(&ctx->d_stage, 3 * bytes) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
     ctx->stage_bytes = 3 * bytes;
   }
-  size_t chunks = 4;
-  if (const char *c = getenv("COFHE_B200_HOST_CHUNKS")) { int v = atoi(c); if (v >= 1 && v <= 64) chunks = (size_t)v; }
+  // Default: two lanes, one per form block (all c1 forms, then all c2 forms: each block is contiguous in the SoA batch,
+  // so its transfers are plain 1-D copies at full PCIe rate, and the c2 upload overlaps the c1 kernels).  Element
+  // ranges (COFHE_B200_HOST_CHUNKS > 0) are strided 2-D copies, which the copy engine runs row by row (~1 us per
+  // row): measured slower on B200 below ~10^5 elements.
+  size_t chunks = 0;
+  if (const char *c = getenv("COFHE_B200_HOST_CHUNKS")) { int v = atoi(c); if (v >= 0 && v <= 64) chunks = (size_t)v; }
+  if (chunks == 0) {
+    const size_t fw = (rows / 2) * n;  // words of one form block
+    for (int y = 0; y < 2 && rc == COFHE_B200_OK; y++) {
+      rc = lane_ready(ctx, y);
+      if (rc != COFHE_B200_OK) break;
+      cudaStream_t st = ctx->lane[y].st;
+      u32 *d1 = ctx->d_stage + y * fw, *d2 = d1 + 2 * fw, *d3 = d2 + 2 * fw;
+      if (cudaMemcpyAsync(d1, ct1 + y * fw, fw * 4, cudaMemcpyHostToDevice, st) != cudaSuccess ||
+          cudaMemcpyAsync(d2, ct2 + y * fw, fw * 4, cudaMemcpyHostToDevice, st) != cudaSuccess) { rc = COFHE_B200_ECUDA; break; }
+      rc = with_lane(ctx, y, [&](cudaStream_t s2) { return launch_op(ctx, 0, 1, n, d1, d2, d3, 0, nullptr, 0, 0, nullptr, 0, s2); });
+      if (rc == COFHE_B200_OK && cudaMemcpyAsync(out + y * fw, d3, fw * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        rc = COFHE_B200_ECUDA;
+    }
+    if (cudaStreamSynchronize(ctx->lane[0].st) != cudaSuccess && rc == COFHE_B200_OK) rc = COFHE_B200_ECUDA;
+    if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->lane[1].st);
+    else if (ctx->lane[1].st) cudaStreamSynchronize(ctx->lane[1].st);
+    return rc;
+  }
   if (chunks > (n + 1023) / 1024) chunks = (n + 1023) / 1024;  // ranges below ~1k elements only add launch overhead
   size_t per = (((n + chunks - 1) / chunks) + 31) & ~(size_t)31;
   int used = 0;
   size_t c = 0;
+  const bool trace = getenv("COFHE_B200_HOST_TRACE") != nullptr;  // debugging aid: device times of the first range
+  cudaEvent_t ev[4];
+  double t_start = 0;
+  if (trace) { for (auto &e : ev) cudaEventCreate(&e); t_start = now_ms(); }
   for (size_t e0 = 0; e0 < n && rc == COFHE_B200_OK; e0 += per, c++) {
     size_t cn = n - e0 < per ? n - e0 : per;
     int l = (int)(c % 4);
@@ -888,20 +957,33 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
     if (l + 1 > used) used = l + 1;
     u32 *d1 = ctx->d_stage + 3 * rows * e0, *d2 = d1 + rows * cn, *d3 = d2 + rows * cn;
     cudaStream_t st = ctx->lane[l].st;
+    if (trace && c == 0) cudaEventRecord(ev[0], st);
     if (cudaMemcpy2DAsync(d1, cn * 4, ct1 + e0, n * 4, cn * 4, rows, cudaMemcpyHostToDevice, st) != cudaSuccess ||
         cudaMemcpy2DAsync(d2, cn * 4, ct2 + e0, n * 4, cn * 4, rows, cudaMemcpyHostToDevice, st) != cudaSuccess) {
       rc = COFHE_B200_ECUDA;
       break;
     }
+    if (trace && c == 0) cudaEventRecord(ev[1], st);
     rc = with_lane(ctx, l, [&](cudaStream_t s2) { return cofhe_b200_add_ciphertexts(ctx, cn, d1, d2, d3, s2); });
+    if (trace && c == 0) cudaEventRecord(ev[2], st);
     if (rc == COFHE_B200_OK &&
         cudaMemcpy2DAsync(out + e0, n * 4, d3, cn * 4, cn * 4, rows, cudaMemcpyDeviceToHost, st) != cudaSuccess)
       rc = COFHE_B200_ECUDA;
+    if (trace && c == 0) cudaEventRecord(ev[3], st);
   }
+  double t_issue = trace ? now_ms() : 0;
   for (int l = 0; l < used; l++) {
     if (l + 1 < used) { if (cudaStreamSynchronize(ctx->lane[l].st) != cudaSuccess && rc == COFHE_B200_OK) rc = COFHE_B200_ECUDA; }
     else if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->lane[l].st);  // last lane: sync + sticky element status
     else cudaStreamSynchronize(ctx->lane[l].st);
+  }
+  if (trace) {
+    double t_end = now_ms();
+    float a = 0, b = 0, d = 0;
+    cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]); cudaEventElapsedTime(&d, ev[2], ev[3]);
+    fprintf(stderr, "add_host n=%zu chunks=%zu: issue %.3f ms, total %.3f ms; first range: H2D %.3f kernels %.3f D2H %.3f ms\n", n, c,
+            t_issue - t_start, t_end - t_start, a, b, d);
+    for (auto &e : ev) cudaEventDestroy(e);
   }
   return rc;
 }

@@ -89,6 +89,9 @@ QF_HD float rcp_approx(float x) {
 // an accepted step has T_{j+1} <= r_{j+1} < r_j, hence T_{j+1}^2 < 2^32: accepted cofactors are below 2^16.
 // EXACT == true (the operands fit the leading limb: last rounds of a full gcd): no test, cofactors may grow up to
 // ah / r_j, so they are formed in 64 bits and the run stops before one reaches 2^30.
+#ifndef QF_HG_PAIRS
+#define QF_HG_PAIRS 4
+#endif
 template <bool EXACT>
 QF_HD Mat2 hgcd32(u32 ah, u32 bh, u32 min_r) {
   u32 rp = ah, rc = bh;
@@ -122,11 +125,15 @@ QF_HD Mat2 hgcd32(u32 ah, u32 bh, u32 min_r) {
     fprev = fcur * kLow;                                                                               \
     j++;                                                                                               \
   }
-  for (;;) {
+  // A truncated run is capped at QF_HG_PAIRS double steps: the lanes of a warp wait for each other at the end of a
+  // round, and the number of steps Jebelean's test lets through varies (9 +- 3), so a cap just below the mean keeps
+  // nearly all lanes busy for the whole round; any prefix of the Euclidean sequence is a valid round.
+  for (int it = 0; EXACT || it < QF_HG_PAIRS; it++) {
     swapped = false;
     QF_HG_STEP(rp, Sp, Tp, rc, Sc, Tc, true)   // index j odd -> even
     swapped = true;
     QF_HG_STEP(rc, Sc, Tc, rp, Sp, Tp, false)  // index j even -> odd
+    swapped = false;
   }
 #undef QF_HG_STEP
   Mat2 m;
@@ -191,7 +198,10 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
   for (int guard = 0;; guard++) {
     int b1 = 0;
     if (!done) {
-      b1 = fw_bits<N>(R1);
+      // R1 < R0 and R0 fills its top limb: R1 is almost always within the top two limbs
+      if (R1[N - 1]) b1 = 32 * N - clz32(R1[N - 1]);
+      else if (N >= 2 && R1[N >= 2 ? N - 2 : 0]) b1 = 32 * (N - 1) - clz32(R1[N >= 2 ? N - 2 : 0]);
+      else b1 = fw_bits<N>(R1);
       if (b1 <= sb) done = true;  // includes R1 == 0
       else if (guard >= 80 * N) { bail = true; QF_NOTE; done = true; }
     }

@@ -74,6 +74,11 @@ class ClassGroupB200:
     def status(self):
         capi.check(self.lib.cofhe_b200_status(self.h, _stream()), "status")
 
+    @property
+    def fast(self):
+        """limbs of the register-resident kernels serving this discriminant (0: generic path)"""
+        return int(self.lib.cofhe_b200_fast_limbs(self.h))
+
     def launches(self):
         return int(self.lib.cofhe_b200_launch_count(self.h))
 

@@ -55,6 +55,8 @@ int cofhe_b200_shape(const cofhe_b200_ctx *ctx, uint32_t *na, uint32_t *nc, uint
 int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream);
 /* Number of kernel launches issued through this context so far (bench.py reports it as gpu_launches). */
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx);
+/* Limbs of the register-resident kernel instantiation serving this discriminant (0: generic integer path only). */
+int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx);
 
 /* out[e] = f1[e] o f2[e]   (negf2 != 0: f1[e] o f2[e]^-1), reduced.
  * ClassGroup::nucomp / nucompinv (qfi.inl:1441-1451 -> QFI::nucomp qfi.inl:683-818). */
@@ -78,6 +80,11 @@ int cofhe_b200_nupow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, const uin
  * (reference include/x86_64/cpu_cryptosystem_tensor_ops.inl:197-267, cpu_cryptosystem_vector_ops.inl:58-120). */
 int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
                                void *stream);
+/* Same, on HOST buffers, blocking (the call a CryptoSystem backend makes per add_ciphertext_tensors).  Page-locked
+ * buffers (cudaHostAlloc / cudaHostRegister / cofhe_b200_host_alloc) are read and written by the kernels directly over
+ * PCIe, without staging; on that path only the a and b rows of the operands are read (c = (b^2 - Delta) / 4a is
+ * recomputed on the device), all rows of `out` are written.  Pageable buffers are staged through device memory by
+ * pipelined copies. */
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out);
 

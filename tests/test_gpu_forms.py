@@ -89,6 +89,29 @@ def test_add_ciphertexts(groups, tier):
     out = np.zeros_like(h1)
     G.add_ciphertexts_host(h1, h2, out)
     assert L.limbs_to_cts(out, G.na, G.nc) == list(I(a["res"]))
+    # page-locked buffers: the kernels read / write host memory directly and do not read the c rows at all
+    # (wiped here); the neutral form and a == c forms are among the operands
+    import torch
+    D = int(tier["params"]["Delta"])
+    one = O.identity(D)
+    cts1 = list(I(a["ct1"])) + [(one, I(a["ct1"])[0][1]), (I(a["ct1"])[0][0], one), (one, one)]
+    cts2 = list(I(a["ct2"])) + [(I(a["ct2"])[0][0], one), (one, I(a["ct2"])[0][1]), (one, one)]
+    want = [O.add_ciphertexts(x, y) for x, y in zip(cts1, cts2)]
+    assert want[:len(a["res"])] == list(I(a["res"]))
+    p1 = torch.from_numpy(L.cts_to_limbs(cts1, G.na, G.nc).view(np.int32)).pin_memory()
+    p2 = torch.from_numpy(L.cts_to_limbs(cts2, G.na, G.nc).view(np.int32)).pin_memory()
+    po = torch.zeros_like(p1).pin_memory()
+    for wipe in (False, True):
+        if wipe and G.fast:
+            p1[:, 2 * G.na:, :] = 0x5a5a5a5a
+            p2[:, 2 * G.na:, :] = 0x5a5a5a5a
+            # elements the register path declines (neutral operands) are redone from the full rows: keep theirs
+            k = len(a["res"])
+            p1[:, :, k:] = torch.from_numpy(L.cts_to_limbs(cts1[k:], G.na, G.nc).view(np.int32))
+            p2[:, :, k:] = torch.from_numpy(L.cts_to_limbs(cts2[k:], G.na, G.nc).view(np.int32))
+        po.zero_()
+        G.add_ciphertexts_host(p1.numpy().view(np.uint32), p2.numpy().view(np.uint32), po.numpy().view(np.uint32))
+        assert L.limbs_to_cts(po.numpy().view(np.uint32), G.na, G.nc) == want
 
 
 def test_ragged_and_empty(groups):
