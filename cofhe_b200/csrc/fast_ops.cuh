@@ -9,8 +9,10 @@
 
 #if defined(__CUDA_ARCH__)
 #define QF_BLOCK_ALIGN() __syncthreads()
+#define QF_BLOCK_ANY(p) (__syncthreads_or(p) != 0)
 #else
 #define QF_BLOCK_ALIGN() ((void)0)
+#define QF_BLOCK_ANY(p) (p)
 #endif
 
 namespace cofhe {
@@ -126,12 +128,16 @@ QF_HD bool hy_compose(const Group<CAP> *G, FormR<N> &r, const FormR<N> &f1, cons
 // of the (large) composition body per (N, DUPL) in the whole library instead of one per call site, a kernel register
 // budget that does not have to hold the loop state across it, and an instruction footprint the SM can cache.
 // x: packed f1 in, packed result out (thread-local); t: packed f2 (any address space).
-template <int N, int CAP, bool DUPL>
-QF_HDN bool cc_compose(const Group<CAP> *G, u32 *x, const u32 *t, bool neg2, int dbits) {
+// SYNC: the composition runs with block barriers between its phases (qf_fast.cuh), so EVERY thread of the block must
+// make the call; a thread with nothing to compose passes active = false, walks through on whatever x and t hold and
+// leaves x untouched.
+template <int N, int CAP, bool DUPL, bool SYNC = false>
+QF_HDN bool cc_compose(const Group<CAP> *G, u32 *x, const u32 *t, bool neg2, int dbits, bool active = true) {
   FormR<N> f1, f2, r;
   fr_unpack<N>(f1, x);
   if (!DUPL) fr_unpack<N>(f2, t);
-  bool ok = fq_compose<N, DUPL>(r, f1, DUPL ? f1 : f2, neg2, dbits);
+  bool ok = fq_compose<N, DUPL, SYNC>(r, f1, DUPL ? f1 : f2, neg2, dbits);
+  if (!active) return true;
   if (ok) fr_pack<N>(x, r);
   else {
     u32 tb[3 * N + 1];
@@ -176,10 +182,15 @@ QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32
     if (!ok) op = 0;  // a failed element idles: every thread of the block runs the same number of rounds
     // ---- execute.  The barrier keeps the warps of a block in the same region of the (large) composition code, so
     // that the SM's instruction cache serves them together; without it they drift apart and refetch from L2.
-    QF_BLOCK_ALIGN();
-    if (op == 1) ok = cc_compose<N, CAP, true>(G, xb, xb, false, dbits);
-    else if (op == 2) ok = cc_compose<N, CAP, false>(G, xb, tab + src * TE, false, dbits);
-    else if (op == 3) {
+    // Whether a step is a squaring or a table composition is the same for the whole block (it depends on the
+    // window position only); who takes part is not.
+    const bool sq_phase = built < NT ? built == 1 : sq_left > 0;
+    if (sq_phase) {
+      if (QF_BLOCK_ANY(op == 1)) { bool k = cc_compose<N, CAP, true, true>(G, xb, xb, false, dbits, op == 1); if (op == 1) ok = k; }
+    } else {
+      if (QF_BLOCK_ANY(op == 2)) { bool k = cc_compose<N, CAP, false, true>(G, xb, tab + src * TE, false, dbits, op == 2); if (op == 2) ok = k; }
+    }
+    if (op == 3) {
       QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = tab[src * TE + i];
       started = true;
     }

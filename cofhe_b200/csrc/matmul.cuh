@@ -130,13 +130,12 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int 
       u32 d = (ok && live) ? exp_digit(e, s.el, sstride, w, s.W) : 0u;
       const u32 *te = tab + mm_tab_index(s, y, (size_t)i * s.m + j, w, d ? (int)d : 1) * TE;
       if (d && mm_kind<N>(te) != 0) { ok = false; d = 0; }
-      QF_BLOCK_ALIGN();
-      if (d) {
-        if (started) ok = cc_compose<N, CAP, false>(G, xb, te, false, dbits);
-        else {
-          QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = te[i];
-          started = true;
-        }
+      // every thread of the block makes the call (barriers inside); threads without a digit here just walk through
+      const bool act = d != 0 && started;
+      if (QF_BLOCK_ANY(act)) { bool k = cc_compose<N, CAP, false, true>(G, xb, te, false, dbits, act); if (act) ok = k; }
+      if (d && !started) {
+        QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = te[i];
+        started = true;
       }
     }
   }
