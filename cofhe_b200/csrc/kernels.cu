@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(kBlock) k_pow(const Group<CAP> *G, Shape s, si
 
 // ---- register-resident fast path (fast_ops.cuh) + sparse robust redo of what it declines -------------------------
 template <int N, int CAP, bool DUPL>
-__global__ void __launch_bounds__(kBlock) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
+__global__ void __launch_bounds__(kBlock, 4) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
                                                          int neg2, u32 *bail, int *nbail) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   // threads past the end stay in the kernel (the composition contains block barriers); they redo the last element
