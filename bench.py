@@ -242,6 +242,17 @@ def run_product(args):
         dist.destroy_process_group()
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed `ncu --set full` capture of
+    this same command (profiles/ncu_traffic.json); None when there is no capture for this tier's kernel."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as fh:
+            t = json.load(fh)[kernel]
+        return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+    except Exception:
+        return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
@@ -339,6 +350,13 @@ def emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks,
     ms_step = kern_ms / args.steps
     value = world * n * args.steps / (kern_ms * 1e-3)
     alg_bytes = 3 * ct_bytes                       # read ct1, ct2; write res -- in this build's limb layout
+    # bytes that cross PCIe towards the device per step: on the register-resident tiers the host entry point reads only
+    # the a and b rows of both operands (c is recomputed on the device); all rows of the result travel back
+    if G.fast:
+        h2d_bytes = 2 * ct_bytes * (2 * G.na) // G.fl
+        h2d_note = "a and b rows only: %d of %d limb rows per form" % (2 * G.na, G.fl)
+    else:
+        h2d_bytes, h2d_note = 2 * ct_bytes, "all limb rows, staged"
     achieved = alg_bytes / (ms_step * 1e-3) / 1e9
     imad = ctypes.c_double(imad_peak)
     macs = 2 * n * w_comp(s) / (ms_step * 1e-3)
@@ -350,13 +368,15 @@ def emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks,
                        "l2": "flushed between steps (256 MiB memset); per-step CUDA events on the launch stream, summed",
                        "sharding": "one independent matrix per rank, no collective"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                         "traffic": None, "peak_source": peak_src, "kernel": "k_compose",
+                         "traffic": ncu_traffic("k_fast_compose"), "peak_source": peak_src, "kernel": "k_fast_compose",
                          "alg_bytes_per_launch": alg_bytes},
             "roofline_imad": {"bound": "imad", "achieved": macs / 1e12, "peak": imad.value / 1e12, "unit": "T MAC/s (32x32->64)",
                               "frac": macs / imad.value, "model": "2*W_comp = 32*s^2 MACs per ct-add (SURVEY.md 8d)",
                               "peak_source": "measured in this run (cofhe_b200_imad_probe, IMAD.WIDE.U32 chains on all SMs)"},
-            "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": "ct_adds/s", "h2d_bytes_per_step": 2 * ct_bytes,
-                    "d2h_bytes_per_step": ct_bytes, "api": "cofhe_b200_add_ciphertexts_host (pinned host SoA buffers)"},
+            "e2e": {"value": world * n * e2e_steps / (e2e_ms * 1e-3), "unit": "ct_adds/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": ct_bytes,
+                    "api": "cofhe_b200_add_ciphertexts_host: blocking call on page-locked host SoA buffers; the kernels read "
+                           "the operands from and write the result to host memory over PCIe inside the call (%s)" % h2d_note},
             "gpu_launches": launches, "clocks": clocks}
     if world == 1 and not args.no_cpu:
         from oracle import ref as R

@@ -127,7 +127,7 @@ QF_HD int bn_ctz(const u32 *a, int na) {
 // Knuth algorithm D.  q gets na-nb+1 limbs, r gets nb limbs; `an` is scratch of na+1 limbs, `bs` of nb limbs.
 // q and r must not alias a or b.  Returns lengths through nq/nr.  Single exit on purpose (the 64-bit divisions are
 // calls on the device; see DESIGN.md "device-code rules").
-QF_HDN void bn_divrem(u32 *q, int *nq, u32 *r, int *nr, const u32 *a, int na, const u32 *b, int nb, u32 *an,
+inline QF_HDN void bn_divrem(u32 *q, int *nq, u32 *r, int *nr, const u32 *a, int na, const u32 *b, int nb, u32 *an,
                       u32 *bs) {
   if (bn_cmp(a, na, b, nb) < 0) {
     for (int i = 0; i < na; i++) r[i] = a[i];

@@ -1,0 +1,4 @@
+// cofhe_b200 -- register-resident kernels for 7-limb coefficients (robust-layer capacity 32): see fast_launch.cuh.
+#include "fast_launch_impl.cuh"
+
+template struct cofhe::FastKernels<7, 32>;

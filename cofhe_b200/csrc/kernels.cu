@@ -11,6 +11,7 @@
 #include <utility>
 
 #include "cofhe_b200.h"
+#include "fast_launch.cuh"
 #include "fast_ops.cuh"
 #include "matmul.cuh"
 #include "scheme_ops.cuh"
@@ -55,8 +56,6 @@ struct cofhe_b200_ctx {
 
 namespace {
 
-constexpr int kBlock = 128;
-constexpr int kPowBlock = 384;  // exponentiation kernel: its warps are kept aligned by block barriers
 
 #define CUDA_TRY(x)                                   \
   do {                                                \
@@ -120,64 +119,7 @@ __global__ void __launch_bounds__(kBlock) k_pow(const Group<CAP> *G, Shape s, si
 }
 
 
-// ---- register-resident fast path (fast_ops.cuh) + sparse robust redo of what it declines -------------------------
-template <int N, int CAP, bool DUPL>
-__global__ void __launch_bounds__(kBlock, 4) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
-                                                         int neg2, u32 *bail, int *nbail) {
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // threads past the end stay in the kernel (the composition contains block barriers); they redo the last element
-  bool live = idx < n;
-  if (!live) idx = n - 1;
-  size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
-  FormR<N> f1, f2, r;
-  bool ok;
-  if (neg2 & 2) {
-    // operands without their c rows (host-pointer entry: the kernel reads pinned host memory directly and c is
-    // redundant): c of the operand the composition needs is recomputed from (a, b, Delta)
-    fr_load_ab<N>(f1, in1 + off, n, idx);
-    if (!DUPL) fr_load_ab<N>(f2, in2 + off, n, idx);
-    bool second = !DUPL && !fw_lt<N>(f1.a, f2.a);  // fq_compose reads the c of the form with the smaller a
-    ok = fr_fill_c<N, CAP>(second ? f2 : f1, G);
-  } else {
-    ok = fr_load<N>(f1, in1 + off, nc, n, idx);
-    if (!DUPL) ok = fr_load<N>(f2, in2 + off, nc, n, idx) && ok;
-  }
-  // an element that does not fit the register shape still walks through the composition (on its truncated limbs: every
-  // loop in there is bounded) so that the block's barriers see all threads; its result is discarded
-  bool cok = fq_compose<N, DUPL, true>(r, f1, DUPL ? f1 : f2, (neg2 & 1) != 0, dbits);
-  if (!live) return;
-  if (ok && !cok && !(neg2 & 2)) {  // declined by the register path: one robust composition for this lane
-    u32 xb[3 * N + 1], tb[3 * N + 1];
-    fr_pack<N>(xb, f1);
-    fr_pack<N>(tb, DUPL ? f1 : f2);
-    cok = slow_compose<N, CAP>(G, xb, tb, (neg2 & 1) != 0, DUPL);
-    fr_unpack<N>(r, xb);
-  }
-  if (ok && cok) fr_store<N>(r, out + off, nc, n, idx);
-  else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
-}
-template <int N, int CAP>
-__global__ void __launch_bounds__(kPowBlock) k_fast_pow(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in, u32 *out,
-                                                        const u32 *exp, int el, int per_elem, const unsigned char *expneg,
-                                                        int shared_neg, u32 *bail, int *nbail) {
-  constexpr int W = 4;
-  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // threads past the end stay in the kernel (fr_pow contains block barriers); they redo the last element and store nothing
-  bool live = idx < n;
-  if (!live) idx = n - 1;
-  size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
-  u32 tab[((1 << W) - 1) * (3 * N + 1)];
-  FormR<N> f, r;
-  bool ok = fr_load<N>(f, in + off, nc, n, idx);
-  bool pok = per_elem ? fr_pow<N, CAP, W>(G, r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, CAP, W>(G, r, f, exp, el, 1, dbits, tab);
-  ok = ok && pok;
-  if (live) {
-    if (ok) {
-      if (per_elem ? (expneg && expneg[idx]) : shared_neg != 0) fr_inverse<N>(r);
-      fr_store<N>(r, out + off, nc, n, idx);
-    } else bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
-  }
-}
+// ---- sparse robust redo of what the register-resident kernels (fast_launch.cuh) decline ---------------------------
 // op: 0 compose, 1 square, 2 pow.  Grid-stride over the bail list; clears the counter of the next call.
 template <int CAP>
 __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, size_t n, int op, const u32 *in1, const u32 *in2,
@@ -308,10 +250,10 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   ctx->flip ^= 1;
   int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
   FAST_DISPATCH(ctx->fastn, {
-    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
-    if (op == 0) k_fast_compose<FN, FCAP, false><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
-    else if (op == 1) k_fast_compose<FN, FCAP, true><<<grid, kBlock, 0, st>>>(G, dbits, nc, n, in1, in1, out, 0, ctx->d_bail, cnt);
-    else k_fast_pow<FN, FCAP><<<dim3((unsigned)((n + kPowBlock - 1) / kPowBlock), ny), kPowBlock, 0, st>>>(G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_bail, cnt);
+    typedef FastKernels<FN, FCAP> K;
+    if (op < 2) K::compose(op == 1, grid, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+    else K::pow(dim3((unsigned)((n + kPowBlock - 1) / kPowBlock), ny), st, ctx->d_group, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
+                shared_neg, ctx->d_bail, cnt);
   })
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
@@ -335,10 +277,10 @@ int mm_tables(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, u32 *tab, cu
   int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
   size_t nb = (size_t)s.n * s.m;
   FAST_DISPATCH(ctx->fastn, {
-    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
-    k_mm_chain<FN, FCAP><<<dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, ct, tab);
+    typedef FastKernels<FN, FCAP> K;
+    K::mm_chain(dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), st, ctx->d_group, dbits, nc, s, ct, tab);
     ctx->launches++;
-    k_mm_fill<FN, FCAP><<<dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, s, tab);
+    K::mm_fill(dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), st, ctx->d_group, dbits, s, tab);
   })
   return check_launch(ctx);
 }
@@ -353,12 +295,12 @@ int mm_eval(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *sca
   int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
   ctx->flip ^= 1;
   FAST_DISPATCH(ctx->fastn, {
-    const Group<FCAP> *G = (const Group<FCAP> *)ctx->d_group;
-    k_mm_accum<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), kMMBlock, 0, st>>>(G, dbits, s, scal, tab, part);
+    typedef FastKernels<FN, FCAP> K;
+    K::mm_accum(dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), st, ctx->d_group, dbits, s, scal, tab, part);
     ctx->launches++;
-    k_mm_final<FN, FCAP><<<dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), kMMBlock, 0, st>>>(G, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
+    K::mm_final(dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), st, ctx->d_group, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
     ctx->launches++;
-    k_mm_robust<FCAP><<<32, kMMBlock, 0, st>>>(G, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err);
+    k_mm_robust<FCAP><<<32, kMMBlock, 0, st>>>((const Group<FCAP> *)ctx->d_group, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err);
   })
   return check_launch(ctx);
 }

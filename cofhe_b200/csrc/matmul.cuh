@@ -14,6 +14,10 @@
 // Elements the fast path declines anywhere are appended to the bail list and recomputed on the robust path.
 #pragma once
 #include "fast_ops.cuh"
+#include "matmul_shape.cuh"
+#if defined(__CUDACC__)
+#include "fast_launch.cuh"
+#endif
 
 namespace cofhe {
 
@@ -41,20 +45,7 @@ QF_HD void mm_store(u32 *t, const FormR<N> &f) {
   QF_UNROLL for (int i = 3 * N + 1; i < MMLayout<N>::TE; i++) t[i] = 0;
 }
 
-struct MMShape {
-  unsigned n, m, p;     // ct is n x m, scalars m x p
-  int nwin, W;          // windows per scalar, window width
-  int el;               // limbs per scalar
-  unsigned chunks, jper;  // j range split: chunks * jper >= m
-};
-
-QF_HD size_t mm_tab_index(const MMShape &s, unsigned y, size_t base, int win, int d) {
-  return ((((size_t)y * s.n * s.m + base) * s.nwin + win) * ((1u << s.W) - 1) + (d - 1));
-}
-
-
 #if defined(__CUDACC__)
-constexpr int kMMBlock = 384;  // one block per SM at 168 registers: all resident warps share the barrier
 
 // 1. one thread per (y, base): B_w = ct^(2^(W*w)) into T[w][1]
 template <int N, int CAP>
