@@ -98,6 +98,7 @@ def cpu_baseline_matadd(tier, G=None, iters=50):
     _, nbits, k = TIERS[tier]
     ref = R.Reference(nbits, k)
     ref.call("keygen")
+    ref.set_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     cores = ref.threads()
     na, nc = (G.na, G.nc) if G is not None else (0, 0)
     dt, bufs = ref.bulk_matadd(ROWS, COLS, iters, na, nc, export=G is not None)
@@ -132,6 +133,9 @@ def run_reference(args):
     _, nbits, k = TIERS[args.tier]
     ref = R.Reference(nbits, k)
     ref.call("keygen")
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1, which would throttle the reference
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    ref.set_threads(cores)
     cores = ref.threads()
     if args.warmup:
         ref.bulk_matadd(ROWS, COLS, args.warmup)
