@@ -168,6 +168,22 @@ def synth_cts(G, fx, n, seed):
     return out
 
 
+def bind_near_gpu(index):
+    """One process per GPU: run on (and allocate page-locked host buffers from) the CPU socket the GPU hangs off, so
+    that the host-pointer path does not cross the socket interconnect.  Best effort (NVML's CPU affinity mask)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
+
+
 def run_product(args):
     import numpy as np
     import torch
@@ -178,6 +194,8 @@ def run_product(args):
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
+        bind_near_gpu(local)
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout for the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     fx = fixture(args.tier)
     G = ClassGroupB200(fx["Delta"], local)
