@@ -11,8 +11,10 @@ namespace cofhe {
 
 #if defined(__CUDACC__)
 #define QF_UNROLL _Pragma("unroll")
+#define QF_NOUNROLL _Pragma("unroll 1")
 #else
 #define QF_UNROLL
+#define QF_NOUNROLL
 #endif
 
 template <int N>
@@ -223,8 +225,11 @@ QF_HD u32 div_2by1(u32 u1, u32 u0, u32 d, u32 v, u32 *rem) {
   return q1;
 }
 
-// rem[ND] = u[NU] mod d[ND] for d != 0 with dynamic size (Knuth D on a left-normalised copy of d).
-// Cost is that of NU-ND+1... quotient limbs regardless of the true sizes; u is destroyed (NU+1 limbs of scratch).
+// rem[ND] = u[NU] mod d[ND] for d != 0 with dynamic size: Knuth D on a left-normalised copy of d.
+// The dividend sits in a shift register T (NU+1 limbs, u << s bits): every step divides the top ND+1 limbs and moves
+// T up by one limb, so all register indices are static while the loop itself stays ROLLED -- its trip count is the
+// true number of quotient limbs (NU - ND + 1 + leading zero limbs of d), and the body exists once per call site
+// (~130 SASS instructions instead of ~1.5 k unrolled: this function was half of the composition's code footprint).
 // Returns false if d == 0.
 template <int NU, int ND>
 QF_HD bool fw_mod(u32 *rem, const u32 *u_in, const u32 *d_in) {
@@ -236,37 +241,40 @@ QF_HD bool fw_mod(u32 *rem, const u32 *u_in, const u32 *d_in) {
   fw_shl_limbs<ND>(d, lz);
   int s = clz32(d[ND - 1]);
   fw_shl_bits<ND>(d, d, s);
-  // u scaled by the same factor: NU + ND limbs window is enough (shift < 32*ND bits)
-  constexpr int NW = NU + ND;
-  u32 u[NW + 1];
-  QF_UNROLL for (int i = 0; i < NW + 1; i++) u[i] = i < NU ? u_in[i] : 0;
-  fw_shl_limbs<NW + 1>(u, lz);
+  // d' = d << (32 lz + s) is normalised; u' = u << (32 lz + s).  T = u << s, read at the position where the first
+  // window u'[jmax .. jmax+ND], jmax = NU + lz - ND, is the top of the register.
+  u32 T[NU + 1];
   {
-    u32 t[NW + 1];
-    fw_shl_bits<NW + 1>(t, u, s);
-    fw_copy<NW + 1>(u, t);
+    u32 t[NU + 1];
+    QF_UNROLL for (int i = 0; i < NU + 1; i++) t[i] = i < NU ? u_in[i] : 0;
+    fw_shl_bits<NU + 1>(T, t, s);
   }
-  u32 dt = d[ND - 1], v = recip32(dt);
-  QF_UNROLL for (int j = NW - ND; j >= 0; j--) {
-    // quotient limb from (u[j+ND], u[j+ND-1]) / dt ; u[j+ND] <= dt is an invariant
-    u32 u1 = u[j + ND], u0 = u[j + ND - 1], r;
+  const u32 dt = d[ND - 1], v = recip32(dt);
+  const int cnt = NU - ND + 1 + lz;
+  constexpr int B = NU - ND;  // window = T[B .. NU]
+  QF_NOUNROLL for (int it = 0; it < cnt; it++) {
+    // quotient limb from the two top limbs; top <= dt is an invariant
+    u32 u1 = T[NU], u0 = T[NU - 1], r;
     u32 qh = (u1 >= dt) ? 0xffffffffu : div_2by1(u1, u0, dt, v, &r);
     if (qh != 0) {
-      // u[j..j+ND] -= qh * d
-      u32 bo = fw_submul1<ND>(u + j, d, qh);
-      u32 top = u[j + ND];
-      u[j + ND] = top - bo;
+      u32 bo = fw_submul1<ND>(T + B, d, qh);
+      u32 top = T[NU];
+      T[NU] = top - bo;
       if (top < bo) {
         // went negative: add back (at most twice)
-        u32 c = fw_add<ND>(u + j, u + j, d);
-        u[j + ND] += c;
-        if (u[j + ND] != 0) { c = fw_add<ND>(u + j, u + j, d); u[j + ND] += c; }
+        u32 c = fw_add<ND>(T + B, T + B, d);
+        T[NU] += c;
+        if (T[NU] != 0) { c = fw_add<ND>(T + B, T + B, d); T[NU] += c; }
       }
     }
+    // the top limb is zero now: move the register up by one limb
+    QF_UNROLL for (int i = NU; i > 0; i--) T[i] = T[i - 1];
+    T[0] = 0;
   }
-  // remainder = u[0..ND) >> (32*lz + s)
-  u32 r2[ND];
-  fw_shr_bits<ND>(r2, u, s);
+  // remainder' = T[B+1 .. NU] (after the last move); remainder = remainder' >> (32*lz + s)
+  u32 r1[ND], r2[ND];
+  QF_UNROLL for (int i = 0; i < ND; i++) r1[i] = T[B + 1 + i];
+  fw_shr_bits<ND>(r2, r1, s);
   fw_shr_limbs<ND>(r2, lz);
   fw_copy<ND>(rem, r2);
   return true;
