@@ -74,29 +74,29 @@ void FastKernels<FN, FCAP>::compose(bool dupl, dim3 grid, cudaStream_t st, const
   else k_fast_compose<FN, FCAP, false><<<grid, kBlock, 0, st>>>(g, dbits, nc, n, in1, in2, out, flags, bail, nbail);
 }
 template <int FN, int FCAP>
-void FastKernels<FN, FCAP>::pow(dim3 grid, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in, u32 *out,
+void FastKernels<FN, FCAP>::pow(dim3 grid, int block, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in, u32 *out,
                                 const u32 *exp, int el, int per_elem, const unsigned char *expneg, int shared_neg, u32 *bail,
                                 int *nbail) {
-  k_fast_pow<FN, FCAP><<<grid, kPowBlock, 0, st>>>((const Group<FCAP> *)G, dbits, nc, n, in, out, exp, el, per_elem, expneg, shared_neg,
+  k_fast_pow<FN, FCAP><<<grid, block, 0, st>>>((const Group<FCAP> *)G, dbits, nc, n, in, out, exp, el, per_elem, expneg, shared_neg,
                                                    bail, nbail);
 }
 template <int FN, int FCAP>
-void FastKernels<FN, FCAP>::mm_chain(dim3 grid, cudaStream_t st, const void *G, int dbits, int nc, MMShape s, const u32 *ct, u32 *tab) {
-  k_mm_chain<FN, FCAP><<<grid, kMMBlock, 0, st>>>((const Group<FCAP> *)G, dbits, nc, s, ct, tab);
+void FastKernels<FN, FCAP>::mm_chain(dim3 grid, int block, cudaStream_t st, const void *G, int dbits, int nc, MMShape s, const u32 *ct, u32 *tab) {
+  k_mm_chain<FN, FCAP><<<grid, block, 0, st>>>((const Group<FCAP> *)G, dbits, nc, s, ct, tab);
 }
 template <int FN, int FCAP>
-void FastKernels<FN, FCAP>::mm_fill(dim3 grid, cudaStream_t st, const void *G, int dbits, MMShape s, u32 *tab) {
-  k_mm_fill<FN, FCAP><<<grid, kMMBlock, 0, st>>>((const Group<FCAP> *)G, dbits, s, tab);
+void FastKernels<FN, FCAP>::mm_fill(dim3 grid, int block, cudaStream_t st, const void *G, int dbits, MMShape s, u32 *tab) {
+  k_mm_fill<FN, FCAP><<<grid, block, 0, st>>>((const Group<FCAP> *)G, dbits, s, tab);
 }
 template <int FN, int FCAP>
-void FastKernels<FN, FCAP>::mm_accum(dim3 grid, cudaStream_t st, const void *G, int dbits, MMShape s, const u32 *scal, const u32 *tab,
+void FastKernels<FN, FCAP>::mm_accum(dim3 grid, int block, cudaStream_t st, const void *G, int dbits, MMShape s, const u32 *scal, const u32 *tab,
                                      u32 *part) {
-  k_mm_accum<FN, FCAP><<<grid, kMMBlock, 0, st>>>((const Group<FCAP> *)G, dbits, s, scal, tab, part);
+  k_mm_accum<FN, FCAP><<<grid, block, 0, st>>>((const Group<FCAP> *)G, dbits, s, scal, tab, part);
 }
 template <int FN, int FCAP>
-void FastKernels<FN, FCAP>::mm_final(dim3 grid, cudaStream_t st, const void *G, int dbits, int nc, MMShape s, const u32 *init,
+void FastKernels<FN, FCAP>::mm_final(dim3 grid, int block, cudaStream_t st, const void *G, int dbits, int nc, MMShape s, const u32 *init,
                                      const u32 *part, u32 *out, u32 *bail, int *nbail) {
-  k_mm_final<FN, FCAP><<<grid, kMMBlock, 0, st>>>((const Group<FCAP> *)G, dbits, nc, s, init, part, out, bail, nbail);
+  k_mm_final<FN, FCAP><<<grid, block, 0, st>>>((const Group<FCAP> *)G, dbits, nc, s, init, part, out, bail, nbail);
 }
 
 }  // namespace cofhe

@@ -214,7 +214,22 @@ QF_HD void fw_divexact_2adic(u32 *q, u32 *num, const u32 *d, u32 dinv) {
 
 // (qhat, rem) of the 64-by-32 division (u1:u0) / d for normalised d (top bit set) and u1 < d, with a precomputed
 // reciprocal v = floor((2^64 - 1) / d) - 2^32  (Moller & Granlund, "Improved division by invariant integers")
-QF_HD u32 recip32(u32 d) { return (u32)(~(u64)0 / d - ((u64)1 << 32)); }
+QF_HD u32 recip32(u32 d) {
+#if defined(__CUDA_ARCH__)
+  // floor((2^64 - 1) / d) - 2^32 = floor(t / d) with t = 2^64 - 1 - d * 2^32 < d * 2^32 (d is normalised).  One
+  // double-precision division (relative error 2^-52 on a quotient below 2^32: off by at most one) and an exact
+  // fix-up, instead of the 64-bit integer division subroutine.
+  u64 t = ((u64)(~d) << 32) | 0xffffffffu;
+  double q = (double)t / (double)d;
+  u32 v = q >= 4294967295.0 ? 0xffffffffu : (u32)q;
+  u64 p = (u64)v * d;
+  if (p > t) v--;
+  else if (t - p >= d) v++;
+  return v;
+#else
+  return (u32)(~(u64)0 / d - ((u64)1 << 32));
+#endif
+}
 QF_HD u32 div_2by1(u32 u1, u32 u0, u32 d, u32 v, u32 *rem) {
   u64 q = (u64)v * u1 + (((u64)u1 << 32) | u0);
   u32 q1 = (u32)(q >> 32) + 1, q0 = (u32)q;

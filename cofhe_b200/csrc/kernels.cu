@@ -249,10 +249,11 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
   ctx->flip ^= 1;
   int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  const int pb = pick_block((size_t)ny * n, ctx->sms);
   FAST_DISPATCH(ctx->fastn, {
     typedef FastKernels<FN, FCAP> K;
     if (op < 2) K::compose(op == 1, grid, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
-    else K::pow(dim3((unsigned)((n + kPowBlock - 1) / kPowBlock), ny), st, ctx->d_group, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
+    else K::pow(dim3((unsigned)((n + pb - 1) / pb), ny), pb, st, ctx->d_group, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
                 shared_neg, ctx->d_bail, cnt);
   })
   rc = check_launch(ctx);
@@ -278,9 +279,10 @@ int mm_tables(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, u32 *tab, cu
   size_t nb = (size_t)s.n * s.m;
   FAST_DISPATCH(ctx->fastn, {
     typedef FastKernels<FN, FCAP> K;
-    K::mm_chain(dim3((unsigned)((nb + kMMBlock - 1) / kMMBlock), 2), st, ctx->d_group, dbits, nc, s, ct, tab);
+    const int b1 = pick_block(2 * nb, ctx->sms), b2 = pick_block(2 * nb * s.nwin, ctx->sms);
+    K::mm_chain(dim3((unsigned)((nb + b1 - 1) / b1), 2), b1, st, ctx->d_group, dbits, nc, s, ct, tab);
     ctx->launches++;
-    K::mm_fill(dim3((unsigned)((nb * s.nwin + kMMBlock - 1) / kMMBlock), 2), st, ctx->d_group, dbits, s, tab);
+    K::mm_fill(dim3((unsigned)((nb * s.nwin + b2 - 1) / b2), 2), b2, st, ctx->d_group, dbits, s, tab);
   })
   return check_launch(ctx);
 }
@@ -296,19 +298,20 @@ int mm_eval(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *sca
   ctx->flip ^= 1;
   FAST_DISPATCH(ctx->fastn, {
     typedef FastKernels<FN, FCAP> K;
-    K::mm_accum(dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2, s.chunks), st, ctx->d_group, dbits, s, scal, tab, part);
+    const int ba = s.block ? s.block : pick_block(2 * no * s.chunks, ctx->sms), bf = pick_block(2 * no, ctx->sms);
+    K::mm_accum(dim3((unsigned)((no + ba - 1) / ba), 2, s.chunks), ba, st, ctx->d_group, dbits, s, scal, tab, part);
     ctx->launches++;
-    K::mm_final(dim3((unsigned)((no + kMMBlock - 1) / kMMBlock), 2), st, ctx->d_group, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
+    K::mm_final(dim3((unsigned)((no + bf - 1) / bf), 2), bf, st, ctx->d_group, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
     ctx->launches++;
-    k_mm_robust<FCAP><<<32, kMMBlock, 0, st>>>((const Group<FCAP> *)ctx->d_group, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err);
+    k_mm_robust<FCAP><<<32, 128, 0, st>>>((const Group<FCAP> *)ctx->d_group, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err);
   })
   return check_launch(ctx);
 }
 int mm_robust_all(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *scal, const u32 *init, u32 *out, cudaStream_t st) {
   Shape sh{(int)ctx->na, (int)ctx->nc};
   size_t no = (size_t)s.n * s.p;
-  unsigned blocks = (unsigned)((2 * no + kMMBlock - 1) / kMMBlock);
-  CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, kMMBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
+  unsigned blocks = (unsigned)((2 * no + 127) / 128);
+  CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, 128, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
                                                                      nullptr, nullptr, nullptr, ctx->d_err))
   return check_launch(ctx);
 }
@@ -511,23 +514,25 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   if (const char *w = getenv("COFHE_B200_MM_W")) { int v = atoi(w); if (v >= 2 && v <= 8) s.W = v; }
   if (ebits == 0 || ebits > 32 * el) ebits = 32 * el;
   s.nwin = (int)((ebits + s.W - 1) / s.W);
-  s.chunks = 1; s.jper = (unsigned)m;
+  s.chunks = 1; s.jper = (unsigned)m; s.block = 0;
   size_t no = n * p;
   if (!ctx->fastn || m == 0) return mm_robust_all(ctx, s, ct, scal, init, out, st);
   // split the j range so that small n*p still fills the machine
-  // k_mm_accum runs one kMMBlock-thread block per SM (register budget), all blocks of equal length: pick the chunk
-  // count whose grid is closest to a whole number of waves (rounds * columns-per-chunk = the time of the launch); each
-  // extra chunk costs one more composition per output in k_mm_final
+  // k_mm_accum: blocks of `block` threads, 512 / block of them resident per SM (128 registers), all equally long: pick
+  // the chunk count whose grid is closest to a whole number of waves (rounds * columns-per-chunk = the time of the
+  // launch); each extra chunk costs one more composition per output in k_mm_final
   size_t ch = 1;
   {
     const size_t sms = (size_t)(ctx->sms > 0 ? ctx->sms : 148);
-    const size_t bpc = 2 * ((no + kMMBlock - 1) / kMMBlock);  // blocks per chunk
     size_t chmax = m / 2 < 1 ? 1 : m / 2;
     if (chmax > 64) chmax = 64;
+    s.block = pick_block(2 * no * chmax, ctx->sms);  // full blocks whenever chunking can fill the machine with them
+    const size_t slots = sms * (size_t)(512 / s.block);
+    const size_t bpc = 2 * ((no + s.block - 1) / s.block);  // blocks per chunk
     double best = 0;
     for (size_t c = 1; c <= chmax; c++) {
       size_t jper = (m + c - 1) / c, cc = (m + jper - 1) / jper;
-      size_t rounds = (bpc * cc + sms - 1) / sms;
+      size_t rounds = (bpc * cc + slots - 1) / slots;
       double cost = (double)rounds * (double)jper * (double)(s.nwin) + (double)cc;
       if (c == 1 || cost < best) { best = cost; ch = c; }
     }
@@ -623,7 +628,7 @@ int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t 
   CUDA_TRY(cudaMemcpy(ctx->d_fb_bases, h, fl * sizeof(u32), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(ctx->d_fb_bases + fl, pk ? pk : h, fl * sizeof(u32), cudaMemcpyHostToDevice));
   MMShape s;
-  s.n = 1; s.m = 1; s.p = 0; s.chunks = 1; s.jper = 1;
+  s.n = 1; s.m = 1; s.p = 0; s.chunks = 1; s.jper = 1; s.block = 0;
   s.W = 8;
   if (const char *w = getenv("COFHE_B200_FB_W")) { int v = atoi(w); if (v >= 2 && v <= 10) s.W = v; }
   s.el = (int)((ebits + 31) / 32);

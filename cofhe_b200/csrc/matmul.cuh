@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int 
 
 // robust path: all outputs (list == nullptr) or the listed ones; clears the next call's counter
 template <int CAP>
-__global__ void __launch_bounds__(kMMBlock) k_mm_robust(const Group<CAP> *G, Shape sh, MMShape s, const u32 *ct, const u32 *scal,
+__global__ void __launch_bounds__(128) k_mm_robust(const Group<CAP> *G, Shape sh, MMShape s, const u32 *ct, const u32 *scal,
                                                         const u32 *init, u32 *out, const u32 *bail, const int *nbail,
                                                         int *nbail_next, int *err) {
   size_t no = (size_t)s.n * s.p, nb = (size_t)s.n * s.m;

@@ -11,6 +11,7 @@ struct MMShape {
   int nwin, W;          // windows per scalar, window width
   int el;               // limbs per scalar
   unsigned chunks, jper;  // j range split: chunks * jper >= m
+  int block;              // threads per block of the accumulate kernel (0: chosen at launch)
 };
 
 QF_HD size_t mm_tab_index(const MMShape &s, unsigned y, size_t base, int win, int d) {
