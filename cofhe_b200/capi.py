@@ -27,6 +27,10 @@ SIGNATURES = {
     "cofhe_b200_status": (i32, [vp, vp]),
     "cofhe_b200_launch_count": (u64, [vp]),
     "cofhe_b200_fast_limbs": (ctypes.c_int, [vp]),
+    "cofhe_b200_wire_header": (i32, [vp, sz, ctypes.POINTER(u32), vp, u32, ctypes.POINTER(sz)]),
+    "cofhe_b200_wire_bound": (sz, [vp, u32, sz]),
+    "cofhe_b200_wire_to_cts": (i32, [vp, vp, sz, u32, sz, vp, vp]),
+    "cofhe_b200_cts_to_wire": (i32, [vp, u32, vp, sz, vp, vp, sz, ctypes.POINTER(sz), vp]),
     "cofhe_b200_nucomp": (i32, [vp, sz, vp, vp, vp, i32, vp]),
     "cofhe_b200_nudupl": (i32, [vp, sz, vp, vp, vp]),
     "cofhe_b200_reduce": (i32, [vp, sz, vp, u32, u32, vp, vp]),

@@ -15,6 +15,7 @@
 #include "fast_ops.cuh"
 #include "matmul.cuh"
 #include "scheme_ops.cuh"
+#include "wire.cuh"
 
 using namespace cofhe;
 
@@ -787,6 +788,89 @@ int cofhe_b200_device_count(void) {
   int c = 0;
   if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; }
   return c;
+}
+
+/* ---- binary tensor wire format (reference cpu_cryptosystem.inl:322-520) <-> SoA batches, on the device -------- */
+int cofhe_b200_wire_header(const uint8_t *wire, size_t bytes, uint32_t *ndim, uint32_t *dims, uint32_t max_dims, size_t *n) {
+  if (!wire || !ndim || !n || bytes < 4) return COFHE_B200_EINVAL;
+  uint32_t nd;
+  memcpy(&nd, wire, 4);
+  if (nd > max_dims || bytes < 4 + 4 * (size_t)nd) return COFHE_B200_EINVAL;
+  size_t cnt = 1;
+  for (uint32_t i = 0; i < nd; i++) {
+    uint32_t d;
+    memcpy(&d, wire + 4 + 4 * (size_t)i, 4);
+    if (dims) dims[i] = d;
+    if (d && cnt > ((size_t)1 << 40) / d) return COFHE_B200_EINVAL;
+    cnt *= d;
+  }
+  if (bytes < 4 + 4 * (size_t)nd + 48 * cnt) return COFHE_B200_EINVAL;
+  *ndim = nd;
+  *n = cnt;
+  return COFHE_B200_OK;
+}
+
+size_t cofhe_b200_wire_bound(const cofhe_b200_ctx *ctx, uint32_t ndim, size_t n) {
+  if (!ctx) return 0;
+  return 4 + 4 * (size_t)ndim + n * (48 + 4 * (size_t)(4 * ctx->na + 1) + 2 * (size_t)(4 * ctx->nc + 1));
+}
+
+int cofhe_b200_wire_to_cts(cofhe_b200_ctx *ctx, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
+                           void *stream) {
+  if (!ctx || (n && (!wire || !out))) return COFHE_B200_EINVAL;
+  size_t head = 4 + 4 * (size_t)ndim;
+  if (bytes < head + 48 * n) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  WireShape s{(int)ctx->na, (int)ctx->nc, n};
+  unsigned blocks = (unsigned)((6 * n + kWireBlock - 1) / kWireBlock);
+  k_wire_read<<<blocks, kWireBlock, 0, (cudaStream_t)stream>>>(s, wire + head, wire + head + 48 * n, (unsigned long long)(bytes - head - 48 * n),
+                                                             out, ctx->d_err);
+  return check_launch(ctx);
+}
+
+int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *dims, size_t n, const uint32_t *ct, uint8_t *wire,
+                           size_t cap, size_t *written, void *stream) {
+  if (!ctx || !written || (ndim && !dims) || ndim > 8 || !wire || (n && !ct)) return COFHE_B200_EINVAL;
+  size_t cnt = 1;
+  for (uint32_t i = 0; i < ndim; i++) cnt *= dims[i];
+  if (cnt != n) return COFHE_B200_EINVAL;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t head = 4 + 4 * (size_t)ndim;
+  *written = head + 48 * n;
+  if (cap < *written) return COFHE_B200_EINVAL;
+  uint32_t hb[9];
+  hb[0] = ndim;
+  for (uint32_t i = 0; i < ndim; i++) hb[1 + i] = dims[i];
+  CUDA_TRY(cudaMemcpyAsync(wire, hb, head, cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaStreamSynchronize(st));  // hb is a stack buffer
+  if (n == 0) return COFHE_B200_OK;
+  // scratch: offsets u64[6n] | block totals u64[nb] | sum u64 | sizes u32[6n] | flags u8[6n]
+  size_t m = 6 * n, nb = (m + kScanBlock - 1) / kScanBlock;
+  int rc = ensure_work(ctx, (m + nb + 1) * 8 + m * 4 + m);
+  if (rc != COFHE_B200_OK) return rc;
+  unsigned long long *offs = (unsigned long long *)ctx->d_work, *totals = offs + m, *sum = totals + nb;
+  u32 *sizes = (u32 *)(sum + 1);
+  unsigned char *flags = (unsigned char *)(sizes + m);
+  WireShape s{(int)ctx->na, (int)ctx->nc, n};
+  unsigned blocks = (unsigned)((m + kWireBlock - 1) / kWireBlock);
+  k_wire_sizes<<<blocks, kWireBlock, 0, st>>>(s, ct, sizes, flags);
+  ctx->launches++;
+  k_scan_blocks<<<(unsigned)nb, kScanBlock, 0, st>>>(m, sizes, offs, totals);
+  ctx->launches++;
+  k_scan_totals<<<1, kScanBlock, 0, st>>>(nb, totals, sum);
+  rc = check_launch(ctx);
+  if (rc != COFHE_B200_OK) return rc;
+  unsigned long long body = 0;
+  CUDA_TRY(cudaMemcpyAsync(&body, sum, 8, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  *written = head + 48 * n + (size_t)body;
+  if (cap < *written) return COFHE_B200_EINVAL;  // *written tells the caller what is needed
+  k_wire_write<<<blocks, kWireBlock, 0, st>>>(s, ct, sizes, flags, offs, totals, wire + head, wire + head + 48 * n);
+  return check_launch(ctx);
 }
 
 }  // extern "C"

@@ -88,6 +88,27 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out);
 
+/* ---- Binary tensor wire format <-> SoA batches on the device.
+ * The format is the one of CPUCryptoSystem::serialize_ciphertext_tensor / deserialize_ciphertext_tensor (reference
+ * include/x86_64/cpu_cryptosystem.inl:322-391 and :393-520): u32 ndim | u32 dims[ndim] | u64 table[6n] | magnitudes;
+ * table entries are byte offsets into the magnitude area with bit 63 set for integers <= 0; an integer x owns
+ * mpz_sizeinbase(x,2)/8 + 1 little-endian bytes.  These calls replace the per-element mpz_import / mpz_export loops
+ * either side of every network operation (reference include/node/compute_request_handler.hpp:414-431, 562-578).
+ *
+ * cofhe_b200_wire_header: parse ndim / dims / element count from the first bytes of a HOST buffer (no device work).
+ * cofhe_b200_wire_bound : upper bound of the serialised size of n ciphertexts of this context's shape.
+ * cofhe_b200_wire_to_cts: wire bytes in DEVICE memory (or page-locked host memory) -> ciphertext batch [2][2na+nc][n].
+ *                         Malformed input (integer wider than its limbs, offsets out of range) raises the sticky
+ *                         element status (COFHE_B200_EARITH at the next cofhe_b200_status).
+ * cofhe_b200_cts_to_wire: ciphertext batch -> wire bytes in device memory; blocking for the size (one 8-byte read-back),
+ *                         *written = bytes produced, or needed when `cap` is too small (COFHE_B200_EINVAL). */
+int cofhe_b200_wire_header(const uint8_t *wire, size_t bytes, uint32_t *ndim, uint32_t *dims, uint32_t max_dims, size_t *n);
+size_t cofhe_b200_wire_bound(const cofhe_b200_ctx *ctx, uint32_t ndim, size_t n);
+int cofhe_b200_wire_to_cts(cofhe_b200_ctx *ctx, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
+                           void *stream);
+int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *dims, size_t n, const uint32_t *ct, uint8_t *wire,
+                           size_t cap, size_t *written, void *stream);
+
 /* Scalar x ciphertext matmul: out[i,k] = init o prod_j ct[i,j]^{s[j,k]}  (i < n, j < m, k < p; row-major).
  * ct: ciphertext batch of n*m elements, scal: non-negative scalars [el][m*p] (limb-major), init: ONE ciphertext
  * (the reference's `zero` = encrypt(pk, 0)), out: ciphertext batch of n*p elements.  ebits: an upper bound on the

@@ -330,3 +330,48 @@ def combine(P, ct, ds):
     for i, di in enumerate(ds):
         d = compose(d, power(di, 1 if i == 0 else -1))
     return dlog_in_F(P, compose_inv(ct[1], d))
+
+
+# ---- binary tensor wire format -------------------------------------------------------------
+def _wire_size(x):
+    """bytes reserved for one integer: mpz_sizeinbase(x, 2) / 8 + 1 (cpu_cryptosystem.inl:340-356; sizeinbase(0) = 1)."""
+    return max(abs(x).bit_length(), 1) // 8 + 1
+
+
+def serialize_ciphertext_tensor(shape, cts):
+    """CPUCryptoSystem::serialize_ciphertext_tensor (include/x86_64/cpu_cryptosystem.inl:322-391): u32 ndim, u32 dims,
+    then 6 u64 offsets per ciphertext (c1.a c1.b c1.c c2.a c2.b c2.c; bit 63 set when sgn != 1, i.e. negative OR zero),
+    then the magnitudes, little endian (mpz_export order -1, size 1), each in its reserved `_wire_size` bytes."""
+    import struct
+    ints = [x for ct in cts for f in ct for x in f]
+    head = struct.pack("<I", len(shape)) + b"".join(struct.pack("<I", d) for d in shape)
+    table, blobs, off = [], [], 0
+    for x in ints:
+        table.append(off | ((1 << 63) if x <= 0 else 0))
+        sz = _wire_size(x)
+        blobs.append(abs(x).to_bytes(sz, "little"))
+        off += sz
+    return head + b"".join(struct.pack("<Q", t) for t in table) + b"".join(blobs)
+
+
+def deserialize_ciphertext_tensor(data):
+    """CPUCryptoSystem::deserialize_ciphertext_tensor (cpu_cryptosystem.inl:393-520): the size of an integer is the
+    distance to the next offset (the last one runs to the end of the buffer).  -> (shape, cts)"""
+    import struct
+    ndim = struct.unpack_from("<I", data, 0)[0]
+    shape = list(struct.unpack_from("<%dI" % ndim, data, 4))
+    n = 1
+    for d in shape:
+        n *= d
+    base = 4 + 4 * ndim
+    table = struct.unpack_from("<%dQ" % (6 * n), data, base)
+    body = base + 48 * n
+    mask = (1 << 63) - 1
+    ints = []
+    for i, t in enumerate(table):
+        lo = t & mask
+        hi = (table[i + 1] & mask) if i + 1 < len(table) else len(data) - body
+        v = int.from_bytes(data[body + lo:body + hi], "little")
+        ints.append(-v if t >> 63 else v)
+    cts = [(tuple(ints[6 * i:6 * i + 3]), tuple(ints[6 * i + 3:6 * i + 6])) for i in range(n)]
+    return shape, cts

@@ -162,6 +162,23 @@ std::string call(Ref &R, const std::string &op, const std::vector<Mpz> &a) {
     for (size_t i = 0; i < n; i++) t.at(i) = new CS::CipherText(ctext(a, 1 + 6 * i));
     auto res = R.cs.negate_ciphertext_tensor(*R.pk, t); res.flatten();
     for (size_t i = 0; i < n; i++) { put(o, *res.at(i)); delete res.at(i); delete t.at(i); }
+  } else if (op == "serialize_ct_tensor") {  // rows cols cts... -> the bytes of serialize_ciphertext_tensor, one number per byte
+    size_t r = to_sz(a[0]), c = to_sz(a[1]), n = r * c;
+    auto t = make_tensor<CS::CipherText>(r, c); t.flatten();
+    for (size_t i = 0; i < n; i++) t.at(i) = new CS::CipherText(ctext(a, 2 + 6 * i));
+    t.reshape({r, c});
+    std::string bytes = R.cs.serialize_ciphertext_tensor(t);
+    t.flatten();
+    for (size_t i = 0; i < n; i++) delete t.at(i);
+    for (unsigned char ch : bytes) o << (unsigned)ch << ' ';
+  } else if (op == "deserialize_ct_tensor") {  // bytes... -> ndim dims... cts...
+    std::string bytes(a.size(), 0);
+    for (size_t i = 0; i < a.size(); i++) bytes[i] = (char)to_sz(a[i]);
+    auto t = R.cs.deserialize_ciphertext_tensor(bytes);
+    o << t.ndim() << ' ';
+    for (size_t i = 0; i < t.ndim(); i++) o << t.shape()[i] << ' ';
+    t.flatten();
+    for (size_t i = 0; i < t.num_elements(); i++) { put(o, *t.at(i)); delete t.at(i); }
   } else {
     throw std::invalid_argument("unknown op " + op);
   }
