@@ -141,6 +141,31 @@ class ClassGroupB200:
                                                    _stream()), "scal_matmul")
         return out
 
+    # ---- binary tensor wire format (reference serialize/deserialize_ciphertext_tensor) on the device -------------------
+    def wire_to_cts(self, data):
+        """bytes of CPUCryptoSystem::serialize_ciphertext_tensor -> (shape, device ciphertext batch [2, fl, n])."""
+        buf = np.frombuffer(bytes(data), dtype=np.uint8)
+        ndim, n = ctypes.c_uint32(), ctypes.c_size_t()
+        dims = (ctypes.c_uint32 * 8)()
+        capi.check(self.lib.cofhe_b200_wire_header(buf.ctypes.data_as(ctypes.c_void_p), buf.size, ctypes.byref(ndim), dims, 8,
+                                                   ctypes.byref(n)), "wire_header")
+        dev = torch.from_numpy(buf.copy()).to(self.device)
+        out = torch.empty((2, self.fl, n.value), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_wire_to_cts(self.h, _ptr(dev), buf.size, ndim.value, n.value, _ptr(out), _stream()), "wire_to_cts")
+        torch.cuda.current_stream().synchronize()  # `dev` must outlive the kernel
+        return [int(dims[i]) for i in range(ndim.value)], out
+
+    def cts_to_wire(self, shape, ct):
+        """device ciphertext batch -> bytes of the reference's binary tensor format."""
+        n = ct.shape[-1]
+        cap = int(self.lib.cofhe_b200_wire_bound(self.h, len(shape), n))
+        dev = torch.empty(cap, dtype=torch.uint8, device=self.device)
+        dims = (ctypes.c_uint32 * max(1, len(shape)))(*shape)
+        written = ctypes.c_size_t()
+        capi.check(self.lib.cofhe_b200_cts_to_wire(self.h, len(shape), dims, n, _ptr(ct), _ptr(dev), cap, ctypes.byref(written),
+                                                   _stream()), "cts_to_wire")
+        return bytes(dev[:written.value].cpu().numpy())
+
     # ---- CL_HSM2k scheme level (mirrors CPUCryptoSystem's batched entry points on SoA device tensors) --------------
     def set_scheme(self, k, N):
         nN = (int(N).bit_length() + 31) // 32

@@ -124,3 +124,14 @@ def test_live_reference_random():
         assert O.power(f1, e) == tuple(R.call("nupow", f1, e))
         m = rng.getrandbits(128)
         assert O.power_of_f(P, m) == tuple(R.call("power_of_f", m))
+
+
+def test_wire_format_matches_reference_bytes():
+    """oracle restatement of the binary tensor format vs bytes written by the compiled reference (tests/golden/ref_wire.json,
+    made by tools/gen_golden_wire.py)."""
+    w = load_golden("ref_wire.json")
+    for tier, t in w.items():
+        cts = [tuple(tuple(int(x) for x in f) for f in ct) for ct in t["cts"]]
+        data = bytes.fromhex(t["hex"])
+        assert O.serialize_ciphertext_tensor(t["shape"], cts) == data, tier
+        assert O.deserialize_ciphertext_tensor(data) == (t["shape"], cts), tier
