@@ -364,6 +364,61 @@ def extras(G, fx, s, world, rank, imad_peak):
     out["decrypt"] = {"workload": "%d ciphertexts/GPU (c1^sk, nucompinv, dlog_F)" % n, "decryptions_per_s": world * n / dt,
                       "roundtrip_ok": bool(torch.equal(holder["m"], ms))}
     G.status()
+    # ---- section 8f-1: the reference's binary tensor wire format <-> SoA on the device (128x128 ciphertexts)
+    out["wire"] = wire_extra(G, fx, world, rank)
+    return out
+
+
+def wire_extra(G, fx, world, rank):
+    """serialize_ciphertext_tensor / deserialize_ciphertext_tensor of a 128x128 tensor as device kernels (wire bytes and SoA
+    batch both resident in HBM), bytes/s of the wire buffer.  On rank 0 of a 1-GPU run the compiled reference does the
+    same tensor on the host cores and its bytes are the parity check."""
+    import ctypes
+    import numpy as np
+    import torch
+    from cofhe_b200 import capi
+    n = ROWS * COLS
+    ct = synth_cts(G, fx, n, 7)
+    ref_line = None
+    if world == 1:
+        try:
+            from oracle import ref as R
+            if R.available():
+                _, nbits, k = TIERS[fx["tier"]]
+                ref = R.Reference(nbits, k)
+                ref.call("keygen")
+                ref.set_threads(len(os.sched_getaffinity(0)))
+                ds, dd, cts, wire = ref.bulk_wire(ROWS, COLS, 3, G.na, G.nc)
+                ref.close()
+                dev = torch.from_numpy(cts.view(np.int32)).to(G.device)
+                mine = G.cts_to_wire([ROWS, COLS], dev)
+                shape, back = G.wire_to_cts(wire)
+                G.status()
+                ref_line = {"serialize_s": ds / 3, "deserialize_s": dd / 3, "bytes": len(wire), "cores": len(os.sched_getaffinity(0)),
+                            "parity": bool(mine == wire and shape == [ROWS, COLS] and torch.equal(back, dev))}
+                ct = dev
+        except Exception as e:  # the checker is optional on the GPU box
+            ref_line = {"error": str(e)[:100]}
+    cap = int(G.lib.cofhe_b200_wire_bound(G.h, 2, n))
+    wbuf = torch.empty(cap, dtype=torch.uint8, device=G.device)
+    dims = (ctypes.c_uint32 * 2)(ROWS, COLS)
+    written = ctypes.c_size_t()
+    st = lambda: ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ptr = lambda t: ctypes.c_void_p(t.data_ptr())
+    def ser():
+        capi.check(G.lib.cofhe_b200_cts_to_wire(G.h, 2, dims, n, ptr(ct), ptr(wbuf), cap, ctypes.byref(written), st()), "cts_to_wire")
+    t_ser = _timed(ser, world, reps=3)
+    nbytes = written.value
+    back = torch.empty_like(ct)
+    def de():
+        capi.check(G.lib.cofhe_b200_wire_to_cts(G.h, ptr(wbuf), nbytes, 2, n, ptr(back), st()), "wire_to_cts")
+    t_de = _timed(de, world, reps=3)
+    G.status()
+    out = {"workload": "%dx%d ciphertext tensor, wire bytes and SoA batch resident in HBM" % (ROWS, COLS), "wire_bytes": nbytes,
+           "serialize_ms": t_ser * 1e3, "deserialize_ms": t_de * 1e3, "serialize_GBps": nbytes / t_ser / 1e9,
+           "deserialize_GBps": nbytes / t_de / 1e9, "roundtrip_ok": bool(torch.equal(back, ct))}
+    if ref_line:
+        out["reference_cpu"] = ref_line
     return out
 
 

@@ -119,6 +119,22 @@ class Reference:
             raise RuntimeError("ref_bulk_matadd failed")
         return dt, bufs
 
+    def bulk_wire(self, rows, cols, iters, na, nc):
+        """-> (serialise seconds, deserialise seconds, ciphertext SoA limbs, wire bytes) for `iters` passes each"""
+        n = rows * cols
+        cts = np.zeros((2, 2 * na + nc, n), dtype=np.uint32)
+        cap = 64 + n * (48 + 4 * (4 * na + 1) + 2 * (4 * nc + 1))
+        wire = np.zeros(cap, dtype=np.uint8)
+        wl, dd = ctypes.c_size_t(), ctypes.c_double()
+        self.lib.ref_bulk_wire.restype = ctypes.c_double
+        self.lib.ref_bulk_wire.argtypes = [ctypes.c_void_p, ctypes.c_uint, ctypes.c_uint, ctypes.c_uint, ctypes.c_void_p, ctypes.c_uint,
+                                           ctypes.c_uint, ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_size_t),
+                                           ctypes.POINTER(ctypes.c_double)]
+        ds = self.lib.ref_bulk_wire(self.h, rows, cols, iters, _ptr(cts), na, nc, _ptr(wire), cap, ctypes.byref(wl), ctypes.byref(dd))
+        if ds < 0:
+            raise RuntimeError("ref_bulk_wire failed")
+        return ds, dd.value, cts, wire[:wl.value].tobytes()
+
     def bulk_scal_matmul(self, n, m, p, iters=1, scalars=None, na=0, nc=0, export=False):
         bi = np.zeros((2, 2 * na + nc, n * m), dtype=np.uint32) if export else None
         bo = np.zeros((2, 2 * na + nc, n * p), dtype=np.uint32) if export else None

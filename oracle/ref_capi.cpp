@@ -284,6 +284,30 @@ double ref_bulk_matadd(void *h, unsigned rows, unsigned cols, unsigned iters,
   } catch (...) { return -1.0; }
 }
 
+// wire format: ct = encrypt_tensor(i+1) [rows x cols]; `iters` x serialize_ciphertext_tensor then `iters` x
+// deserialize_ciphertext_tensor of the bytes (reference cpu_cryptosystem.inl:322-520).  Exports the ciphertexts (SoA limbs) and
+// the serialised bytes (wire, capacity cap; *wire_len = length) so that the device kernels can be checked against them.
+// Returns the serialise time, *deser_s the deserialise time (seconds, all iterations).
+double ref_bulk_wire(void *h, unsigned rows, unsigned cols, unsigned iters, uint32_t *cts, unsigned na, unsigned nc,
+                     unsigned char *wire, size_t cap, size_t *wire_len, double *deser_s) {
+  try {
+    Ref &R = *(Ref *)h; size_t n = (size_t)rows * cols;
+    auto ct = enc_pattern(R, rows, cols, 0);
+    ct.flatten(); if (cts) export_cts(ct, n, cts, na, nc); ct.reshape({rows, cols});
+    std::string bytes;
+    auto t0 = std::chrono::steady_clock::now();
+    for (unsigned it = 0; it < iters; it++) bytes = R.cs.serialize_ciphertext_tensor(ct);
+    double ds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    t0 = std::chrono::steady_clock::now();
+    for (unsigned it = 0; it < iters; it++) { auto back = R.cs.deserialize_ciphertext_tensor(bytes); free_cts(back); }
+    if (deser_s) *deser_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (wire_len) *wire_len = bytes.size();
+    if (wire && bytes.size() <= cap) memcpy(wire, bytes.data(), bytes.size());
+    free_cts(ct);
+    return ds;
+  } catch (...) { return -1.0; }
+}
+
 // scal_matmul: ct = encrypt_tensor(i+1) [n x m], scalars s[j] (decimal strings, m*p, row-major) or the
 // benchmark pattern i+1 when scal == NULL; `iters` chained calls ct <- scal_ciphertext_tensors(pk, s, ct)
 // needs p == m when iters > 1.  Exports the input ct, the `zero` ciphertext used by the LAST call is not
