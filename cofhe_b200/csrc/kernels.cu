@@ -511,9 +511,26 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   cudaStream_t st = (cudaStream_t)stream;
   MMShape s;
   s.n = (unsigned)n; s.m = (unsigned)m; s.p = (unsigned)p; s.el = (int)el;
-  s.W = 4;
-  if (const char *w = getenv("COFHE_B200_MM_W")) { int v = atoi(w); if (v >= 2 && v <= 8) s.W = v; }
   if (ebits == 0 || ebits > 32 * el) ebits = 32 * el;
+  // Window width: every base serves p outputs, so a wider window (fewer compositions per output, a larger table per
+  // base) pays off with p.  Cost per base in compositions: p * nwin * (1 - 2^-W) for the outputs, nwin * (2^W - 1) table
+  // entries (weighted 2: measured on B200, W = 5 and 6 tie at p = 256 for 17-bit scalars, 6 wins for 128-bit ones)
+  // and nwin * W squarings for the chain; the table must also fit comfortably in HBM.
+  {
+    size_t fm = 0, tm = 0;
+    if (cudaMemGetInfo(&fm, &tm) != cudaSuccess) { cudaGetLastError(); fm = (size_t)8 << 30; }
+    const double te_bytes = 4.0 * (((3 * ctx->fastn + 1) + 3) & ~3);
+    double best = 0;
+    s.W = 4;
+    for (int W = 2; W <= 8; W++) {
+      double nwin = (double)((ebits + W - 1) / W), ent = (double)((1u << W) - 1);
+      double bytes = 2.0 * (double)n * (double)m * nwin * ent * te_bytes;
+      if (ctx->fastn && bytes > 0.4 * (double)fm && W > 2) continue;
+      double cost = (double)p * nwin * (1.0 - 1.0 / (double)(1u << W)) + 2.0 * nwin * ent + nwin * W;
+      if (best == 0 || cost < best) { best = cost; s.W = W; }
+    }
+  }
+  if (const char *w = getenv("COFHE_B200_MM_W")) { int v = atoi(w); if (v >= 2 && v <= 8) s.W = v; }
   s.nwin = (int)((ebits + s.W - 1) / s.W);
   s.chunks = 1; s.jper = (unsigned)m; s.block = 0;
   size_t no = n * p;
