@@ -27,6 +27,9 @@ SIGNATURES = {
     "cofhe_b200_status": (i32, [vp, vp]),
     "cofhe_b200_launch_count": (u64, [vp]),
     "cofhe_b200_fast_limbs": (ctypes.c_int, [vp]),
+    "cofhe_b200_scal_ciphertexts": (i32, [vp, sz, vp, vp, u32, i32, vp, i32, vp, vp]),
+    "cofhe_b200_beaver_open": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp]),
+    "cofhe_b200_beaver_close": (i32, [vp, sz, vp, vp, u32, vp, vp, vp, vp, u32, vp, vp]),
     "cofhe_b200_wire_header": (i32, [vp, sz, ctypes.POINTER(u32), vp, u32, ctypes.POINTER(sz)]),
     "cofhe_b200_wire_bound": (sz, [vp, u32, sz]),
     "cofhe_b200_wire_to_cts": (i32, [vp, vp, sz, u32, sz, vp, vp]),

@@ -207,6 +207,24 @@ __global__ void k_bcast(size_t n, int rows, const u32 *in, u32 *out) {
     default: return COFHE_B200_ESTATE;                                                              \
   })
 
+// out[.][e] = a[.][e] * b[.][e] mod 2^(32 ml)  (plaintexts are used modulo 2^k only: f has order 2^k)
+__global__ void __launch_bounds__(kBlock) k_mul_lo(size_t n, int ml, const u32 *a, const u32 *b, u32 *out) {
+  size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  u32 r[16];
+  for (int i = 0; i < ml; i++) r[i] = 0;
+  for (int i = 0; i < ml; i++) {
+    unsigned long long c = 0;
+    u32 ai = a[(size_t)i * n + e];
+    for (int j = 0; i + j < ml; j++) {
+      c += (unsigned long long)ai * b[(size_t)j * n + e] + r[i + j];
+      r[i + j] = (u32)c;
+      c >>= 32;
+    }
+  }
+  for (int i = 0; i < ml; i++) out[(size_t)i * n + e] = r[i];
+}
+
 int ensure_tmp(cofhe_b200_ctx *ctx, size_t bytes) {
   if (bytes <= ctx->tmp_bytes) return COFHE_B200_OK;
   if (ctx->d_tmp) cudaFree(ctx->d_tmp);
@@ -703,6 +721,70 @@ int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_
   rc = cofhe_b200_power_of_f(ctx, n, m, ml, fm, stream);
   if (rc != COFHE_B200_OK) return rc;
   return launch_op(ctx, 0, 1, n, out + fl * n, fm, out + fl * n, 0, nullptr, 0, 0, nullptr, 0, st);
+}
+
+int cofhe_b200_scal_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *exp, uint32_t el, int per_elem,
+                                const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!ct || !out)) || !exp || el == 0) return COFHE_B200_EINVAL;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  return launch_op(ctx, 2, 2, n, ct, ct, out, 0, exp, (int)el, per_elem, expneg, shared_neg, (cudaStream_t)stream);
+}
+
+// out = ct o x^(2^k - 1): ct + negate(x), both without randomness (the first half of a Beaver multiplication)
+static int beaver_sub(cofhe_b200_ctx *ctx, size_t n, const u32 *ct, const u32 *x, u32 *out, cudaStream_t st) {
+  int rc = launch_op(ctx, 2, 2, n, x, x, out, 0, ctx->d_exp, (ctx->k + 31) / 32, 0, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  return launch_op(ctx, 0, 2, n, ct, out, out, 0, nullptr, 0, 0, nullptr, 0, st);
+}
+
+int cofhe_b200_beaver_open(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, const uint32_t *a,
+                           const uint32_t *b, uint32_t *out1, uint32_t *out2, void *stream) {
+  if (!ctx || (n && (!ct1 || !ct2 || !a || !b || !out1 || !out2))) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme || ctx->k <= 0 || ctx->k > 32 * 64) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the exponent of negate_ciphertext_tensor: make_plaintext(-1) = 2^k - 1
+  u32 ones[64];
+  int el = (ctx->k + 31) / 32;
+  for (int i = 0; i < el; i++) ones[i] = 0xffffffffu;
+  if (ctx->k & 31) ones[el - 1] = (1u << (ctx->k & 31)) - 1;
+  CUDA_TRY(cudaMemcpyAsync(ctx->d_exp, ones, el * sizeof(u32), cudaMemcpyHostToDevice, st));
+  int rc = beaver_sub(ctx, n, ct1, a, out1, st);
+  if (rc != COFHE_B200_OK) return rc;
+  return beaver_sub(ctx, n, ct2, b, out2, st);
+}
+
+int cofhe_b200_beaver_close(cofhe_b200_ctx *ctx, size_t n, const uint32_t *pt1, const uint32_t *pt2, uint32_t ml, const uint32_t *a,
+                            const uint32_t *b, const uint32_t *c, const uint32_t *r, uint32_t el, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!pt1 || !pt2 || !a || !b || !c || !out)) || !r || ml == 0 || ml > 16 || el == 0) return COFHE_B200_EINVAL;
+  if (!ctx->fb_set || !ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  DevGuard g(ctx->device);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t cw = (size_t)2 * (2 * ctx->na + ctx->nc) * n;
+  // work: b^pt1 | a^pt2 | pt1 * pt2
+  int rc = ensure_work(ctx, (2 * cw + (size_t)ml * n) * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  u32 *t1 = ctx->d_work, *t2 = t1 + cw, *prod = t2 + cw;
+  rc = launch_op(ctx, 2, 2, n, b, b, t1, 0, pt1, (int)ml, 1, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  rc = launch_op(ctx, 2, 2, n, a, a, t2, 0, pt2, (int)ml, 1, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  k_mul_lo<<<grid_for(n), kBlock, 0, st>>>(n, (int)ml, pt1, pt2, prod);
+  rc = check_launch(ctx);
+  if (rc != COFHE_B200_OK) return rc;
+  rc = cofhe_b200_encrypt(ctx, n, prod, ml, r, el, 1, out, stream);
+  if (rc != COFHE_B200_OK) return rc;
+  rc = launch_op(ctx, 0, 2, n, t1, t2, t1, 0, nullptr, 0, 0, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  rc = launch_op(ctx, 0, 2, n, t1, c, t1, 0, nullptr, 0, 0, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  return launch_op(ctx, 0, 2, n, t1, out, out, 0, nullptr, 0, 0, nullptr, 0, st);
 }
 
 int cofhe_b200_part_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *share, uint32_t el, int share_neg,

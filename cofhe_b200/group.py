@@ -216,6 +216,38 @@ class ClassGroupB200:
                                                _stream()), "encrypt")
         return out
 
+    def scal_ciphertexts(self, ct, exps=None, shared=None):
+        """ct[e]^x on both forms: exps = per-element ints / device tensor [el, n], or shared = one int (negate: 2^k - 1)."""
+        n = ct.shape[-1]
+        out = torch.empty_like(ct)
+        if shared is not None:
+            el = max(1, (abs(shared).bit_length() + 31) // 32)
+            ex = self.ints([abs(shared)], el)
+            capi.check(self.lib.cofhe_b200_scal_ciphertexts(self.h, n, _ptr(ct), _ptr(ex), el, 0, None, int(shared < 0), _ptr(out),
+                                                            _stream()), "scal_ciphertexts")
+        else:
+            ex = exps if torch.is_tensor(exps) else self.ints([abs(int(e)) for e in exps], max(1, max((abs(int(e)).bit_length() + 31) // 32 for e in exps)))
+            sg = None if torch.is_tensor(exps) else torch.tensor([1 if e < 0 else 0 for e in exps], dtype=torch.uint8, device=self.device)
+            capi.check(self.lib.cofhe_b200_scal_ciphertexts(self.h, n, _ptr(ct), _ptr(ex), ex.shape[0], 1, _ptr(sg), 0, _ptr(out),
+                                                            _stream()), "scal_ciphertexts")
+        return out
+
+    def beaver_open(self, ct1, ct2, a, b):
+        """(ct1 - a, ct2 - b) as ciphertexts: SMPCCipherTextMultiplier's masking step, on the device."""
+        o1, o2 = torch.empty_like(ct1), torch.empty_like(ct2)
+        capi.check(self.lib.cofhe_b200_beaver_open(self.h, ct1.shape[-1], _ptr(ct1), _ptr(ct2), _ptr(a), _ptr(b), _ptr(o1), _ptr(o2),
+                                                   _stream()), "beaver_open")
+        return o1, o2
+
+    def beaver_close(self, pt1, pt2, a, b, c, r):
+        """pt1*b + pt2*a + c + Enc_r(pt1*pt2): pt1, pt2 device tensors [ml, n] (the opened values), r one int."""
+        n = a.shape[-1]
+        rr = self.ints([r], self.el_r)
+        out = torch.empty_like(a)
+        capi.check(self.lib.cofhe_b200_beaver_close(self.h, n, _ptr(pt1), _ptr(pt2), pt1.shape[0], _ptr(a), _ptr(b), _ptr(c), _ptr(rr),
+                                                    rr.shape[0], _ptr(out), _stream()), "beaver_close")
+        return out
+
     def _host_exp(self, e):
         el = max(1, (abs(int(e)).bit_length() + 31) // 32)
         return L.ints_to_limbs([abs(int(e))], el)[:, 0].copy(), el

@@ -88,6 +88,25 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out);
 
+/* out[e] = ct[e]^x (both forms), no re-randomisation: the 1-D branch of CPUCryptoSystem::scal_ciphertext_tensors and
+ * scal_ciphertext_vector (reference include/x86_64/cpu_cryptosystem_tensor_ops.inl:280-340, cpu_cryptosystem_vector_ops.inl
+ * :122-242) with per_elem != 0, negate_ciphertext_tensor (:135-195) with the shared exponent 2^k - 1.  Exponent
+ * arguments as cofhe_b200_nupow. */
+int cofhe_b200_scal_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *exp, uint32_t el, int per_elem,
+                                const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream);
+
+/* Beaver-triple ciphertext x ciphertext multiplication, the device side of
+ * SMPCCipherTextMultiplier::handle_vector_ciphertext_mul (reference include/smpc/ciphertext_multiplications.hpp:115-160),
+ * as two fused pipelines around the network round that opens the masked operands (needs set_scheme / set_bases):
+ *   open : out1 = ct1 + negate(a), out2 = ct2 + negate(b)             (2 negate + 2 add, :127-130)
+ *   close: out  = pt1 * b + pt2 * a + c + encrypt_tensor(pt1 * pt2)   (2 scal + encrypt + 3 add, :133-139)
+ * pt1, pt2: the opened plaintexts [ml][n]; r: the ONE randomness of the encrypt_tensor call (device memory, el limbs, as cofhe_b200_encrypt with shared_r);
+ * (a, b, c): the triple, ciphertext batches.  Everything stays in device memory between the steps. */
+int cofhe_b200_beaver_open(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, const uint32_t *a,
+                           const uint32_t *b, uint32_t *out1, uint32_t *out2, void *stream);
+int cofhe_b200_beaver_close(cofhe_b200_ctx *ctx, size_t n, const uint32_t *pt1, const uint32_t *pt2, uint32_t ml, const uint32_t *a,
+                            const uint32_t *b, const uint32_t *c, const uint32_t *r, uint32_t el, uint32_t *out, void *stream);
+
 /* ---- Binary tensor wire format <-> SoA batches on the device.
  * The format is the one of CPUCryptoSystem::serialize_ciphertext_tensor / deserialize_ciphertext_tensor (reference
  * include/x86_64/cpu_cryptosystem.inl:322-391 and :393-520): u32 ndim | u32 dims[ndim] | u64 table[6n] | magnitudes;

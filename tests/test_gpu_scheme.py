@@ -118,3 +118,48 @@ def test_mixed_sequence_keeps_state(systems):
     m = [2 * (i + 1) for i in range(12)]
     want = [sum(m[i * 3 + j] * sc[j * 2 + k] for j in range(3)) % (1 << G.k) for i in range(4) for k in range(2)]
     assert got == want
+
+
+def test_beaver_pipeline_and_scal(systems, tier):
+    """Ciphertext x ciphertext through a Beaver triple (reference include/smpc/ciphertext_multiplications.hpp:115-160),
+    the two device pipelines against the oracle's composition of the same reference operations, and the decrypted
+    product; plus the ciphertext-level scal / negate entry point."""
+    G = systems(tier)
+    P = O.Params.from_dict({k: (I(v) if isinstance(v, list) else v if isinstance(v, bool) else int(v)) for k, v in tier["params"].items()})
+    k, sk, pk = P.k, int(tier["sk"]), I(tier["pk"])
+    rng = random.Random(77)
+    n = 9 if tier["tier"] != "t1" else 3  # the oracle's exponentiations at 2053 bits are slow in Python
+    M = 1 << k
+    enc = lambda m: O.encrypt(P, pk, m % M, rng.randrange(1, P.exponent_bound))
+    xs, ys = [rng.randrange(M) for _ in range(n)], [rng.randrange(M) for _ in range(n)]
+    xs[0], ys[1] = 0, 1
+    ta, tb = [rng.randrange(10) for _ in range(n)], [rng.randrange(10) for _ in range(n)]  # generate_random_beavers_triplet: bound 10
+    ct1, ct2 = [enc(x) for x in xs], [enc(y) for y in ys]
+    A, B, C = [enc(a) for a in ta], [enc(b) for b in tb], [enc(a * b) for a, b in zip(ta, tb)]
+    neg = M - 1
+    # --- scal / negate entry point
+    dA = G.cts(A)
+    assert G.cts_out(G.scal_ciphertexts(dA, shared=neg)) == [O.scal_ciphertext(c, neg) for c in A]
+    ex = [rng.randrange(M) for _ in range(n)]
+    assert G.cts_out(G.scal_ciphertexts(dA, exps=ex)) == [O.scal_ciphertext(c, e) for c, e in zip(A, ex)]
+    # --- open
+    o1, o2 = G.beaver_open(G.cts(ct1), G.cts(ct2), dA, G.cts(B))
+    G.status()
+    w1 = [O.add_ciphertexts(c, O.scal_ciphertext(a, neg)) for c, a in zip(ct1, A)]
+    w2 = [O.add_ciphertexts(c, O.scal_ciphertext(b, neg)) for c, b in zip(ct2, B)]
+    assert G.cts_out(o1) == w1 and G.cts_out(o2) == w2
+    p1 = G.decrypt(o1, sk)
+    p2 = G.decrypt(o2, sk)
+    assert G.ints_out(p1) == [(x - a) % M for x, a in zip(xs, ta)]
+    # --- close
+    r = rng.randrange(1, P.exponent_bound)
+    res = G.beaver_close(p1, p2, dA, G.cts(B), G.cts(C), r)
+    G.status()
+    e1, e2 = G.ints_out(p1), G.ints_out(p2)
+    want = []
+    for i in range(n):
+        acc = O.add_ciphertexts(O.scal_ciphertext(B[i], e1[i]), O.scal_ciphertext(A[i], e2[i]))
+        acc = O.add_ciphertexts(acc, C[i])
+        want.append(O.add_ciphertexts(acc, O.encrypt(P, pk, (e1[i] * e2[i]) % M, r)))
+    assert G.cts_out(res) == want
+    assert G.ints_out(G.decrypt(res, sk)) == [(x * y) % M for x, y in zip(xs, ys)]
