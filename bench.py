@@ -364,6 +364,24 @@ def extras(G, fx, s, world, rank, imad_peak):
     out["decrypt"] = {"workload": "%d ciphertexts/GPU (c1^sk, nucompinv, dlog_F)" % n, "decryptions_per_s": world * n / dt,
                       "roundtrip_ok": bool(torch.equal(holder["m"], ms))}
     G.status()
+    # ---- section 8f-2: Beaver-triple ciphertext x ciphertext multiplication (device side, without the network round)
+    try:
+        A, B = holder["ct"], G.encrypt(ms, 4242)
+        C = G.add_ciphertexts(A, B)  # any ciphertext batch serves as c for timing; correctness is in tests/test_gpu_scheme.py
+        hb = {}
+        def bopen():
+            hb["o"] = G.beaver_open(holder["ct"], B, A, B)
+        t_open = _timed(bopen, world, reps=1)
+        def bclose():
+            hb["r"] = G.beaver_close(ms, ms, A, B, C, 31337)
+        t_close = _timed(bclose, world, reps=1)
+        out["beaver"] = {"workload": "%d ciphertext pairs/GPU: open (2 negate + 2 add) + close (2 scal + encrypt_tensor + 3 add), k = %d bit exponents; "
+                                     "the threshold-decryption round between them is not included" % (n, k),
+                         "open_ms": t_open * 1e3, "close_ms": t_close * 1e3, "ct_mults_per_s": world * n / (t_open + t_close),
+                         "form_exps_per_s": world * n * 8 / (t_open + t_close)}
+        G.status()
+    except Exception as e:
+        out["beaver"] = {"error": str(e)[:120]}
     # ---- section 8f-1: the reference's binary tensor wire format <-> SoA on the device (128x128 ciphertexts)
     out["wire"] = wire_extra(G, fx, world, rank)
     return out
