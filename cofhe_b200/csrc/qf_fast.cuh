@@ -90,7 +90,7 @@ QF_HD float rcp_approx(float x) {
 // EXACT == true (the operands fit the leading limb: last rounds of a full gcd): no test, cofactors may grow up to
 // ah / r_j, so they are formed in 64 bits and the run stops before one reaches 2^30.
 #ifndef QF_HG_PAIRS
-#define QF_HG_PAIRS 4
+#define QF_HG_PAIRS 5
 #endif
 template <bool EXACT>
 QF_HD Mat2 hgcd32(u32 ah, u32 bh, u32 min_r) {
@@ -126,7 +126,7 @@ QF_HD Mat2 hgcd32(u32 ah, u32 bh, u32 min_r) {
     j++;                                                                                               \
   }
   // A truncated run is capped at QF_HG_PAIRS double steps: the lanes of a warp wait for each other at the end of a
-  // round, and the number of steps Jebelean's test lets through varies (9 +- 3), so a cap just below the mean keeps
+  // round, and the number of steps Jebelean's test lets through varies (9 +- 3), so a cap near the mean (measured best at 5 double steps: 3, 4, 6, 8 are 1-9 % slower) keeps
   // nearly all lanes busy for the whole round; any prefix of the Euclidean sequence is a valid round.
   for (int it = 0; EXACT || it < QF_HG_PAIRS; it++) {
     swapped = false;
