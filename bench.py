@@ -382,9 +382,56 @@ def extras(G, fx, s, world, rank, imad_peak):
         G.status()
     except Exception as e:
         out["beaver"] = {"error": str(e)[:120]}
+    # ---- the reference's own CPU code on bounded samples of the same workloads, same run (rank 0 of a 1-GPU run)
+    if world == 1:
+        out["reference_cpu"] = reference_extras(G, fx)
     # ---- section 8f-1: the reference's binary tensor wire format <-> SoA on the device (128x128 ciphertexts)
     out["wire"] = wire_extra(G, fx, world, rank)
     return out
+
+
+def reference_extras(G, fx):
+    """Bounded samples of configs 3-5 on the UNMODIFIED reference (oracle/_ref) with all host threads, and the GPU on the
+    reference's own inputs where the outputs are comparable (encryption with the reference's (m, r), part-decryption)."""
+    import numpy as np
+    import torch
+    try:
+        from oracle import ref as R
+        if not R.available():
+            return {"unavailable": "oracle/_ref not loadable"}
+        _, nbits, k = TIERS[fx["tier"]]
+        ref = R.Reference(nbits, k)
+        ks = ref.call("keygen")
+        sk, pk = int(ks[0]), tuple(int(x) for x in ks[1:4])
+        cores = len(os.sched_getaffinity(0))
+        ref.set_threads(cores)
+        res = {"cores": cores, "kind": "reference"}
+        dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.int32)).to(G.device)
+        # config 5a: scalar x ciphertext matmul, 2 ct rows of the 256-wide problem, benchmark scalars i+1
+        rows, m, p = 2, 256, 256
+        dt, _, _ = ref.bulk_scal_matmul(rows, m, p)
+        res["scal_matmul"] = {"sample": "%dx%d . %dx%d, pattern i+1, one call" % (rows, m, m, p), "seconds": dt,
+                              "form_exps_per_s": 2 * rows * m * p / dt}
+        # config 3 mode B: own r per ciphertext; the GPU repeats it with the reference's (m, r) under the reference's pk
+        cnt = 4096
+        dt, mo, ro, co = ref.bulk_encrypt(cnt, G.ml, G.el_r, G.na, G.nc)
+        G.set_bases(fx["h"], pk, fx["bound"].bit_length())
+        mine = G.encrypt(dev(mo), dev(ro))
+        G.status()
+        res["encrypt"] = {"sample": "%d ciphertexts, own r each" % cnt, "seconds": dt, "encryptions_per_s": cnt / dt,
+                          "gpu_parity": bool(torch.equal(mine, dev(co)))}
+        # config 4: part_decrypt_tensor with one share
+        cnt = 2048
+        dt, co, do = ref.bulk_part_decrypt(cnt, sk, G.na, G.nc)
+        mine = G.part_decrypt(dev(co), sk)
+        G.status()
+        res["part_decrypt"] = {"sample": "%d ciphertexts, %d-bit share" % (cnt, sk.bit_length()), "seconds": dt,
+                               "form_exps_per_s": cnt / dt, "gpu_parity": bool(torch.equal(mine, dev(do)))}
+        G.set_bases(fx["h"], fx["pk"], fx["bound"].bit_length())
+        ref.close()
+        return res
+    except Exception as e:
+        return {"error": str(e)[:160]}
 
 
 def wire_extra(G, fx, world, rank):
