@@ -209,3 +209,29 @@ def test_scal_matmul_degenerate(groups):
     assert G.cts_out(G.scal_matmul(G.cts(cts), s[:4], 1, 4, 1, G.cts([zero]))) == want
     assert G.cts_out(G.scal_matmul(G.cts(cts), s[4:], 1, 4, 1, G.cts([zero]))) == [zero]
     G.status()
+
+
+def test_add_host_staged_ranges(groups, monkeypatch):
+    """Pageable host buffers take the staged pipelines: one lane per form block (default) and element ranges over four
+    lanes (COFHE_B200_HOST_CHUNKS); ragged sizes, results identical to the device-resident call."""
+    from cofhe_b200 import limbs as L
+    t = load_golden("ref_t0.json")
+    G = groups(int(t["params"]["Delta"]))
+    rng = random.Random(21)
+    h = I(t["params"]["h"])
+    base = [O.power(h, rng.getrandbits(50) + 1) for _ in range(20)]
+    n = 2500
+    c1 = [(base[rng.randrange(20)], base[rng.randrange(20)]) for _ in range(n)]
+    c2 = [(base[rng.randrange(20)], base[rng.randrange(20)]) for _ in range(n)]
+    want = G.cts_out(G.add_ciphertexts(G.cts(c1), G.cts(c2)))
+    G.status()
+    assert want[:50] == [O.add_ciphertexts(x, y) for x, y in zip(c1[:50], c2[:50])]
+    h1, h2 = L.cts_to_limbs(c1, G.na, G.nc), L.cts_to_limbs(c2, G.na, G.nc)
+    for chunks in (None, "1", "3", "7"):
+        if chunks is None:
+            monkeypatch.delenv("COFHE_B200_HOST_CHUNKS", raising=False)
+        else:
+            monkeypatch.setenv("COFHE_B200_HOST_CHUNKS", chunks)
+        out = np.zeros_like(h1)
+        G.add_ciphertexts_host(h1, h2, out)
+        assert L.limbs_to_cts(out, G.na, G.nc) == want, chunks
