@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
+#include <mutex>
 #include <new>
 #include <utility>
 
@@ -53,6 +54,15 @@ struct cofhe_b200_ctx {
   u32 *d_fb_tab;      // window tables of h and pk (fast tiers)
   MMShape fb;
   int fb_set;
+  // One context may be shared by threads and streams (include/cofhe_b200.h "Threads and streams"): entry points
+  // serialise on `mu`; when the caller's stream changes, the new stream is ordered after the previous one, because the
+  // scratch above is shared by all calls.
+  std::recursive_mutex mu;
+  cudaStream_t last;
+  bool busy;
+  cudaEvent_t order;
+  // tuning knobs (cofhe_b200_set_option; the COFHE_B200_* environment variables are read once, at creation)
+  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace; } opt;
 };
 
 namespace {
@@ -133,7 +143,7 @@ __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, s
     u32 e = bail[i];
     size_t y = e / n, idx = e % n, off = y * form_limbs(s) * n;
     int c;
-    if (op == 0) c = op_compose<CAP>(*G, s, n, idx, in1 + off, in2 + off, out + off, neg2 != 0);
+    if (op == 0) c = op_compose<CAP>(*G, s, n, idx, in1 + off, in2 + off, out + off, (neg2 & 1) != 0, (neg2 & 2) != 0);
     else if (op == 1) c = op_square<CAP>(*G, s, n, idx, in1 + off, out + off);
     else c = op_pow<CAP>(*G, s, n, idx, in1 + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
     if (c) atomicMax(err, c);
@@ -160,9 +170,15 @@ __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, s
 #define FAST_HAVE(na) ((na) == 2 || (na) == 4 || (na) == 7 || (na) == 11)
 #endif
 int fast_cap(int fn) { return fn == 11 ? 48 : 32; }
-int fast_n_for(u32 na, int cap) {
+int fast_n_for(u32 na, int cap, bool no_fast) {
   bool have = FAST_HAVE(na) && fast_cap((int)na) == cap;
-  return have && !getenv("COFHE_B200_NO_FAST") ? (int)na : 0;
+  return have && !no_fast ? (int)na : 0;
+}
+long env_opt(const char *name, long lo, long hi) {
+  const char *v = getenv(name);
+  if (!v) return -1;
+  long x = atol(v);
+  return x >= lo && x <= hi ? x : -1;
 }
 
 int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
@@ -278,7 +294,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
   unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
-  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, op, in1, in2, out, neg2 & 1, exp, el,
+  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, op, in1, in2, out, neg2, exp, el,
                                                           per_elem, expneg, shared_neg, ctx->d_bail, cnt, cnt_next, ctx->d_err))
   return check_launch(ctx);
 }
@@ -355,6 +371,33 @@ struct DevGuard {
   ~DevGuard() { if (ok && prev >= 0) cudaSetDevice(prev); }
 };
 
+// Entry guard of every call that issues work on `st`: the context lock, the device, and stream ordering.
+struct Enter {
+  std::unique_lock<std::recursive_mutex> lk;
+  DevGuard g;
+  bool ok;
+  Enter(cofhe_b200_ctx *ctx, cudaStream_t st) : lk(ctx->mu), g(ctx->device), ok(g.ok) {
+    if (!ok) return;
+    if (ctx->busy && ctx->last != st) {
+      if (cudaEventRecord(ctx->order, ctx->last) != cudaSuccess || cudaStreamWaitEvent(st, ctx->order, 0) != cudaSuccess) {
+        cudaGetLastError();
+        ok = false;
+      }
+    }
+    ctx->last = st;
+    ctx->busy = true;
+  }
+};
+// Entry guard of the blocking _host calls (internal streams): waits for whatever the context still has in flight.
+struct EnterHost {
+  std::unique_lock<std::recursive_mutex> lk;
+  DevGuard g;
+  bool ok;
+  explicit EnterHost(cofhe_b200_ctx *ctx) : lk(ctx->mu), g(ctx->device), ok(g.ok) {
+    if (ok && ctx->busy) { ok = cudaStreamSynchronize(ctx->last) == cudaSuccess; ctx->busy = false; }
+  }
+};
+
 }  // namespace
 
 extern "C" {
@@ -375,6 +418,16 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   if (getenv("COFHE_B200_STACK")) cudaDeviceSetLimit(cudaLimitStackSize, (size_t)atoi(getenv("COFHE_B200_STACK")));
   cofhe_b200_ctx *ctx = new (std::nothrow) cofhe_b200_ctx();
   if (!ctx) return COFHE_B200_ENOMEM;
+  ctx->last = nullptr; ctx->busy = false; ctx->order = nullptr;
+  ctx->opt.no_fast = getenv("COFHE_B200_NO_FAST") ? 1 : 0;
+  ctx->opt.mm_w = env_opt("COFHE_B200_MM_W", 2, 8);
+  ctx->opt.mm_chunks = env_opt("COFHE_B200_MM_CHUNKS", 1, 1 << 20);
+  ctx->opt.mm_block = env_opt("COFHE_B200_MM_BLOCK", 128, 512);
+  ctx->opt.fb_w = env_opt("COFHE_B200_FB_W", 2, 10);
+  ctx->opt.host_staged = getenv("COFHE_B200_HOST_STAGED") ? 1 : 0;
+  ctx->opt.host_loadc = getenv("COFHE_B200_HOST_LOADC") ? 1 : 0;
+  ctx->opt.host_chunks = env_opt("COFHE_B200_HOST_CHUNKS", 0, 64);
+  ctx->opt.host_trace = getenv("COFHE_B200_HOST_TRACE") ? 1 : 0;
   ctx->device = device;
   ctx->sms = 0;
   if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); ctx->sms = 0; }
@@ -386,7 +439,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->launches = 0;
   ctx->dbits = (u32)dbits;
   for (u32 i = 0; i < n; i++) ctx->h_absd[i] = abs_delta[i];
-  ctx->fastn = fast_n_for(ctx->na, cap);
+  ctx->fastn = fast_n_for(ctx->na, cap, ctx->opt.no_fast != 0);
   ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
   memset(ctx->lane, 0, sizeof(ctx->lane));
   ctx->d_stage = nullptr; ctx->stage_bytes = 0;
@@ -415,6 +468,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
                               cudaMalloc(&ctx->d_nbail, 2 * sizeof(int)) != cudaSuccess ||
                               cudaMalloc(&ctx->d_exp, 64 * sizeof(u32)) != cudaSuccess ||
                               cudaMemset(ctx->d_nbail, 0, 2 * sizeof(int)) != cudaSuccess ||
+                              cudaEventCreateWithFlags(&ctx->order, cudaEventDisableTiming) != cudaSuccess ||
                               cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking) != cudaSuccess))
     rc = COFHE_B200_ECUDA;
   if (rc != COFHE_B200_OK) { cofhe_b200_destroy(ctx); return rc; }
@@ -437,6 +491,7 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
   if (ctx->d_fb_tab) cudaFree(ctx->d_fb_tab);
   if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
+  if (ctx->order) cudaEventDestroy(ctx->order);
   for (auto &L : ctx->lane) {
     if (L.d_bail) cudaFree(L.d_bail);
     if (L.d_nbail) cudaFree(L.d_nbail);
@@ -455,12 +510,13 @@ int cofhe_b200_shape(const cofhe_b200_ctx *ctx, uint32_t *na, uint32_t *nc, uint
 
 int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream) {
   if (!ctx) return COFHE_B200_EINVAL;
-  DevGuard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  Enter g(ctx, st);
   if (!g.ok) return COFHE_B200_ECUDA;
   int h = 0;
-  cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaMemcpyAsync(&h, ctx->d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
+  ctx->busy = false;  // everything the context issued is ordered before `st`, which is idle now
   if (h) {
     CUDA_TRY(cudaMemsetAsync(ctx->d_err, 0, sizeof(int), st));
     CUDA_TRY(cudaStreamSynchronize(st));
@@ -472,11 +528,23 @@ int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream) {
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx) { return ctx ? ctx->fastn : 0; }
 
+int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
+  if (!ctx || !name) return COFHE_B200_EINVAL;
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  struct { const char *n; long *p; } tab[] = {
+      {"mm_w", &ctx->opt.mm_w}, {"mm_chunks", &ctx->opt.mm_chunks}, {"mm_block", &ctx->opt.mm_block}, {"fb_w", &ctx->opt.fb_w},
+      {"host_staged", &ctx->opt.host_staged}, {"host_loadc", &ctx->opt.host_loadc}, {"host_chunks", &ctx->opt.host_chunks},
+      {"host_trace", &ctx->opt.host_trace}};
+  for (auto &t : tab)
+    if (!strcmp(t.n, name)) { *t.p = value; return COFHE_B200_OK; }
+  return COFHE_B200_EINVAL;
+}
+
 int cofhe_b200_nucomp(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f1, const uint32_t *f2, uint32_t *out, int negf2,
                       void *stream) {
   if (!ctx || (n && (!f1 || !f2 || !out))) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   return launch_op(ctx, 0, 1, n, f1, f2, out, negf2, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
@@ -484,7 +552,7 @@ int cofhe_b200_nucomp(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f1, const u
 int cofhe_b200_nudupl(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *out, void *stream) {
   if (!ctx || (n && (!f || !out))) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   return launch_op(ctx, 1, 1, n, f, f, out, 0, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
@@ -493,7 +561,7 @@ int cofhe_b200_reduce(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t
                       void *stream) {
   if (!ctx || (n && (!f || !out)) || na_in == 0 || nc_in == 0) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   Shape sin{(int)na_in, (int)nc_in}, sout{(int)ctx->na, (int)ctx->nc};
   CAP_DISPATCH(ctx->cap, k_reduce<CAP><<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>((const Group<CAP> *)ctx->d_group, sin,
@@ -505,7 +573,7 @@ int cofhe_b200_nupow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, const uin
                      const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream) {
   if (!ctx || (n && (!f || !out || !exp)) || el == 0) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   return launch_op(ctx, 2, 1, n, f, f, out, 0, exp, (int)el, per_elem, expneg, shared_neg, (cudaStream_t)stream);
 }
@@ -514,7 +582,7 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
                                void *stream) {
   if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   return launch_op(ctx, 0, 2, n, ct1, ct2, out, 0, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
 }
@@ -524,7 +592,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   if (!ctx || el == 0 || !init || ((n && p) && !out) || ((n && m) && !ct) || ((m && p) && !scal)) return COFHE_B200_EINVAL;
   if (n == 0 || p == 0) return COFHE_B200_OK;
   if ((n * p) >> 30 || (n * m) >> 30 || (m * p) >> 30) return COFHE_B200_EINVAL;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   MMShape s;
@@ -548,7 +616,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
       if (best == 0 || cost < best) { best = cost; s.W = W; }
     }
   }
-  if (const char *w = getenv("COFHE_B200_MM_W")) { int v = atoi(w); if (v >= 2 && v <= 8) s.W = v; }
+  if (ctx->opt.mm_w >= 2) s.W = (int)ctx->opt.mm_w;
   s.nwin = (int)((ebits + s.W - 1) / s.W);
   s.chunks = 1; s.jper = (unsigned)m; s.block = 0;
   size_t no = n * p;
@@ -563,6 +631,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
     size_t chmax = m / 2 < 1 ? 1 : m / 2;
     if (chmax > 64) chmax = 64;
     s.block = pick_block(2 * no * chmax, ctx->sms);  // full blocks whenever chunking can fill the machine with them
+    if (ctx->opt.mm_block == 128 || ctx->opt.mm_block == 256 || ctx->opt.mm_block == 512) s.block = (int)ctx->opt.mm_block;
     const size_t slots = sms * (size_t)(512 / s.block);
     const size_t bpc = 2 * ((no + s.block - 1) / s.block);  // blocks per chunk
     double best = 0;
@@ -573,7 +642,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
       if (c == 1 || cost < best) { best = cost; ch = c; }
     }
   }
-  if (const char *c = getenv("COFHE_B200_MM_CHUNKS")) { int v = atoi(c); if (v >= 1 && (size_t)v <= m) ch = (size_t)v; }
+  if (ctx->opt.mm_chunks >= 1 && (size_t)ctx->opt.mm_chunks <= m) ch = (size_t)ctx->opt.mm_chunks;
   s.jper = (unsigned)((m + ch - 1) / ch);
   s.chunks = (unsigned)((m + s.jper - 1) / s.jper);
   size_t tw = mm_tab_words(ctx, s), pw = mm_part_words(ctx, s);
@@ -588,7 +657,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
 // ---- CL_HSM2k scheme level ---------------------------------------------------------------------------------------
 int cofhe_b200_set_scheme(cofhe_b200_ctx *ctx, uint32_t k, const uint32_t *N, uint32_t nN) {
   if (!ctx || !N || nN == 0 || k == 0 || k > 256) return COFHE_B200_EINVAL;
-  DevGuard g(ctx->device);
+  EnterHost g(ctx);
   if (!g.ok) return COFHE_B200_ECUDA;
   int n = bn_norm(N, (int)nN);
   if (n == 0) return COFHE_B200_EINVAL;
@@ -634,7 +703,7 @@ int cofhe_b200_power_of_f(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint
   if (!ctx || (n && (!m || !out)) || ml == 0) return COFHE_B200_EINVAL;
   if (!ctx->d_scheme) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   Shape s{(int)ctx->na, (int)ctx->nc};
   SCHEME_DISPATCH(ctx, k_power_of_f<KL, CAP><<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(
@@ -646,7 +715,7 @@ int cofhe_b200_dlog(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *
   if (!ctx || (n && (!m || !f)) || ml == 0) return COFHE_B200_EINVAL;
   if (!ctx->d_scheme) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   Shape s{(int)ctx->na, (int)ctx->nc};
   SCHEME_DISPATCH(ctx, k_dlog<KL, CAP><<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(
@@ -656,7 +725,7 @@ int cofhe_b200_dlog(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *
 
 int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t *pk, uint32_t ebits) {
   if (!ctx || !h || ebits == 0) return COFHE_B200_EINVAL;
-  DevGuard g(ctx->device);
+  EnterHost g(ctx);
   if (!g.ok) return COFHE_B200_ECUDA;
   size_t fl = 2 * ctx->na + ctx->nc;
   if (!ctx->d_fb_bases && cudaMalloc(&ctx->d_fb_bases, 2 * fl * sizeof(u32)) != cudaSuccess) return COFHE_B200_ENOMEM;
@@ -666,7 +735,7 @@ int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t 
   MMShape s;
   s.n = 1; s.m = 1; s.p = 0; s.chunks = 1; s.jper = 1; s.block = 0;
   s.W = 8;
-  if (const char *w = getenv("COFHE_B200_FB_W")) { int v = atoi(w); if (v >= 2 && v <= 10) s.W = v; }
+  if (ctx->opt.fb_w >= 2) s.W = (int)ctx->opt.fb_w;
   s.el = (int)((ebits + 31) / 32);
   s.nwin = (32 * s.el + s.W - 1) / s.W;
   ctx->fb = s;
@@ -683,7 +752,7 @@ int cofhe_b200_fixed_base_pow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *exp
   if (!ctx || (n && (!exps || !out)) || el == 0 || n >> 30) return COFHE_B200_EINVAL;
   if (!ctx->fb_set) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   MMShape s = ctx->fb;
   s.p = (unsigned)n;
@@ -697,7 +766,7 @@ int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_
   if (!ctx || (n && (!m || !out)) || !r || ml == 0 || el == 0 || n >> 30) return COFHE_B200_EINVAL;
   if (!ctx->fb_set || !ctx->d_scheme) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   size_t fl = 2 * ctx->na + ctx->nc;
@@ -727,7 +796,7 @@ int cofhe_b200_scal_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *c
                                 const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream) {
   if (!ctx || (n && (!ct || !out)) || !exp || el == 0) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   return launch_op(ctx, 2, 2, n, ct, ct, out, 0, exp, (int)el, per_elem, expneg, shared_neg, (cudaStream_t)stream);
 }
@@ -744,7 +813,7 @@ int cofhe_b200_beaver_open(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, c
   if (!ctx || (n && (!ct1 || !ct2 || !a || !b || !out1 || !out2))) return COFHE_B200_EINVAL;
   if (!ctx->d_scheme || ctx->k <= 0 || ctx->k > 32 * 64) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   // the exponent of negate_ciphertext_tensor: make_plaintext(-1) = 2^k - 1
@@ -763,7 +832,7 @@ int cofhe_b200_beaver_close(cofhe_b200_ctx *ctx, size_t n, const uint32_t *pt1, 
   if (!ctx || (n && (!pt1 || !pt2 || !a || !b || !c || !out)) || !r || ml == 0 || ml > 16 || el == 0) return COFHE_B200_EINVAL;
   if (!ctx->fb_set || !ctx->d_scheme) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   size_t cw = (size_t)2 * (2 * ctx->na + ctx->nc) * n;
@@ -791,7 +860,7 @@ int cofhe_b200_part_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, c
                             uint32_t *out, void *stream) {
   if (!ctx || (n && (!ct || !out)) || !share || el == 0 || el > 64) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaMemcpyAsync(ctx->d_exp, share, el * sizeof(u32), cudaMemcpyHostToDevice, st));
@@ -803,7 +872,7 @@ int cofhe_b200_combine(cofhe_b200_ctx *ctx, size_t n, uint32_t t, const uint32_t
   if (!ctx || (n && (!ct || !ds || !m)) || t == 0 || ml == 0) return COFHE_B200_EINVAL;
   if (!ctx->d_scheme) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   size_t fl = 2 * ctx->na + ctx->nc;
@@ -828,7 +897,7 @@ int cofhe_b200_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const 
   if (!ctx || (n && (!ct || !m)) || !sk || el == 0 || el > 64 || ml == 0) return COFHE_B200_EINVAL;
   if (!ctx->d_scheme) return COFHE_B200_ESTATE;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   size_t fl = 2 * ctx->na + ctx->nc;
@@ -870,7 +939,7 @@ void *cofhe_b200_stream(cofhe_b200_ctx *ctx) { return ctx ? (void *)ctx->xfer : 
 int cofhe_b200_upload(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream) {
   if (!ctx || (bytes && (!dst || !src))) return COFHE_B200_EINVAL;
   if (bytes == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
   return COFHE_B200_OK;
@@ -878,7 +947,7 @@ int cofhe_b200_upload(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t by
 int cofhe_b200_download(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream) {
   if (!ctx || (bytes && (!dst || !src))) return COFHE_B200_EINVAL;
   if (bytes == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   return COFHE_B200_OK;
@@ -920,7 +989,7 @@ int cofhe_b200_wire_to_cts(cofhe_b200_ctx *ctx, const uint8_t *wire, size_t byte
   size_t head = 4 + 4 * (size_t)ndim;
   if (bytes < head + 48 * n) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   WireShape s{(int)ctx->na, (int)ctx->nc, n};
   unsigned blocks = (unsigned)((6 * n + kWireBlock - 1) / kWireBlock);
@@ -935,7 +1004,7 @@ int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *d
   size_t cnt = 1;
   for (uint32_t i = 0; i < ndim; i++) cnt *= dims[i];
   if (cnt != n) return COFHE_B200_EINVAL;
-  DevGuard g(ctx->device);
+  Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   size_t head = 4 + 4 * (size_t)ndim;
@@ -1010,7 +1079,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
                                     uint32_t *out) {
   if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
-  DevGuard g(ctx->device);
+  EnterHost g(ctx);
   if (!g.ok) return COFHE_B200_ECUDA;
   const size_t rows = (size_t)2 * (2 * ctx->na + ctx->nc);
   size_t bytes = rows * n * sizeof(u32);
@@ -1020,7 +1089,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   // redundant and recomputed on the device) and writes the result rows straight back, so the transfer of one warp
   // overlaps the arithmetic of the others inside a single launch.  Measured on B200 against copy-engine staging,
   // which pays a slow start after every idle gap: 0.29 ms vs 0.37-0.58 ms per 128x128 add.
-  if (ctx->fastn && !getenv("COFHE_B200_HOST_STAGED")) {
+  if (ctx->fastn && !ctx->opt.host_staged) {
     cudaPointerAttributes a1, a2, a3;
     bool pinned = cudaPointerGetAttributes(&a1, ct1) == cudaSuccess && cudaPointerGetAttributes(&a2, ct2) == cudaSuccess &&
                   cudaPointerGetAttributes(&a3, out) == cudaSuccess && a1.type == cudaMemoryTypeHost &&
@@ -1030,7 +1099,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
     if (pinned) {
       rc = lane_ready(ctx, 0);
       if (rc != COFHE_B200_OK) return rc;
-      int flags = getenv("COFHE_B200_HOST_LOADC") ? 0 : 2;  // 2: operands without c rows
+      int flags = ctx->opt.host_loadc ? 0 : 2;  // 2: operands without c rows
       rc = with_lane(ctx, 0, [&](cudaStream_t s2) {
         return launch_op(ctx, 0, 2, n, (const u32 *)a1.devicePointer, (const u32 *)a2.devicePointer, (u32 *)a3.devicePointer, flags,
                          nullptr, 0, 0, nullptr, 0, s2);
@@ -1051,8 +1120,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   // so its transfers are plain 1-D copies at full PCIe rate, and the c2 upload overlaps the c1 kernels).  Element
   // ranges (COFHE_B200_HOST_CHUNKS > 0) are strided 2-D copies, which the copy engine runs row by row (~1 us per
   // row): measured slower on B200 below ~10^5 elements.
-  size_t chunks = 0;
-  if (const char *c = getenv("COFHE_B200_HOST_CHUNKS")) { int v = atoi(c); if (v >= 0 && v <= 64) chunks = (size_t)v; }
+  size_t chunks = ctx->opt.host_chunks > 0 ? (size_t)ctx->opt.host_chunks : 0;
   if (chunks == 0) {
     const size_t fw = (rows / 2) * n;  // words of one form block
     for (int y = 0; y < 2 && rc == COFHE_B200_OK; y++) {
@@ -1075,7 +1143,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
   size_t per = (((n + chunks - 1) / chunks) + 31) & ~(size_t)31;
   int used = 0;
   size_t c = 0;
-  const bool trace = getenv("COFHE_B200_HOST_TRACE") != nullptr;  // debugging aid: device times of the first range
+  const bool trace = ctx->opt.host_trace != 0;  // debugging aid: device times of the first range
   cudaEvent_t ev[4];
   double t_start = 0;
   if (trace) { for (auto &e : ev) cudaEventCreate(&e); t_start = now_ms(); }
@@ -1094,7 +1162,7 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
       break;
     }
     if (trace && c == 0) cudaEventRecord(ev[1], st);
-    rc = with_lane(ctx, l, [&](cudaStream_t s2) { return cofhe_b200_add_ciphertexts(ctx, cn, d1, d2, d3, s2); });
+    rc = with_lane(ctx, l, [&](cudaStream_t s2) { return launch_op(ctx, 0, 2, cn, d1, d2, d3, 0, nullptr, 0, 0, nullptr, 0, s2); });
     if (trace && c == 0) cudaEventRecord(ev[2], st);
     if (rc == COFHE_B200_OK &&
         cudaMemcpy2DAsync(out + e0, n * 4, d3, cn * 4, cn * 4, rows, cudaMemcpyDeviceToHost, st) != cudaSuccess)

@@ -25,14 +25,31 @@ QF_HDN void form_store(Err &e, const Form<CAP> &f, u32 *p, const Shape &s, size_
   z_store(e, f.c, p + (size_t)2 * s.na * n + idx, s.nc, n, false);
 }
 
-// out[idx] = in1[idx] o in2[idx]^(neg2 ? -1 : 1)
+// a and b rows only; c = (b^2 + |Delta|) / (4a) is recomputed (operands of the host-pointer add: include/cofhe_b200.h)
+template <int CAP>
+QF_HDN void form_load_ab(Err &e, const Group<CAP> &G, Form<CAP> &f, const u32 *p, const Shape &s, size_t n, size_t idx) {
+  z_load(e, f.a, p + idx, s.na, n, false);
+  z_load(e, f.b, p + (size_t)s.na * n + idx, s.na, n, true);
+  Z<CAP> t, u;
+  z_mul(e, t, f.b, f.b);
+  z_add(e, u, t, G.absD);
+  z_shr(e, t, u, 2);
+  z_divexact<CAP>(e, f.c, t, f.a);
+}
+
+// out[idx] = in1[idx] o in2[idx]^(neg2 ? -1 : 1); no_c: the operands' c rows are not read
 template <int CAP>
 QF_HDN int op_compose(const Group<CAP> &G, const Shape &s, size_t n, size_t idx, const u32 *in1, const u32 *in2, u32 *out,
-                      bool neg2) {
+                      bool neg2, bool no_c = false) {
   Err e; e.code = 0;
   Form<CAP> f1, f2;
-  form_load(e, f1, in1, s, n, idx);
-  form_load(e, f2, in2, s, n, idx);
+  if (no_c) {
+    form_load_ab(e, G, f1, in1, s, n, idx);
+    form_load_ab(e, G, f2, in2, s, n, idx);
+  } else {
+    form_load(e, f1, in1, s, n, idx);
+    form_load(e, f2, in2, s, n, idx);
+  }
   qf_compose(e, G, f1, f1, f2, neg2, false);
   form_store(e, f1, out, s, n, idx);
   return e.code;

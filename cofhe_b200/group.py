@@ -79,6 +79,10 @@ class ClassGroupB200:
         """limbs of the register-resident kernels serving this discriminant (0: generic path)"""
         return int(self.lib.cofhe_b200_fast_limbs(self.h))
 
+    def set_option(self, name, value):
+        """tuning knob of the C ABI (cofhe_b200_set_option); -1 = automatic"""
+        capi.check(self.lib.cofhe_b200_set_option(self.h, name.encode(), int(value)), "set_option")
+
     def launches(self):
         return int(self.lib.cofhe_b200_launch_count(self.h))
 

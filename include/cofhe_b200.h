@@ -18,6 +18,12 @@
  * void*; NULL = legacy default stream) and are asynchronous.  Entry points ending in _host take HOST
  * pointers, do the transfers on an internal stream and return when the result is in the output buffer.
  *
+ * Threads and streams.  A context may be shared: every entry point takes the context's lock for the time it issues
+ * work, and because all calls of a context share its scratch buffers, a call on a stream other than the previous
+ * call's stream is ordered after it on the device (event wait).  Calls on ONE stream from one thread at a time pay
+ * nothing for this; callers that want concurrency between streams use one context per stream (contexts are cheap:
+ * the fixed-base tables, ~0.6 MB at the reference's default size, are the only sizeable per-context state).
+ *
  * Errors.  Every call returns a COFHE_B200_* code; nothing throws across this boundary.  Arithmetic failures
  * of individual elements (operand not a form of this discriminant, value outside the limb shape) are
  * sticky per context: cofhe_b200_status() synchronises the stream and reports/clears them; _host calls
@@ -57,6 +63,11 @@ int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream);
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx);
 /* Limbs of the register-resident kernel instantiation serving this discriminant (0: generic integer path only). */
 int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx);
+/* Tuning knobs, -1 = automatic: "mm_w" (window bits of the matmul multi-exponentiation, 2..8), "mm_chunks" (split of
+ * the inner dimension), "mm_block" (128/256/512 threads), "fb_w" (fixed-base window bits, before set_bases),
+ * "host_staged", "host_loadc", "host_chunks", "host_trace" (variants of the host-pointer add).  They change how the work
+ * is laid out, never the results.  The COFHE_B200_<NAME> environment variables give the defaults at creation. */
+int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value);
 
 /* out[e] = f1[e] o f2[e]   (negf2 != 0: f1[e] o f2[e]^-1), reduced.
  * ClassGroup::nucomp / nucompinv (qfi.inl:1441-1451 -> QFI::nucomp qfi.inl:683-818). */
@@ -83,8 +94,8 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
 /* Same, on HOST buffers, blocking (the call a CryptoSystem backend makes per add_ciphertext_tensors).  Page-locked
  * buffers (cudaHostAlloc / cudaHostRegister / cofhe_b200_host_alloc) are read and written by the kernels directly over
  * PCIe, without staging; on that path only the a and b rows of the operands are read (c = (b^2 - Delta) / 4a is
- * recomputed on the device), all rows of `out` are written.  Pageable buffers are staged through device memory by
- * pipelined copies. */
+ * recomputed on the device, also for the elements that take the robust path), all rows of `out` are written.
+ * Pageable buffers are staged through device memory by pipelined copies (all rows are read). */
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out);
 

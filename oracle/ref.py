@@ -161,6 +161,61 @@ class Reference:
             raise RuntimeError("ref_bulk_part_decrypt failed")
         return dt, co, do
 
+    # ---- the same entry points on caller-supplied SoA limb buffers (full-size parity) -----------------
+    def _fn(self, name, argtypes):
+        fn = getattr(self.lib, name)
+        fn.restype = ctypes.c_double
+        fn.argtypes = argtypes
+        return fn
+
+    def scal_matmul_given(self, n, m, p, scalars, ct, na, nc, exact_zero=None):
+        """reference scal_ciphertext_tensors (exact_zero None) or the exact product built from ClassGroup::nupow /
+        nucomp with the given `zero` ciphertext limbs; ct: uint32 [2, fl, n*m] -> (seconds, uint32 [2, fl, n*p])."""
+        u, vp, cp = ctypes.c_uint, ctypes.c_void_p, ctypes.c_char_p
+        out = np.zeros((2, 2 * na + nc, n * p), dtype=np.uint32)
+        s = " ".join(str(int(x)) for x in scalars).encode()
+        ct = np.ascontiguousarray(ct, dtype=np.uint32)
+        if exact_zero is None:
+            dt = self._fn("ref_bulk_scal_matmul_given", [vp, u, u, u, cp, vp, vp, u, u])(self.h, n, m, p, s, _ptr(ct), _ptr(out), na, nc)
+        else:
+            z = np.ascontiguousarray(exact_zero, dtype=np.uint32)
+            dt = self._fn("ref_bulk_matmul_exact", [vp, u, u, u, cp, vp, vp, vp, u, u])(self.h, n, m, p, s, _ptr(ct), _ptr(z), _ptr(out), na, nc)
+        if dt < 0:
+            raise RuntimeError("reference matmul failed")
+        return dt, out
+
+    def encrypt_given(self, m, r, na, nc):
+        """m: uint32 [nm, count], r: uint32 [nr, count] -> (seconds, cts [2, fl, count]) by `count` single encryptions"""
+        u, vp = ctypes.c_uint, ctypes.c_void_p
+        m, r = np.ascontiguousarray(m, dtype=np.uint32), np.ascontiguousarray(r, dtype=np.uint32)
+        count = m.shape[1]
+        out = np.zeros((2, 2 * na + nc, count), dtype=np.uint32)
+        dt = self._fn("ref_bulk_encrypt_given", [vp, u, vp, u, vp, u, vp, u, u])(self.h, count, _ptr(m), m.shape[0], _ptr(r), r.shape[0], _ptr(out), na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_encrypt_given failed")
+        return dt, out
+
+    def part_decrypt_given(self, share, ct, na, nc):
+        u, vp = ctypes.c_uint, ctypes.c_void_p
+        ct = np.ascontiguousarray(ct, dtype=np.uint32)
+        count = ct.shape[-1]
+        out = np.zeros((2 * na + nc, count), dtype=np.uint32)
+        dt = self._fn("ref_bulk_part_decrypt_given", [vp, u, ctypes.c_char_p, vp, vp, u, u])(self.h, count, str(int(share)).encode(), _ptr(ct), _ptr(out), na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_part_decrypt_given failed")
+        return dt, out
+
+    def combine_given(self, ct, ds, nm, na, nc):
+        """ct [2, fl, count], ds [t, fl, count] -> (seconds, plaintexts [nm, count])"""
+        u, vp = ctypes.c_uint, ctypes.c_void_p
+        ct, ds = np.ascontiguousarray(ct, dtype=np.uint32), np.ascontiguousarray(ds, dtype=np.uint32)
+        count, t = ct.shape[-1], ds.shape[0]
+        out = np.zeros((nm, count), dtype=np.uint32)
+        dt = self._fn("ref_bulk_combine_given", [vp, u, u, vp, vp, vp, u, u, u])(self.h, count, t, _ptr(ct), _ptr(ds), _ptr(out), nm, na, nc)
+        if dt < 0:
+            raise RuntimeError("ref_bulk_combine_given failed")
+        return dt, out
+
 
 def _flatten(a):
     for x in a:

@@ -379,4 +379,138 @@ double ref_bulk_part_decrypt(void *h, unsigned count, const char *share, uint32_
   } catch (...) { return -1.0; }
 }
 
+// ---------------------------------------------------------------------------------------------
+// "Given-input" bulk calls: the reference's own tensor entry points on SoA limb buffers supplied by the
+// caller (full-size parity at the configurations bench.py times: matmul at p = 256, encryption /
+// threshold decryption at 2^16).  Layouts as above.
+// ---------------------------------------------------------------------------------------------
+static Mpz import_int(const uint32_t *src, size_t nl, size_t stride, bool twos) {
+  std::vector<uint32_t> tmp(nl);
+  for (size_t i = 0; i < nl; i++) tmp[i] = src[i * stride];
+  bool neg = twos && (tmp[nl - 1] >> 31);
+  if (neg) {
+    uint64_t c = 1;
+    for (size_t i = 0; i < nl; i++) { uint64_t v = (uint64_t)(uint32_t)~tmp[i] + c; tmp[i] = (uint32_t)v; c = v >> 32; }
+  }
+  mpz_t raw;
+  mpz_init(raw);
+  mpz_import(raw, nl, -1, 4, 0, 0, tmp.data());
+  Mpz z(std::move(raw));
+  if (neg) z.neg();
+  return z;
+}
+static QFI import_form(const uint32_t *buf, size_t idx, size_t n, size_t na, size_t nc) {
+  return QFI(import_int(buf + idx, na, n, false), import_int(buf + na * n + idx, na, n, true),
+             import_int(buf + 2 * na * n + idx, nc, n, false), true);
+}
+static Tensor<CS::CipherText *> import_cts(const uint32_t *buf, size_t rows, size_t cols, size_t na, size_t nc) {
+  size_t n = rows * cols, fl = 2 * na + nc;
+  auto t = make_tensor<CS::CipherText>(rows, cols); t.flatten();
+  for (size_t i = 0; i < n; i++) t.at(i) = new CS::CipherText(import_form(buf, i, n, na, nc), import_form(buf + fl * n, i, n, na, nc));
+  t.reshape({rows, cols});
+  return t;
+}
+
+// scal_ciphertext_tensors (matmul branch) on given ciphertexts ct[n*m] and scalars (decimal text, m*p).  The call
+// draws its `zero` from the RandGen: seed it first (ref_call set_seed) to know which.
+double ref_bulk_scal_matmul_given(void *h, unsigned n, unsigned m, unsigned p, const char *scal, const uint32_t *ct_in,
+                                  uint32_t *out, unsigned na, unsigned nc) {
+  try {
+    Ref &R = *(Ref *)h;
+    auto ct = import_cts(ct_in, n, m, na, nc);
+    auto s = make_tensor<CS::PlainText>(m, p); s.flatten();
+    auto v = parse(scal);
+    for (size_t i = 0; i < (size_t)m * p; i++) s.at(i) = new CS::PlainText(v[i]);
+    s.reshape({m, p});
+    auto t0 = std::chrono::steady_clock::now();
+    auto res = R.cs.scal_ciphertext_tensors(*R.pk, s, ct);
+    double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    res.flatten(); export_cts(res, (size_t)n * p, out, na, nc);
+    free_cts(res); free_cts(ct);
+    s.flatten(); for (size_t i = 0; i < (size_t)m * p; i++) delete s.at(i);
+    return dt;
+  } catch (...) { return -1.0; }
+}
+
+// The same matmul from the reference's exact primitives: out[i,k] = zero o prod_j nupow(ct[i,j], s[j,k]) with
+// ClassGroup::nupow / nucomp (qfi.inl:1441-1477) -- the value scal_ciphertext_tensors is meant to return; its
+// qfi_nupow is wrong for some scalars >= 2^65.
+double ref_bulk_matmul_exact(void *h, unsigned n, unsigned m, unsigned p, const char *scal, const uint32_t *ct_in,
+                             const uint32_t *zero_in, uint32_t *out, unsigned na, unsigned nc) {
+  try {
+    Ref &R = *(Ref *)h; const auto &H = R.cs.get_hsm2k(); const BICYCL::ClassGroup &G = H.Cl_G();
+    size_t fl = 2 * na + nc, nb = (size_t)n * m, no = (size_t)n * p;
+    auto v = parse(scal);
+    std::vector<QFI> base(2 * nb);
+    for (size_t i = 0; i < nb; i++) { base[i] = import_form(ct_in, i, nb, na, nc); base[nb + i] = import_form(ct_in + fl * nb, i, nb, na, nc); }
+    QFI z[2] = {import_form(zero_in, 0, 1, na, nc), import_form(zero_in + fl, 0, 1, na, nc)};
+    auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for schedule(dynamic, 4)
+    for (size_t q = 0; q < 2 * no; q++) {
+      size_t y = q / no, idx = q % no, i = idx / p, k = idx % p;
+      QFI acc = z[y], t;
+      for (size_t j = 0; j < m; j++) { G.nupow(t, base[y * nb + i * m + j], v[j * p + k]); G.nucomp(acc, acc, t); }
+      export_form(acc, out + y * fl * no, idx, no, na, nc);
+    }
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  } catch (...) { return -1.0; }
+}
+
+// N single encryptions with the caller's plaintexts and randomness (config 3 mode B on given inputs)
+double ref_bulk_encrypt_given(void *h, unsigned count, const uint32_t *m_in, unsigned nm, const uint32_t *r_in, unsigned nr,
+                              uint32_t *ct_out, unsigned na, unsigned nc) {
+  try {
+    Ref &R = *(Ref *)h; const auto &H = R.cs.get_hsm2k();
+    std::vector<CS::CipherText> cts(count);
+    auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for schedule(static)
+    for (unsigned i = 0; i < count; i++)
+      cts[i] = CS::CipherText(H, *R.pk, BICYCL::CL_HSM2k::ClearText(H, import_int(m_in + i, nm, count, false)), import_int(r_in + i, nr, count, false));
+    double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    size_t fl = 2 * na + nc;
+    for (unsigned i = 0; i < count; i++) { export_form(cts[i].c1(), ct_out, i, count, na, nc); export_form(cts[i].c2(), ct_out + fl * count, i, count, na, nc); }
+    return dt;
+  } catch (...) { return -1.0; }
+}
+
+// part_decrypt_tensor with one share on given ciphertexts
+double ref_bulk_part_decrypt_given(void *h, unsigned count, const char *share, const uint32_t *ct_in, uint32_t *d_out,
+                                   unsigned na, unsigned nc) {
+  try {
+    Ref &R = *(Ref *)h; Mpz sh{std::string(share)};
+    auto ct = import_cts(ct_in, count, 1, na, nc);
+    auto t0 = std::chrono::steady_clock::now();
+    auto ds = R.cs.part_decrypt_tensor(sh, ct);
+    double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    ds.flatten();
+    for (unsigned i = 0; i < count; i++) { export_form(*ds.at(i), d_out, i, count, na, nc); delete ds.at(i); }
+    free_cts(ct);
+    return dt;
+  } catch (...) { return -1.0; }
+}
+
+// combine_part_decryption_results_tensor: ct[count], ds = [t][form batch] -> plaintexts [nm][count]
+double ref_bulk_combine_given(void *h, unsigned count, unsigned t, const uint32_t *ct_in, const uint32_t *ds_in, uint32_t *m_out,
+                              unsigned nm, unsigned na, unsigned nc) {
+  try {
+    Ref &R = *(Ref *)h; size_t fl = 2 * na + nc;
+    auto ct = import_cts(ct_in, count, 1, na, nc);
+    Vector<Tensor<CS::PartDecryptionResult *>> pd;
+    for (unsigned j = 0; j < t; j++) {
+      auto d = make_tensor<CS::PartDecryptionResult>(count, 1); d.flatten();
+      for (unsigned i = 0; i < count; i++) d.at(i) = new CS::PartDecryptionResult(import_form(ds_in + (size_t)j * fl * count, i, count, na, nc));
+      d.reshape({count, 1});
+      pd.push_back(d);
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    auto pt = R.cs.combine_part_decryption_results_tensor(ct, pd);
+    double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    pt.flatten();
+    for (unsigned i = 0; i < count; i++) { export_int(*pt.at(i), m_out + i, nm, count, false); delete pt.at(i); }
+    for (auto &d : pd) { d.flatten(); for (unsigned i = 0; i < count; i++) delete d.at(i); }
+    free_cts(ct);
+    return dt;
+  } catch (...) { return -1.0; }
+}
+
 } // extern "C"

@@ -135,3 +135,29 @@ def test_wire_format_matches_reference_bytes():
         data = bytes.fromhex(t["hex"])
         assert O.serialize_ciphertext_tensor(t["shape"], cts) == data, tier
         assert O.deserialize_ciphertext_tensor(data) == (t["shape"], cts), tier
+
+
+def test_big_fixture_heads():
+    """tests/golden/big_t0.npz (outputs of the compiled reference at the benched sizes) against the restatement on
+    the leading elements: one matmul output column of the sweep shape, the first encryptions / partial decryptions"""
+    import big_inputs as B
+    from cofhe_b200 import limbs as L
+    t = load_golden("ref_t0.json")
+    P = params_of(t)
+    z = B.load()
+    na, nc, _ = L.limb_shape((-P.Delta).bit_length())
+    n, m, p = B.SWEEP_SHAPE
+    cts = L.limbs_to_cts(z["sweep_ct"], na, nc)
+    zero = L.limbs_to_cts(z["mm_zero"], na, nc)[0]
+    sc = B.sweep_scalars()
+    want = L.limbs_to_cts(z["sweep_res"], na, nc)
+    got = O.scal_matmul(zero, cts[:m], [sc[j * p + 1] for j in range(m)], 1, m, 1)
+    assert got[0] == want[1]
+    ms, rs = B.enc_inputs(P.k, P.exponent_bound)
+    pk = I(t["pk"])
+    heads = L.limbs_to_cts(z["enc_head"], na, nc)
+    for i in range(2):
+        ct = O.encrypt(P, pk, ms[i], rs[i])
+        assert ct == heads[i]
+        for q in range(2):
+            assert O.part_decrypt(int(t["shares"][q][0]), ct) == L.limbs_to_forms(z["pd_head_%d" % q], na, nc)[i]
