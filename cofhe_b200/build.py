@@ -25,7 +25,7 @@ def extra_flags():
 def sources():
     names = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
     if "-DCOFHE_B200_DEV_N7" in extra_flags():
-        names = [f for f in names if not f.startswith("fast_n") or f == "fast_n7.cu"]
+        names = [f for f in names if not f.startswith(("fast_n", "coop_n")) or f in ("fast_n7.cu", "coop_n7.cu")]
     return [os.path.join(CSRC, f) for f in names]
 
 

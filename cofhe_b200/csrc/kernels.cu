@@ -12,6 +12,7 @@
 #include <utility>
 
 #include "cofhe_b200.h"
+#include "coop_launch.cuh"
 #include "fast_launch.cuh"
 #include "fast_ops.cuh"
 #include "matmul.cuh"
@@ -31,6 +32,7 @@ struct cofhe_b200_ctx {
   cudaStream_t xfer;  // internal stream of the _host entry points
   uint64_t launches;
   int fastn;          // limbs of the register-resident instantiation serving this shape (0: none, robust path only)
+  int coopn;          // limbs of the cooperative (lane-group) instantiation serving this shape (0: none)
   u32 *d_bail;        // elements the fast path declined, redone by the sparse robust kernels
   int *d_nbail;       // two counters used alternately (the sparse kernel of call k clears the one of call k+1)
   size_t bail_cap;
@@ -62,7 +64,7 @@ struct cofhe_b200_ctx {
   bool busy;
   cudaEvent_t order;
   // tuning knobs (cofhe_b200_set_option; the COFHE_B200_* environment variables are read once, at creation)
-  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace; } opt;
+  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop; } opt;
 };
 
 namespace {
@@ -181,6 +183,32 @@ long env_opt(const char *name, long lo, long hi) {
   return x >= lo && x <= hi ? x : -1;
 }
 
+// cooperative instantiations: (lanes per form, limbs per lane) per coefficient width; coop_n<N>.cu
+#ifdef COFHE_B200_DEV_N7
+#define COOP_DISPATCH(cn, ...)                                                                   \
+  switch (cn) {                                                                                  \
+    case 7: { constexpr int CT = 2, CL = 5, CN = 7, CCAP = 32; __VA_ARGS__; } break;             \
+    default: return COFHE_B200_EINVAL;                                                           \
+  }
+#define COOP_HAVE(na) ((na) == 7)
+#else
+#define COOP_DISPATCH(cn, ...)                                                                   \
+  switch (cn) {                                                                                  \
+    case 7: { constexpr int CT = 2, CL = 5, CN = 7, CCAP = 32; __VA_ARGS__; } break;             \
+    case 11: { constexpr int CT = 2, CL = 7, CN = 11, CCAP = 48; __VA_ARGS__; } break;           \
+    case 33: { constexpr int CT = 4, CL = 9, CN = 33, CCAP = 136; __VA_ARGS__; } break;          \
+    default: return COFHE_B200_EINVAL;                                                           \
+  }
+#define COOP_HAVE(na) ((na) == 7 || (na) == 11 || (na) == 33)
+#endif
+int coop_cap(int cn) { return cn == 33 ? 136 : (cn == 11 ? 48 : 32); }
+// which path serves a batched form operation: the cooperative kernels where no register instantiation exists (the large
+// discriminants), or when forced ("coop" option: 1 always, 0 never)
+bool use_coop(const cofhe_b200_ctx *ctx) {
+  if (!ctx->coopn || ctx->opt.coop == 0) return false;
+  return ctx->opt.coop == 1 || !ctx->fastn;
+}
+
 int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
   if (entries >> 32) return COFHE_B200_EINVAL;
   if (entries <= ctx->bail_cap) return COFHE_B200_OK;
@@ -270,7 +298,8 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
               const u32 *exp, int el, int per_elem, const unsigned char *expneg, int shared_neg, cudaStream_t st) {
   Shape s{(int)ctx->na, (int)ctx->nc};
   dim3 grid(grid_for(n), ny);
-  if (!ctx->fastn) {
+  const bool coop = use_coop(ctx) && op < 2 && !(neg2 & 2);
+  if (!ctx->fastn && !coop) {
     CAP_DISPATCH(ctx->cap, {
       const Group<CAP> *G = (const Group<CAP> *)ctx->d_group;
       if (op == 0) k_compose<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, in2, out, neg2 & 1, ctx->d_err);
@@ -284,13 +313,20 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
   ctx->flip ^= 1;
   int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
-  const int pb = pick_block((size_t)ny * n, ctx->sms);
-  FAST_DISPATCH(ctx->fastn, {
-    typedef FastKernels<FN, FCAP> K;
-    if (op < 2) K::compose(op == 1, grid, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
-    else K::pow(dim3((unsigned)((n + pb - 1) / pb), ny), pb, st, ctx->d_group, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
-                shared_neg, ctx->d_bail, cnt);
-  })
+  if (coop) {
+    COOP_DISPATCH(ctx->coopn, {
+      typedef CoopKernels<CT, CL, CN, CCAP> K;
+      K::compose(op == 1, ny, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+    })
+  } else {
+    const int pb = pick_block((size_t)ny * n, ctx->sms);
+    FAST_DISPATCH(ctx->fastn, {
+      typedef FastKernels<FN, FCAP> K;
+      if (op < 2) K::compose(op == 1, grid, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+      else K::pow(dim3((unsigned)((n + pb - 1) / pb), ny), pb, st, ctx->d_group, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
+                  shared_neg, ctx->d_bail, cnt);
+    })
+  }
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
   unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
@@ -428,6 +464,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->opt.host_loadc = getenv("COFHE_B200_HOST_LOADC") ? 1 : 0;
   ctx->opt.host_chunks = env_opt("COFHE_B200_HOST_CHUNKS", 0, 64);
   ctx->opt.host_trace = getenv("COFHE_B200_HOST_TRACE") ? 1 : 0;
+  ctx->opt.coop = env_opt("COFHE_B200_COOP", 0, 1);
   ctx->device = device;
   ctx->sms = 0;
   if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); ctx->sms = 0; }
@@ -440,6 +477,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->dbits = (u32)dbits;
   for (u32 i = 0; i < n; i++) ctx->h_absd[i] = abs_delta[i];
   ctx->fastn = fast_n_for(ctx->na, cap, ctx->opt.no_fast != 0);
+  ctx->coopn = (COOP_HAVE(ctx->na) && coop_cap((int)ctx->na) == cap && !getenv("COFHE_B200_NO_COOP")) ? (int)ctx->na : 0;
   ctx->d_bail = nullptr; ctx->d_nbail = nullptr; ctx->bail_cap = 0; ctx->flip = 0;
   memset(ctx->lane, 0, sizeof(ctx->lane));
   ctx->d_stage = nullptr; ctx->stage_bytes = 0;
@@ -526,7 +564,8 @@ int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream) {
 }
 
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx) { return ctx ? ctx->launches : 0; }
-int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx) { return ctx ? ctx->fastn : 0; }
+int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx) { return ctx ? (ctx->fastn ? ctx->fastn : ctx->coopn) : 0; }
+int cofhe_b200_coop_limbs(const cofhe_b200_ctx *ctx) { return ctx ? ctx->coopn : 0; }
 
 int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
   if (!ctx || !name) return COFHE_B200_EINVAL;
@@ -534,7 +573,7 @@ int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
   struct { const char *n; long *p; } tab[] = {
       {"mm_w", &ctx->opt.mm_w}, {"mm_chunks", &ctx->opt.mm_chunks}, {"mm_block", &ctx->opt.mm_block}, {"fb_w", &ctx->opt.fb_w},
       {"host_staged", &ctx->opt.host_staged}, {"host_loadc", &ctx->opt.host_loadc}, {"host_chunks", &ctx->opt.host_chunks},
-      {"host_trace", &ctx->opt.host_trace}};
+      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) { *t.p = value; return COFHE_B200_OK; }
   return COFHE_B200_EINVAL;

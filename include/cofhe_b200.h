@@ -61,11 +61,16 @@ int cofhe_b200_shape(const cofhe_b200_ctx *ctx, uint32_t *na, uint32_t *nc, uint
 int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream);
 /* Number of kernel launches issued through this context so far (bench.py reports it as gpu_launches). */
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx);
-/* Limbs of the register-resident kernel instantiation serving this discriminant (0: generic integer path only). */
+/* Coefficient limbs of the hand-written kernel instantiation serving this discriminant -- register-resident (one thread
+ * per form) or cooperative (one lane group per form) -- or 0 when only the generic integer path exists. */
 int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx);
+/* Coefficient limbs of the cooperative instantiation for this discriminant (0: none).  It serves the widths without a
+ * register instantiation (2053-bit discriminants) and, with the option "coop" = 1, every form operation. */
+int cofhe_b200_coop_limbs(const cofhe_b200_ctx *ctx);
 /* Tuning knobs, -1 = automatic: "mm_w" (window bits of the matmul multi-exponentiation, 2..8), "mm_chunks" (split of
  * the inner dimension), "mm_block" (128/256/512 threads), "fb_w" (fixed-base window bits, before set_bases),
- * "host_staged", "host_loadc", "host_chunks", "host_trace" (variants of the host-pointer add).  They change how the work
+ * "host_staged", "host_loadc", "host_chunks", "host_trace" (variants of the host-pointer add), "coop" (1: cooperative
+ * kernels for every form operation, 0: never).  They change how the work
  * is laid out, never the results.  The COFHE_B200_<NAME> environment variables give the defaults at creation. */
 int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value);
 

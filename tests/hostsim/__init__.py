@@ -14,6 +14,8 @@ CSRC = os.path.join(ROOT, "cofhe_b200", "csrc")
 
 _lib = None
 EXTRA_SIGS = {
+    "hs_coop_compose": [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p,
+                        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p],
     "hs_fast_compose": [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p,
                         ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p],
     "hs_scheme": [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
@@ -28,7 +30,7 @@ def _stale():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [SRC, os.path.join(HERE, "hostsim_extra.inc")] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+    deps = [SRC, os.path.join(HERE, "hostsim_extra.inc"), os.path.join(HERE, "coop_sim.inc")] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 

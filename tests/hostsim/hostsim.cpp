@@ -6,6 +6,7 @@
 #include <cstring>
 #include "ops.cuh"
 #include "hostsim_extra.inc"
+#include "coop_sim.inc"
 
 using namespace cofhe;
 

@@ -1,0 +1,74 @@
+"""GPU parity of the cooperative (lane-group) kernels through the C ABI: the reference-generated fixtures with the
+"coop" option forced, and equality with the register / generic path on large batches."""
+import random
+
+import pytest
+import torch
+
+from conftest import I, load_golden
+from oracle import qf_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def groups():
+    from cofhe_b200.group import ClassGroupB200
+    cache = {}
+
+    def get(D):
+        if D not in cache:
+            cache[D] = ClassGroupB200(D)
+        return cache[D]
+    yield get
+    for g in cache.values():
+        g.close()
+
+
+def coop_group(groups, tier):
+    G = groups(int(tier["params"]["Delta"]))
+    if not int(G.lib.cofhe_b200_coop_limbs(G.h)):
+        pytest.skip("no cooperative instantiation for this width")
+    return G
+
+
+def test_coop_compose_fixtures(groups, tier):
+    G = coop_group(groups, tier)
+    G.set_option("coop", 1)
+    try:
+        vs = tier["compose"] + tier["compose_edge"]
+        f1, f2 = G.forms([I(v["f1"]) for v in vs]), G.forms([I(v["f2"]) for v in vs])
+        assert G.forms_out(G.nucomp(f1, f2)) == [I(v["r"]) for v in vs]
+        assert G.forms_out(G.nucomp(f2, f1)) == [I(v["r"]) for v in vs]
+        assert G.forms_out(G.nucomp(f1, f2, negf2=True)) == [I(v["rinv"]) for v in vs]
+        assert G.forms_out(G.nudupl(f1)) == [I(v["sq"]) for v in vs]
+        a = tier["add_tensors"]
+        assert G.cts_out(G.add_ciphertexts(G.cts(I(a["ct1"])), G.cts(I(a["ct2"])))) == list(I(a["res"]))
+        G.status()
+    finally:
+        G.set_option("coop", -1)
+
+
+@pytest.mark.parametrize("name", ["t0", "node", "t1"])
+def test_coop_equals_other_path_at_scale(groups, name):
+    t = load_golden("ref_%s.json" % name)
+    G = coop_group(groups, t)
+    rng = random.Random(11)
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    base = [O.power(h, rng.getrandbits(64)) for _ in range(8)] + [O.power(pk, rng.getrandbits(64)) for _ in range(8)]
+    n = 1 << (15 if name != "t1" else 12)
+    f = G.forms([base[i % 16] for i in range(n)])
+    g = G.forms([base[(5 * i + 3) % 16] for i in range(n)])
+    G.set_option("coop", 0)
+    want = (G.nucomp(f, g), G.nucomp(f, g, negf2=True), G.nudupl(f))
+    G.status()
+    G.set_option("coop", 1)
+    try:
+        got = (G.nucomp(f, g), G.nucomp(f, g, negf2=True), G.nudupl(f))
+        G.status()
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+        assert torch.equal(G.nucomp(got[0], g, negf2=True), f)
+        G.status()
+    finally:
+        G.set_option("coop", -1)

@@ -1,0 +1,77 @@
+"""Logic tests of the cooperative path (cofhe_b200/csrc/coop*.cuh compiled with g++, the lanes of a group run as fibers by
+tests/hostsim/coop_sim.inc): every element it accepts must equal the reference fixtures / the oracle; what it declines
+is counted.  Shapes: (T lanes, L limbs per lane) per coefficient width N."""
+import random
+
+import numpy as np
+import pytest
+
+import hostsim as HS
+from conftest import I, load_golden
+from cofhe_b200 import limbs as L
+from oracle import qf_oracle as O
+
+SHAPES = {7: [(2, 5), (4, 3)], 11: [(2, 7), (4, 4)], 33: [(4, 9), (8, 5)]}
+
+
+class CoopSim:
+    def __init__(self, D, T, LL):
+        self.D, self.T, self.L = D, T, LL
+        self.dbits = (-D).bit_length()
+        self.na, self.nc, self.nd = L.limb_shape(self.dbits)
+        self.lib = HS.load()
+
+    def run(self, f1, f2=None, inv=False, dupl=False):
+        n = len(f1)
+        a = L.forms_to_limbs(f1, self.na, self.nc)
+        b = L.forms_to_limbs(f2 if f2 is not None else f1, self.na, self.nc)
+        o = np.zeros_like(a)
+        bail = np.zeros(n, dtype=np.uint8)
+        nb = self.lib.hs_coop_compose(self.T, self.L, self.na, self.dbits, self.nc, n, HS.P(a), HS.P(b), HS.P(o), int(inv), int(dupl), HS.P(bail))
+        assert nb >= 0
+        return L.limbs_to_forms(o, self.na, self.nc), bail
+
+
+def check(got, bail, want):
+    bad = [i for i, (g, w) in enumerate(zip(got, want)) if not bail[i] and g != w]
+    assert not bad, "cooperative path wrong at %s" % bad[:5]
+
+
+def sims(tier):
+    D = int(tier["params"]["Delta"])
+    na = L.limb_shape((-D).bit_length())[0]
+    return [CoopSim(D, t, l) for t, l in SHAPES.get(na, [])]
+
+
+def test_coop_fixtures(tier):
+    ss = sims(tier)
+    if not ss:
+        pytest.skip("no cooperative instantiation for this width")
+    vs = tier["compose"] + tier["compose_edge"]
+    nr = len(tier["compose"])
+    f1, f2 = [I(v["f1"]) for v in vs], [I(v["f2"]) for v in vs]
+    for S in ss:
+        g, b = S.run(f1, f2); check(g, b, [I(v["r"]) for v in vs])
+        assert int(b[:nr].sum()) == 0, "random reduced forms must stay on the cooperative path"
+        g, b = S.run(f2, f1); check(g, b, [I(v["r"]) for v in vs])
+        g, b = S.run(f1, f2, inv=True); check(g, b, [I(v["rinv"]) for v in vs])
+        g, b = S.run(f1, dupl=True); check(g, b, [I(v["sq"]) for v in vs])
+        assert int(b[:nr].sum()) == 0
+
+
+@pytest.mark.parametrize("name", ["t0", "node", "t1"])
+def test_coop_random_chains(name):
+    """products of random group elements: compose, inverse-compose, square; gcd(a1, a2) != 1 pairs included"""
+    t = load_golden("ref_%s.json" % name)
+    rng = random.Random(77)
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    n = 24 if name != "t1" else 8
+    base = [O.power(h, rng.getrandbits(40) + 1) for _ in range(n)] + [O.power(pk, rng.getrandbits(40) + 1) for _ in range(n)]
+    f1 = base
+    f2 = base[::-1]
+    for S in sims(t):
+        g, b = S.run(f1, f2); check(g, b, [O.compose(x, y) for x, y in zip(f1, f2)])
+        assert int(b.sum()) == 0
+        g, b = S.run(f1, f2, inv=True); check(g, b, [O.compose_inv(x, y) for x, y in zip(f1, f2)])
+        g, b = S.run(f1, dupl=True); check(g, b, [O.square(x) for x in f1])
+        assert int(b.sum()) == 0
