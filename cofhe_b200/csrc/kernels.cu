@@ -566,6 +566,7 @@ int cofhe_b200_status(cofhe_b200_ctx *ctx, void *stream) {
 uint64_t cofhe_b200_launch_count(const cofhe_b200_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx) { return ctx ? (ctx->fastn ? ctx->fastn : ctx->coopn) : 0; }
 int cofhe_b200_coop_limbs(const cofhe_b200_ctx *ctx) { return ctx ? ctx->coopn : 0; }
+int cofhe_b200_reg_limbs(const cofhe_b200_ctx *ctx) { return ctx ? ctx->fastn : 0; }
 
 int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
   if (!ctx || !name) return COFHE_B200_EINVAL;

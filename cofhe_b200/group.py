@@ -76,8 +76,13 @@ class ClassGroupB200:
 
     @property
     def fast(self):
-        """limbs of the register-resident kernels serving this discriminant (0: generic path)"""
+        """limbs of the hand-written kernels (register-resident or cooperative) serving this discriminant (0: generic path)"""
         return int(self.lib.cofhe_b200_fast_limbs(self.h))
+
+    @property
+    def reg(self):
+        """limbs of the register-resident (one thread per form) kernels for this discriminant (0: none)"""
+        return int(self.lib.cofhe_b200_reg_limbs(self.h))
 
     def set_option(self, name, value):
         """tuning knob of the C ABI (cofhe_b200_set_option); -1 = automatic"""

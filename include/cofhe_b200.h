@@ -67,6 +67,9 @@ int cofhe_b200_fast_limbs(const cofhe_b200_ctx *ctx);
 /* Coefficient limbs of the cooperative instantiation for this discriminant (0: none).  It serves the widths without a
  * register instantiation (2053-bit discriminants) and, with the option "coop" = 1, every form operation. */
 int cofhe_b200_coop_limbs(const cofhe_b200_ctx *ctx);
+/* Coefficient limbs of the register-resident instantiation (one thread per form) for this discriminant (0: none).  The
+ * zero-copy variant of cofhe_b200_add_ciphertexts_host exists on these widths. */
+int cofhe_b200_reg_limbs(const cofhe_b200_ctx *ctx);
 /* Tuning knobs, -1 = automatic: "mm_w" (window bits of the matmul multi-exponentiation, 2..8), "mm_chunks" (split of
  * the inner dimension), "mm_block" (128/256/512 threads), "fb_w" (fixed-base window bits, before set_bases),
  * "host_staged", "host_loadc", "host_chunks", "host_trace" (variants of the host-pointer add), "coop" (1: cooperative
@@ -98,7 +101,8 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
                                void *stream);
 /* Same, on HOST buffers, blocking (the call a CryptoSystem backend makes per add_ciphertext_tensors).  Page-locked
  * buffers (cudaHostAlloc / cudaHostRegister / cofhe_b200_host_alloc) are read and written by the kernels directly over
- * PCIe, without staging; on that path only the a and b rows of the operands are read (c = (b^2 - Delta) / 4a is
+ * PCIe, without staging (discriminants with a register-resident instantiation, cofhe_b200_reg_limbs() != 0; the others
+ * are staged); on that path only the a and b rows of the operands are read (c = (b^2 - Delta) / 4a is
  * recomputed on the device, also for the elements that take the robust path), all rows of `out` are written.
  * Pageable buffers are staged through device memory by pipelined copies (all rows are read). */
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,

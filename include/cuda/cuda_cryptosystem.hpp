@@ -25,13 +25,32 @@
 #include <string>
 #include <vector>
 
+// The reference class stays the host side of this backend (setup, keys, RandGen draw order).  With -DCOFHE_B200 the
+// NAME CoFHE::CPUCryptoSystem is handed to this backend (alias at the end of this file), so that sources which spell the
+// class name -- benchmarks/local.cpp:35,38, benchmarks/network.cpp, examples/*.cpp -- build unchanged on it; the reference
+// class is then compiled under the name CPUCryptoSystemHost.  This header (or this repository's cofhe.hpp, which
+// includes it) must come before the reference's own headers in that mode.
+#ifdef COFHE_B200
+#ifdef CPU_CRYPTO_SYSTEM_HPP_INCLUDED
+#error "COFHE_B200: include cuda/cuda_cryptosystem.hpp (or cofhe_b200's cofhe.hpp) before x86_64/cpu_cryptosystem.hpp"
+#endif
+#define CPUCryptoSystem CPUCryptoSystemHost
 #include "x86_64/cpu_cryptosystem.hpp"
+#undef CPUCryptoSystem
+#else
+#include "x86_64/cpu_cryptosystem.hpp"
+#endif
 #include "cofhe_b200.h"
 
 namespace CoFHE
 {
     namespace b200_detail
     {
+#ifdef COFHE_B200
+        using HostCS = ::CoFHE::CPUCryptoSystemHost;
+#else
+        using HostCS = ::CoFHE::CPUCryptoSystem;
+#endif
         // status codes of the C ABI back into the exceptions the reference throws (std::invalid_argument for bad
         // shapes/arguments, std::runtime_error otherwise; node handlers catch std::exception)
         inline void check(int rc, const char *what)
@@ -96,12 +115,12 @@ namespace CoFHE
     class B200CryptoSystem
     {
     public:
-        using SecretKey = CPUCryptoSystem::SecretKey;
-        using SecretKeyShare = CPUCryptoSystem::SecretKeyShare;
-        using PublicKey = CPUCryptoSystem::PublicKey;
-        using PlainText = CPUCryptoSystem::PlainText;
-        using CipherText = CPUCryptoSystem::CipherText;
-        using PartDecryptionResult = CPUCryptoSystem::PartDecryptionResult;
+        using SecretKey = b200_detail::HostCS::SecretKey;
+        using SecretKeyShare = b200_detail::HostCS::SecretKeyShare;
+        using PublicKey = b200_detail::HostCS::PublicKey;
+        using PlainText = b200_detail::HostCS::PlainText;
+        using CipherText = b200_detail::HostCS::CipherText;
+        using PartDecryptionResult = b200_detail::HostCS::PartDecryptionResult;
 
         // (N_bits a.k.a. security_level, k, compact): same meaning as CPUCryptoSystem (cpu_cryptosystem.hpp:33).
         // The compact variant keeps c1 in Cl(DeltaK); the device path covers the non-compact scheme every caller
@@ -173,7 +192,7 @@ namespace CoFHE
         String serialize_plaintext_tensor(const Tensor<PlainText *> &t) const { return host_.serialize_plaintext_tensor(t); }
         String serialize_ciphertext_tensor(const Tensor<CipherText *> &t) const { return host_.serialize_ciphertext_tensor(t); }
         String serialize_part_decryption_result_tensor(const Tensor<PartDecryptionResult *> &t) const { return host_.serialize_part_decryption_result_tensor(t); }
-        static B200CryptoSystem deserialize(const String &data) { return B200CryptoSystem(CPUCryptoSystem::deserialize(data)); }
+        static B200CryptoSystem deserialize(const String &data) { return B200CryptoSystem(b200_detail::HostCS::deserialize(data)); }
         SecretKey deserialize_secret_key(const String &d) const { return host_.deserialize_secret_key(d); }
         SecretKeyShare deserialize_secret_key_share(const String &d) const { return host_.deserialize_secret_key_share(d); }
         PublicKey deserialize_public_key(const String &d) const { return host_.deserialize_public_key(d); }
@@ -206,7 +225,7 @@ namespace CoFHE
         Tensor<CipherText *> negate_ciphertext_tensor(const PublicKey &pk, const Tensor<CipherText *> &ct) const;
 
         // wrap an existing reference object (used by deserialize)
-        explicit B200CryptoSystem(CPUCryptoSystem host, int device = 0) : host_(std::move(host)), device_(device)
+        explicit B200CryptoSystem(b200_detail::HostCS host, int device = 0) : host_(std::move(host)), device_(device)
         {
             if (host_.get_hsm2k().compact_variant())
                 throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
@@ -214,7 +233,7 @@ namespace CoFHE
         }
 
     private:
-        mutable CPUCryptoSystem host_; // RandGen lives here; draws happen in the reference's call order
+        mutable b200_detail::HostCS host_; // RandGen lives here; draws happen in the reference's call order
         int device_;
         cofhe_b200_ctx *ctx_ = nullptr;
         uint32_t na_ = 0, nc_ = 0, nd_ = 0, ml_ = 0, el_r_ = 0;
@@ -684,11 +703,17 @@ namespace CoFHE
         return res;
     }
 
-    // ---- factory: honours Device::GPU, which the reference's make_cryptosystem ignores (cofhe.hpp:96-121) ----------
+    // ---- factory: a B200 backend on CUDA device `device` (the reference's make_cryptosystem ignores its Device
+    // argument, cofhe.hpp:96-121; this repository's cofhe.hpp adds the Device::GPU dispatch on top of this) --------------
     inline B200CryptoSystem make_b200_cryptosystem(uint32_t security_level, uint32_t k, int device = 0)
     {
         return B200CryptoSystem{security_level, k, false, device};
     }
+
+#ifdef COFHE_B200
+    // the drivers that spell the class name (benchmarks/local.cpp:35,38 ...) now name the device backend
+    using CPUCryptoSystem = B200CryptoSystem;
+#endif
 
 } // namespace CoFHE
 

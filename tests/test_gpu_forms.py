@@ -102,7 +102,7 @@ def test_add_ciphertexts(groups, tier):
     p2 = torch.from_numpy(L.cts_to_limbs(cts2, G.na, G.nc).view(np.int32)).pin_memory()
     po = torch.zeros_like(p1).pin_memory()
     for wipe in (False, True):
-        if wipe and G.fast:
+        if wipe and G.reg:
             # also for the elements the register path declines (neutral operands): the robust redo recomputes c as well
             p1[:, 2 * G.na:, :] = 0x5a5a5a5a
             p2[:, 2 * G.na:, :] = 0x5a5a5a5a
