@@ -31,6 +31,7 @@ SIGNATURES = {
     "cofhe_b200_reg_limbs": (ctypes.c_int, [vp]),
     "cofhe_b200_set_option": (i32, [vp, ctypes.c_char_p, ctypes.c_long]),
     "cofhe_b200_scal_ciphertexts": (i32, [vp, sz, vp, vp, u32, i32, vp, i32, vp, vp]),
+    "cofhe_b200_rerandomize": (i32, [vp, sz, vp, vp, u32, i32, vp, vp]),
     "cofhe_b200_beaver_open": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp]),
     "cofhe_b200_beaver_close": (i32, [vp, sz, vp, vp, u32, vp, vp, vp, vp, u32, vp, vp]),
     "cofhe_b200_wire_header": (i32, [vp, sz, ctypes.POINTER(u32), vp, u32, ctypes.POINTER(sz)]),

@@ -15,7 +15,7 @@ template <int T, int L, int N, int CAP>
 struct CoopKernels {
   // flags of compose: 1 = second operand inverted
   static void compose(bool dupl, unsigned ny, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2,
-                      u32 *out, int flags, u32 *bail, int *nbail);
+                      u32 *out, int flags, u32 *bail, int *nbail, int mb);
 };
 
 }  // namespace cofhe

@@ -5,6 +5,7 @@
 #include "coop_ops.cuh"
 #include "ops.cuh"
 
+
 namespace cofhe {
 
 template <int T>
@@ -13,36 +14,47 @@ __device__ __forceinline__ Grp<T> make_group(u32 *scr_block, int words) {
   g.lane = threadIdx.x % T;
   g.scr = scr_block + (threadIdx.x / T) * words;
   g.base = (threadIdx.x & 31) & ~(T - 1);
-  g.mask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << g.base;
+  g.all = __activemask();  // every lane is here: 0xffffffff
   return g;
 }
 
-// one lane group per form operation; grid.y selects the form block inside a ciphertext batch (0: c1, 1: c2)
-template <int T, int L, int N, int CAP, bool DUPL>
-__global__ void __launch_bounds__(kCoopBlock) k_coop_compose(int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out, int neg2,
-                                                            u32 *bail, int *nbail) {
+// one lane group per form operation, the 32/T groups of a warp in lock step (coop.cuh); grid.y selects the form block
+// inside a ciphertext batch (0: c1, 1: c2).  Groups past the end of the batch ride along on the last element.
+template <int T, int L, int N, int CAP, bool DUPL, int MB>
+__global__ void __launch_bounds__(kCoopBlock, MB) k_coop_compose(int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
+                                                                             int neg2, u32 *bail, int *nbail) {
   constexpr int GPB = kCoopBlock / T, SW = CgScratch<T, L>::words;
   __shared__ u32 scr[GPB * SW];
   Grp<T> g = make_group<T>(scr, SW);
   size_t idx = (size_t)blockIdx.x * GPB + threadIdx.x / T;
-  if (idx >= n) return;  // whole groups leave together
+  const bool have = idx < n;
+  if (!have) idx = n - 1;
   size_t off = (size_t)blockIdx.y * (2 * N + nc) * n;
   FormC<L> f1, f2, r;
   bool ok = cq_load<T, L, N>(g, f1, in1 + off, nc, n, idx);
   if (!DUPL) ok = cq_load<T, L, N>(g, f2, in2 + off, nc, n, idx) && ok;
-  if (ok) ok = cq_compose<T, L, N, DUPL>(g, r, f1, DUPL ? f1 : f2, (neg2 & 1) != 0, dbits);
-  if (ok) ok = cq_store<T, L, N>(g, r, out + off, nc, n, idx);
-  if (!ok && g.lane == 0) bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
+  ok = cq_compose<T, L, N, DUPL>(g, r, f1, DUPL ? f1 : f2, (neg2 & 1) != 0, dbits, have && ok);
+  ok = cq_store<T, L, N>(g, r, out + off, nc, n, idx, have && ok);
+  if (have && !ok && g.lane == 0) bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
 }
 
+// mb: resident blocks per SM the kernel is compiled for (3: up to 168 registers, 4: 128, 5: 96) -- an occupancy /
+// spilling trade-off chosen per width by the caller
 template <int T, int L, int N, int CAP>
 void CoopKernels<T, L, N, CAP>::compose(bool dupl, unsigned ny, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in1,
-                                        const u32 *in2, u32 *out, int flags, u32 *bail, int *nbail) {
+                                        const u32 *in2, u32 *out, int flags, u32 *bail, int *nbail, int mb) {
   (void)G;
   constexpr int GPB = kCoopBlock / T;
   dim3 grid((unsigned)((n + GPB - 1) / GPB), ny);
-  if (dupl) k_coop_compose<T, L, N, CAP, true><<<grid, kCoopBlock, 0, st>>>(dbits, nc, n, in1, in1, out, 0, bail, nbail);
-  else k_coop_compose<T, L, N, CAP, false><<<grid, kCoopBlock, 0, st>>>(dbits, nc, n, in1, in2, out, flags, bail, nbail);
+#define COOP_LAUNCH(MB)                                                                                                              \
+  do {                                                                                                                               \
+    if (dupl) k_coop_compose<T, L, N, CAP, true, MB><<<grid, kCoopBlock, 0, st>>>(dbits, nc, n, in1, in1, out, 0, bail, nbail);        \
+    else k_coop_compose<T, L, N, CAP, false, MB><<<grid, kCoopBlock, 0, st>>>(dbits, nc, n, in1, in2, out, flags, bail, nbail);       \
+  } while (0)
+  if (mb >= 5) COOP_LAUNCH(5);
+  else if (mb == 4) COOP_LAUNCH(4);
+  else COOP_LAUNCH(3);
+#undef COOP_LAUNCH
 }
 
 }  // namespace cofhe

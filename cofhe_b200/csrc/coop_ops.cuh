@@ -25,11 +25,12 @@ CG_FN bool cq_load(const Grp<T> &g, FormC<L> &f, const u32 *p, int nc, size_t n,
   if (g.lane == T - 1) hi |= f.c[L - 1] >> 28;
   return !g_any<T>(g, hi != 0);
 }
-// registers -> SoA batch; false when c does not fit nc limbs (nothing is written then)
+// registers -> SoA batch when `on`; false when not `on` or c does not fit nc limbs (nothing is written then)
 template <int T, int L, int N>
-CG_FN bool cq_store(const Grp<T> &g, const FormC<L> &f, u32 *p, int nc, size_t n, size_t idx) {
+CG_FN bool cq_store(const Grp<T> &g, const FormC<L> &f, u32 *p, int nc, size_t n, size_t idx, bool on) {
   constexpr int K = T * L;
-  if (nc < K && !g_high_zero<T, L>(g, f.c, nc)) return false;
+  bool fits = g_high_zero<T, L>(g, f.c, nc < K ? nc : K);
+  if (!on || !fits) return false;
   QF_UNROLL for (int i = 0; i < L; i++) {
     int q = g.lane * L + i;
     if (q < N) { p[(size_t)q * n + idx] = f.a[i]; p[(size_t)(N + q) * n + idx] = f.b[i]; }

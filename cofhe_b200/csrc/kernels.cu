@@ -64,7 +64,7 @@ struct cofhe_b200_ctx {
   bool busy;
   cudaEvent_t order;
   // tuning knobs (cofhe_b200_set_option; the COFHE_B200_* environment variables are read once, at creation)
-  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop; } opt;
+  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop, coop_mb; } opt;
 };
 
 namespace {
@@ -316,7 +316,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   if (coop) {
     COOP_DISPATCH(ctx->coopn, {
       typedef CoopKernels<CT, CL, CN, CCAP> K;
-      K::compose(op == 1, ny, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+      K::compose(op == 1, ny, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
     })
   } else {
     const int pb = pick_block((size_t)ny * n, ctx->sms);
@@ -465,6 +465,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->opt.host_chunks = env_opt("COFHE_B200_HOST_CHUNKS", 0, 64);
   ctx->opt.host_trace = getenv("COFHE_B200_HOST_TRACE") ? 1 : 0;
   ctx->opt.coop = env_opt("COFHE_B200_COOP", 0, 1);
+  ctx->opt.coop_mb = env_opt("COFHE_B200_COOP_MB", 3, 5);
   ctx->device = device;
   ctx->sms = 0;
   if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); ctx->sms = 0; }
@@ -574,7 +575,7 @@ int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
   struct { const char *n; long *p; } tab[] = {
       {"mm_w", &ctx->opt.mm_w}, {"mm_chunks", &ctx->opt.mm_chunks}, {"mm_block", &ctx->opt.mm_block}, {"fb_w", &ctx->opt.fb_w},
       {"host_staged", &ctx->opt.host_staged}, {"host_loadc", &ctx->opt.host_loadc}, {"host_chunks", &ctx->opt.host_chunks},
-      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}};
+      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}, {"coop_mb", &ctx->opt.coop_mb}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) { *t.p = value; return COFHE_B200_OK; }
   return COFHE_B200_EINVAL;
@@ -830,6 +831,37 @@ int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_
   rc = cofhe_b200_power_of_f(ctx, n, m, ml, fm, stream);
   if (rc != COFHE_B200_OK) return rc;
   return launch_op(ctx, 0, 1, n, out + fl * n, fm, out + fl * n, 0, nullptr, 0, 0, nullptr, 0, st);
+}
+
+/* out[e] = (ct.c1[e] o h^r, ct.c2[e] o pk^r): the re-randomisation step of the single-ciphertext add / scal / negate
+ * (reference thirdparty/bicycl/src/bicycl/CL_HSM_utils.inl:188-246: c1 = h^r o ..., c2 = pk^r o ...), batched. */
+int cofhe_b200_rerandomize(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *r, uint32_t el, int shared_r, uint32_t *out,
+                           void *stream) {
+  if (!ctx || (n && (!ct || !out)) || !r || el == 0 || n >> 30) return COFHE_B200_EINVAL;
+  if (!ctx->fb_set) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t fl = 2 * ctx->na + ctx->nc;
+  size_t nr = shared_r ? 1 : n;
+  MMShape s = ctx->fb;
+  s.p = (unsigned)nr;
+  size_t pw = ctx->fastn ? mm_part_words(ctx, s) : 0;
+  // tmp: partial products | (h^r, pk^r) batch [2][fl][n] | the shared pair [2][fl][1]
+  int rc = ensure_tmp(ctx, (pw + 2 * fl * n + 2 * fl) * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  u32 *part = ctx->d_tmp, *hr = part + pw, *one = hr + 2 * fl * n;
+  if (shared_r) {
+    rc = fb_pow(ctx, 1, r, el, one, part, st);
+    if (rc != COFHE_B200_OK) return rc;
+    k_bcast<<<grid_for(n), kBlock, 0, st>>>(n, (int)(2 * fl), one, hr);
+    rc = check_launch(ctx);
+  } else {
+    rc = fb_pow(ctx, n, r, el, hr, part, st);
+  }
+  if (rc != COFHE_B200_OK) return rc;
+  return launch_op(ctx, 0, 2, n, ct, hr, out, 0, nullptr, 0, 0, nullptr, 0, st);
 }
 
 int cofhe_b200_scal_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *exp, uint32_t el, int per_elem,

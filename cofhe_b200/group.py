@@ -241,6 +241,16 @@ class ClassGroupB200:
                                                             _stream()), "scal_ciphertexts")
         return out
 
+    def rerandomize(self, ct, r):
+        """(c1 o h^r, c2 o pk^r): r one int (shared) or a list / device tensor [el, n] (per element).  With add_ciphertexts /
+        scal_ciphertexts this gives the reference's single-ciphertext add / scal / negate (CL_HSM_utils.inl:188-246), batched."""
+        n = ct.shape[-1]
+        shared = isinstance(r, int)
+        rr = r if torch.is_tensor(r) else self.ints([r] if shared else r, self.el_r)
+        out = torch.empty_like(ct)
+        capi.check(self.lib.cofhe_b200_rerandomize(self.h, n, _ptr(ct), _ptr(rr), rr.shape[0], int(shared), _ptr(out), _stream()), "rerandomize")
+        return out
+
     def beaver_open(self, ct1, ct2, a, b):
         """(ct1 - a, ct2 - b) as ciphertexts: SMPCCipherTextMultiplier's masking step, on the device."""
         o1, o2 = torch.empty_like(ct1), torch.empty_like(ct2)

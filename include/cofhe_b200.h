@@ -73,7 +73,7 @@ int cofhe_b200_reg_limbs(const cofhe_b200_ctx *ctx);
 /* Tuning knobs, -1 = automatic: "mm_w" (window bits of the matmul multi-exponentiation, 2..8), "mm_chunks" (split of
  * the inner dimension), "mm_block" (128/256/512 threads), "fb_w" (fixed-base window bits, before set_bases),
  * "host_staged", "host_loadc", "host_chunks", "host_trace" (variants of the host-pointer add), "coop" (1: cooperative
- * kernels for every form operation, 0: never).  They change how the work
+ * kernels for every form operation, 0: never), "coop_mb" (3/4/5: resident blocks per SM the cooperative kernels are compiled for).  They change how the work
  * is laid out, never the results.  The COFHE_B200_<NAME> environment variables give the defaults at creation. */
 int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value);
 
@@ -114,6 +114,14 @@ int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_
  * arguments as cofhe_b200_nupow. */
 int cofhe_b200_scal_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *exp, uint32_t el, int per_elem,
                                 const uint8_t *expneg, int shared_neg, uint32_t *out, void *stream);
+
+/* out[e] = (ct.c1[e] o h^r, ct.c2[e] o pk^r), r = r[.][e] per element (shared_r == 0) or one r[0..el) for the batch: the
+ * re-randomisation that the reference's single-ciphertext add / scal / negate apply after the homomorphic operation
+ * (CL_HSM_CipherText constructors, reference thirdparty/bicycl/src/bicycl/CL_HSM_utils.inl:188-215 and :218-246;
+ * CPUCryptoSystem::add_ciphertexts / scal_ciphertext / negate_ciphertext, include/x86_64/cpu_cryptosystem.inl:26-34, 95-98).
+ * add = add_ciphertexts + rerandomize, scal = scal_ciphertexts + rerandomize.  Needs set_bases; r in DEVICE memory. */
+int cofhe_b200_rerandomize(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *r, uint32_t el, int shared_r, uint32_t *out,
+                           void *stream);
 
 /* Beaver-triple ciphertext x ciphertext multiplication, the device side of
  * SMPCCipherTextMultiplier::handle_vector_ciphertext_mul (reference include/smpc/ciphertext_multiplications.hpp:115-160),

@@ -72,3 +72,28 @@ def test_coop_equals_other_path_at_scale(groups, name):
         G.status()
     finally:
         G.set_option("coop", -1)
+
+
+def test_coop_lockstep_regression():
+    """Eight 2053-bit pairs (one warp of the 4-lane kernel) on which the first warp-converged version fell out of step
+    after the lane-divergent scalar Euclid (illegal address on the device; the pair list was found by bisection on a
+    B200): expected results from the robust path of the same run (tests/golden/coop_case_t1.bin)."""
+    import os
+    import struct
+    import numpy as np
+    from conftest import GOLDEN
+    from cofhe_b200.group import ClassGroupB200
+    raw = open(os.path.join(GOLDEN, "coop_case_t1.bin"), "rb").read()
+    dbits, nc, n = struct.unpack("III", raw[:12])
+    t = load_golden("ref_t1.json")
+    G = ClassGroupB200(int(t["params"]["Delta"]))
+    assert G.nc == nc and (-int(t["params"]["Delta"])).bit_length() == dbits
+    arr = np.frombuffer(raw[12:], dtype=np.uint32).reshape(3, G.fl, n).copy()
+    dev = lambda a: torch.from_numpy(a.view(np.int32)).to(G.device)
+    G.set_option("coop", 1)
+    for reps in (1, 64):   # one warp, and the same warp many times over (several waves)
+        f, g, want = (dev(np.tile(arr[k], (1, reps))) for k in range(3))
+        got = G.nucomp(f, g)
+        G.status()
+        assert torch.equal(got, want)
+    G.close()

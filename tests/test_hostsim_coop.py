@@ -75,3 +75,19 @@ def test_coop_random_chains(name):
         g, b = S.run(f1, f2, inv=True); check(g, b, [O.compose_inv(x, y) for x, y in zip(f1, f2)])
         g, b = S.run(f1, dupl=True); check(g, b, [O.square(x) for x in f1])
         assert int(b.sum()) == 0
+
+
+def test_coop_full_warp_case():
+    """one full warp (8 groups of 4 lanes in lock step, each on its own 2053-bit pair) of tests/golden/coop_case_t1.bin"""
+    import os
+    import struct
+    from conftest import GOLDEN
+    raw = open(os.path.join(GOLDEN, "coop_case_t1.bin"), "rb").read()
+    dbits, nc, n = struct.unpack("III", raw[:12])
+    na = 33
+    arr = np.frombuffer(raw[12:], dtype=np.uint32).reshape(3, 2 * na + nc, n).copy()
+    lib = HS.load()
+    o = np.zeros_like(arr[0])
+    bail = np.zeros(n, dtype=np.uint8)
+    assert lib.hs_coop_compose(4, 9, na, dbits, nc, n, HS.P(arr[0]), HS.P(arr[1]), HS.P(o), 0, 0, HS.P(bail)) == 0
+    assert (o == arr[2]).all()
