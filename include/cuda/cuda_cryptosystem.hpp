@@ -160,17 +160,19 @@ namespace CoFHE
         }
         ~B200CryptoSystem() { close(); }
 
-        // ---- host side: forwarded to the embedded reference object (same RandGen draws, same results) ----------
+        // ---- host side: setup, keys, shares, RandGen, plaintext arithmetic and the text serialisers are forwarded to the
+        // embedded reference object (same RandGen draws, same results).  Everything that computes in the class group --
+        // also the single-ciphertext calls -- runs on the device (definitions below).
         SecretKey keygen() const { return host_.keygen(); }
         PublicKey keygen(const SecretKey &sk) const { return host_.keygen(sk); }
         Vector<Vector<SecretKeyShare>> keygen(const SecretKey &sk, size_t threshold, size_t num_parties) const { return host_.keygen(sk, threshold, num_parties); }
-        CipherText encrypt(const PublicKey &pk, const PlainText &pt) const { return host_.encrypt(pk, pt); }
-        PlainText decrypt(const SecretKey &sk, const CipherText &ct) const { return host_.decrypt(sk, ct); }
-        PartDecryptionResult part_decrypt(const SecretKeyShare &sks, const CipherText &ct) const { return host_.part_decrypt(sks, ct); }
-        PlainText combine_part_decryption_results(const CipherText &ct, const Vector<PartDecryptionResult> &pdrs) const { return host_.combine_part_decryption_results(ct, pdrs); }
-        CipherText add_ciphertexts(const PublicKey &pk, const CipherText &ct1, const CipherText &ct2) const { return host_.add_ciphertexts(pk, ct1, ct2); }
-        CipherText scal_ciphertext(const PublicKey &pk, const PlainText &s, const CipherText &ct) const { return host_.scal_ciphertext(pk, s, ct); }
-        CipherText negate_ciphertext(const PublicKey &pk, const CipherText &ct) const { return host_.negate_ciphertext(pk, ct); }
+        CipherText encrypt(const PublicKey &pk, const PlainText &pt) const;
+        PlainText decrypt(const SecretKey &sk, const CipherText &ct) const;
+        PartDecryptionResult part_decrypt(const SecretKeyShare &sks, const CipherText &ct) const;
+        PlainText combine_part_decryption_results(const CipherText &ct, const Vector<PartDecryptionResult> &pdrs) const;
+        CipherText add_ciphertexts(const PublicKey &pk, const CipherText &ct1, const CipherText &ct2) const;
+        CipherText scal_ciphertext(const PublicKey &pk, const PlainText &s, const CipherText &ct) const;
+        CipherText negate_ciphertext(const PublicKey &pk, const CipherText &ct) const { return this->scal_ciphertext(pk, this->make_plaintext(-1), ct); }
         PlainText generate_random_plaintext() const { return host_.generate_random_plaintext(); }
         Vector<PlainText> generate_random_beavers_triplet() const { return host_.generate_random_beavers_triplet(); }
         PlainText add_plaintexts(const PlainText &a, const PlainText &b) const { return host_.add_plaintexts(a, b); }
@@ -504,6 +506,115 @@ namespace CoFHE
         CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = get_ct(ho, i, n);
     }
 
+
+    // =================================================================================================================
+    // single-element entry points: the same device paths with n = 1 (no computation is left to the host object)
+    // =================================================================================================================
+    namespace b200_detail
+    {
+        template <class T> struct OneIn { const T *p; const T *operator[](size_t) const { return p; } };
+        template <class T> struct OneOut { T *r = nullptr; T *&operator[](size_t) { return r; } };
+        template <class T> inline T take(OneOut<T> &o) { T v(std::move(*o.r)); delete o.r; return v; }
+    }
+    // encrypt: one draw, c1 = h^r, c2 = pk^r o f^m (cpu_cryptosystem.inl:11-14 -> CL_HSM_utils.inl:161-185)
+    inline B200CryptoSystem::CipherText B200CryptoSystem::encrypt(const PublicKey &pk, const PlainText &pt) const
+    {
+        b200_detail::OneIn<PlainText> in{&pt};
+        b200_detail::OneOut<CipherText> out;
+        encrypt_flat(pk, in, 1, out);
+        return b200_detail::take(out);
+    }
+    inline B200CryptoSystem::PlainText B200CryptoSystem::decrypt(const SecretKey &sk, const CipherText &ct) const
+    {
+        b200_detail::OneIn<CipherText> in{&ct};
+        b200_detail::OneOut<PlainText> out;
+        decrypt_flat(sk, in, 1, out);
+        return b200_detail::take(out);
+    }
+    inline B200CryptoSystem::PartDecryptionResult B200CryptoSystem::part_decrypt(const SecretKeyShare &sks, const CipherText &ct) const
+    {
+        b200_detail::OneIn<CipherText> in{&ct};
+        b200_detail::OneOut<PartDecryptionResult> out;
+        part_decrypt_flat(sks, in, 1, out);
+        return b200_detail::take(out);
+    }
+    // m = dlog_F(c2 o (d_0 o d_1^-1 o ...)^-1) for one ciphertext and t parties (cpu_cryptosystem_distributed.inl:316-319)
+    inline B200CryptoSystem::PlainText B200CryptoSystem::combine_part_decryption_results(const CipherText &ct, const Vector<PartDecryptionResult> &pdrs) const
+    {
+        using namespace b200_detail;
+        if (pdrs.empty())
+            throw std::invalid_argument("No partial decryption results");
+        std::lock_guard<std::mutex> lock(mu_);
+        size_t t = pdrs.size(), cw = 2 * fl(), dw = fl() * t;
+        reserve(cw + dw + ml_);
+        uint32_t *hc = h_arena_, *hd = hc + cw, *hm = hd + dw;
+        put_form(ct.c1(), hc, 0, 1);
+        put_form(ct.c2(), hc + fl(), 0, 1);
+        for (size_t j = 0; j < t; j++)
+            put_form(pdrs[j], hd + j * fl(), 0, 1);
+        up(hc, cw + dw);
+        check(cofhe_b200_combine(ctx_, 1, (uint32_t)t, dev(hc), dev(hd), dev(hm), ml_, cofhe_b200_stream(ctx_)), "combine");
+        down(hm, ml_);
+        return get_mpz(hm, ml_, 1, false);
+    }
+    // (c1 o c1' o h^r, c2 o c2' o pk^r): homomorphic add with re-randomisation, one draw
+    // (cpu_cryptosystem.inl:26-29 -> CL_HSM2k.inl:534-550 -> CL_HSM_utils.inl:188-215)
+    inline B200CryptoSystem::CipherText B200CryptoSystem::add_ciphertexts(const PublicKey &pk, const CipherText &ct1, const CipherText &ct2) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
+        BICYCL::Mpz r = host_.get_rand_gen().random_mpz(H.encrypt_randomness_bound());
+        ensure_pk(pk);
+        size_t cw = 2 * fl();
+        reserve(3 * cw + el_r_);
+        uint32_t *h1 = h_arena_, *h2 = h1 + cw, *hr = h2 + cw, *ho = hr + el_r_;
+        put_form(ct1.c1(), h1, 0, 1);
+        put_form(ct1.c2(), h1 + fl(), 0, 1);
+        put_form(ct2.c1(), h2, 0, 1);
+        put_form(ct2.c2(), h2 + fl(), 0, 1);
+        put_mpz(r, hr, el_r_, 1, false);
+        up(h1, 2 * cw + el_r_);
+        void *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_add_ciphertexts(ctx_, 1, dev(h1), dev(h2), dev(ho), st), "add_ciphertexts");
+        check(cofhe_b200_rerandomize(ctx_, 1, dev(ho), dev(hr), el_r_, 1, dev(ho), st), "rerandomize");
+        down(ho, cw);
+        CipherText *p = get_ct(ho, 0, 1);
+        CipherText res(std::move(*p));
+        delete p;
+        return res;
+    }
+    // (c1^s o h^r, c2^s o pk^r): scalar multiplication with re-randomisation, one draw; any sign of s
+    // (cpu_cryptosystem.inl:31-34 -> CL_HSM2k.inl:561-577 -> CL_HSM_utils.inl:218-246); negate_ciphertext is s = 2^k - 1
+    inline B200CryptoSystem::CipherText B200CryptoSystem::scal_ciphertext(const PublicKey &pk, const PlainText &s, const CipherText &ct) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
+        BICYCL::Mpz r = host_.get_rand_gen().random_mpz(H.encrypt_randomness_bound());
+        ensure_pk(pk);
+        BICYCL::Mpz mag(s);
+        int sneg = mag.sgn() < 0;
+        BICYCL::Mpz::abs(mag, mag);
+        uint32_t el = limbs_of(mag);
+        size_t cw = 2 * fl();
+        reserve(2 * cw + el_r_ + el);
+        uint32_t *hc = h_arena_, *hr = hc + cw, *he = hr + el_r_, *ho = he + el;
+        put_form(ct.c1(), hc, 0, 1);
+        put_form(ct.c2(), hc + fl(), 0, 1);
+        put_mpz(r, hr, el_r_, 1, false);
+        put_mpz(mag, he, el, 1, false);
+        up(hc, cw + el_r_ + el);
+        void *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_scal_ciphertexts(ctx_, 1, dev(hc), dev(he), el, 0, nullptr, sneg, dev(ho), st), "scal_ciphertexts");
+        check(cofhe_b200_rerandomize(ctx_, 1, dev(ho), dev(hr), el_r_, 1, dev(ho), st), "rerandomize");
+        down(ho, cw);
+        CipherText *p = get_ct(ho, 0, 1);
+        CipherText res(std::move(*p));
+        delete p;
+        return res;
+    }
+
     // =================================================================================================================
     // public batched entry points: containers, shapes and exceptions as the reference's
     // =================================================================================================================
@@ -555,11 +666,20 @@ namespace CoFHE
         pdr.reshape(ct.shape());
         return pdr;
     }
-    // the reference's vector variant indexes `pdrs` both as parties and as results (cpu_cryptosystem_vector_ops.inl:42-56);
-    // that quirk is kept by forwarding
+    // the reference's vector variant takes ONE ciphertext and uses `pdrs` both as the parties' results and as the length of
+    // the output (cpu_cryptosystem_vector_ops.inl:42-56): pdrs.size() copies of the one combined plaintext.  Kept.
     inline Vector<B200CryptoSystem::PlainText *> B200CryptoSystem::combine_part_decryption_results_vector(const CipherText &ct, const Vector<PartDecryptionResult *> &pdrs) const
     {
-        return host_.combine_part_decryption_results_vector(ct, pdrs);
+        Vector<PlainText *> res(pdrs.size());
+        if (pdrs.empty())
+            return res;
+        Vector<PartDecryptionResult> parties;
+        for (size_t j = 0; j < pdrs.size(); j++)
+            parties.push_back(*pdrs[j]);
+        PlainText m = this->combine_part_decryption_results(ct, parties);
+        for (size_t i = 0; i < pdrs.size(); i++)
+            res[i] = new PlainText(m);
+        return res;
     }
     // m_i = dlog_F(c2_i o (d_0i o d_1i^-1 o ...)^-1)  (cpu_cryptosystem_tensor_ops.inl:49-73 -> finalDecrypt)
     inline Tensor<B200CryptoSystem::PlainText *> B200CryptoSystem::combine_part_decryption_results_tensor(const Tensor<CipherText *> &ct, const Vector<Tensor<PartDecryptionResult *>> &pdrs) const

@@ -137,6 +137,38 @@ int main(int argc, char** argv) {
   auto neg = cs.negate_ciphertext_tensor(pk, ct); auto neg2 = ref.negate_ciphertext_tensor(pk2, ct2);
   neg.flatten(); neg2.flatten();
   for (size_t i = 0; i < n*m; i++) bad += !(neg.at(i)->c1() == neg2.at(i)->c1() && neg.at(i)->c2() == neg2.at(i)->c2());
+  // single-ciphertext calls: same draws from the two default-seeded RandGens, results compared bit for bit
+  { auto ks2 = ref.keygen(sk2, 3, 5); (void)ks2; }  // keep the reference's RandGen in step with cs.keygen(sk, 3, 5) above
+  try {
+    auto same = [](const B200CryptoSystem::CipherText& a, const B200CryptoSystem::CipherText& b) { return a.c1() == b.c1() && a.c2() == b.c2(); };
+    B200CryptoSystem::PlainText m1((unsigned long)123456789), m2((unsigned long)42), sc((unsigned long)1000003), neg_s(-77L);
+    auto e1 = cs.encrypt(pk, m1); auto r1 = ref.encrypt(pk2, m1);
+    auto e2 = cs.encrypt(pk, m2); auto r2 = ref.encrypt(pk2, m2);
+    bad += !same(e1, r1) + !same(e2, r2);
+    auto a = cs.add_ciphertexts(pk, e1, e2); auto ar = ref.add_ciphertexts(pk2, r1, r2);
+    bad += !same(a, ar);
+    auto sm = cs.scal_ciphertext(pk, sc, e1); auto smr = ref.scal_ciphertext(pk2, sc, r1);
+    bad += !same(sm, smr);
+    auto sn = cs.scal_ciphertext(pk, neg_s, e2); auto snr = ref.scal_ciphertext(pk2, neg_s, r2);
+    bad += !same(sn, snr);
+    auto ng = cs.negate_ciphertext(pk, e1); auto ngr = ref.negate_ciphertext(pk2, r1);
+    bad += !same(ng, ngr);
+    bad += !(cs.decrypt(sk, sm) == ref.decrypt(sk2, smr)) + !(cs.decrypt(sk, ng) == ref.decrypt(sk2, ngr));
+    Vector<B200CryptoSystem::PartDecryptionResult> ps, psr;
+    Vector<B200CryptoSystem::PartDecryptionResult*> pp;
+    for (int q = 0; q < 3; q++) { ps.push_back(cs.part_decrypt(shares[q][0], a)); psr.push_back(ref.part_decrypt(shares[q][0], ar)); bad += !(ps[q] == psr[q]); }
+    bad += !(cs.combine_part_decryption_results(a, ps) == ref.combine_part_decryption_results(ar, psr));
+    bad += !(cs.combine_part_decryption_results(a, ps) == ref.decrypt(sk2, ar));
+    for (int q = 0; q < 3; q++) pp.push_back(&ps[q]);
+    auto cv = cs.combine_part_decryption_results_vector(a, pp); auto cvr = ref.combine_part_decryption_results_vector(ar, pp);
+    bad += cv.size() != cvr.size();
+    for (size_t i = 0; i < cv.size() && i < cvr.size(); i++) { bad += !(*cv[i] == *cvr[i]); delete cv[i]; delete cvr[i]; }
+    // 0-D tensors take the single-ciphertext paths (one draw each)
+    Tensor<B200CryptoSystem::CipherText*> z1(new B200CryptoSystem::CipherText(e1)), z2(new B200CryptoSystem::CipherText(e2));
+    Tensor<B200CryptoSystem::CipherText*> y1(new B200CryptoSystem::CipherText(r1)), y2(new B200CryptoSystem::CipherText(r2));
+    auto zs = cs.add_ciphertext_tensors(pk, z1, z2); auto ys = ref.add_ciphertext_tensors(pk2, y1, y2);
+    bad += !same(*zs.get_value(), *ys.get_value());
+  } catch (const std::exception& e) { std::cout << "single-ciphertext block threw: " << e.what() << " after " << bad << " mismatches" << std::endl; bad += 1000; }
   std::cout << "mismatches " << bad << " launches " << cs.gpu_launches() << std::endl;
   return bad != 0;
 }

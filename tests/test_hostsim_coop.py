@@ -87,7 +87,9 @@ def test_coop_full_warp_case():
     na = 33
     arr = np.frombuffer(raw[12:], dtype=np.uint32).reshape(3, 2 * na + nc, n).copy()
     lib = HS.load()
+    lib.hs_coop_groups(0)  # a full warp
     o = np.zeros_like(arr[0])
     bail = np.zeros(n, dtype=np.uint8)
     assert lib.hs_coop_compose(4, 9, na, dbits, nc, n, HS.P(arr[0]), HS.P(arr[1]), HS.P(o), 0, 0, HS.P(bail)) == 0
+    lib.hs_coop_groups(2)
     assert (o == arr[2]).all()
