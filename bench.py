@@ -692,6 +692,9 @@ def class_e2e(steps):
     d = json.loads(r.stdout.strip().splitlines()[-1])
     return {"value": d["b200_units_per_s"], "unit": "ct_adds/s", "reference_value": d["cpu_units_per_s"], "reference_threads": d["cpu_threads"],
             "parity": d["mismatches"] == 0, "steps": d["iters"],
+            "device_resident_value": d.get("b200_resident_units_per_s"),
+            "device_resident_api": "B200CryptoSystem::upload_ciphertexts x2, add_ciphertext_tensors(pk, DeviceBatch, DeviceBatch) x steps, "
+                                   "download_ciphertexts: the same chain with the tensors kept on the device between the calls",
             "api": "B200CryptoSystem::add_ciphertext_tensors(pk, Tensor<CipherText*>, Tensor<CipherText*>) -> Tensor<CipherText*>: "
                    "mpz_export of 2 x 16384 ciphertexts, upload, kernel, download, 16384 new CipherText per step; reference_value = "
                    "CPUCryptoSystem::add_ciphertext_tensors on the same host in the same process"}

@@ -31,9 +31,17 @@ SIGNATURES = {
     "cofhe_b200_reg_limbs": (ctypes.c_int, [vp]),
     "cofhe_b200_set_option": (i32, [vp, ctypes.c_char_p, ctypes.c_long]),
     "cofhe_b200_scal_ciphertexts": (i32, [vp, sz, vp, vp, u32, i32, vp, i32, vp, vp]),
+    "cofhe_b200_beaver_triplets": (i32, [vp, sz, vp, vp, u32, vp, u32, vp, vp]),
+    "cofhe_b200_ct_matmul_expand": (i32, [vp, sz, sz, sz, vp, vp, vp, vp, vp]),
+    "cofhe_b200_ct_matmul_reduce": (i32, [vp, sz, sz, sz, vp, vp, vp, vp]),
+    "cofhe_b200_copy": (i32, [vp, vp, vp, sz, vp]),
+    "cofhe_b200_plaintexts_mod2k": (i32, [vp, sz, vp, u32, vp, vp, u32, vp]),
     "cofhe_b200_rerandomize": (i32, [vp, sz, vp, vp, u32, i32, vp, vp]),
     "cofhe_b200_beaver_open": (i32, [vp, sz, vp, vp, vp, vp, vp, vp, vp]),
     "cofhe_b200_beaver_close": (i32, [vp, sz, vp, vp, u32, vp, vp, vp, vp, u32, vp, vp]),
+    "cofhe_b200_wire_bound_kind": (sz, [vp, i32, u32, sz, u32]),
+    "cofhe_b200_wire_to_batch": (i32, [vp, i32, vp, sz, u32, sz, vp, u32, vp, vp]),
+    "cofhe_b200_batch_to_wire": (i32, [vp, i32, u32, vp, sz, vp, u32, vp, vp, sz, ctypes.POINTER(sz), vp]),
     "cofhe_b200_wire_header": (i32, [vp, sz, ctypes.POINTER(u32), vp, u32, ctypes.POINTER(sz)]),
     "cofhe_b200_wire_bound": (sz, [vp, u32, sz]),
     "cofhe_b200_wire_to_cts": (i32, [vp, vp, sz, u32, sz, vp, vp]),

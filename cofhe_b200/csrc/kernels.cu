@@ -8,6 +8,7 @@
 #include <string.h>
 #include <time.h>
 #include <mutex>
+#include <vector>
 #include <new>
 #include <utility>
 
@@ -64,6 +65,10 @@ struct cofhe_b200_ctx {
   bool busy;
   cudaEvent_t order;
   // tuning knobs (cofhe_b200_set_option; the COFHE_B200_* environment variables are read once, at creation)
+  // device blocks handed out by cofhe_b200_dev_alloc (live) and returned ones kept for reuse (pool)
+  struct Block { void *p; size_t bytes; };
+  std::vector<Block> live, pool;
+  size_t pool_bytes = 0;
   struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop, coop_mb; } opt;
 };
 
@@ -529,6 +534,7 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
   if (ctx->d_fb_tab) cudaFree(ctx->d_fb_tab);
+  for (auto &b : ctx->pool) cudaFree(b.p);
   if (ctx->xfer) cudaStreamDestroy(ctx->xfer);
   if (ctx->order) cudaEventDestroy(ctx->order);
   for (auto &L : ctx->lane) {
@@ -802,6 +808,32 @@ int cofhe_b200_fixed_base_pow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *exp
   return fb_pow(ctx, n, exps, el, out, ctx->d_tmp, (cudaStream_t)stream);
 }
 
+// out[.][e] = (sign[e] ? -mag[e] : mag[e]) mod 2^k as ml_out limb rows: what Mpz::mod(m, pt, 2^k) gives on the host
+__global__ void __launch_bounds__(kBlock) k_pt_mod2k(size_t n, int k, const u32 *mag, int ml, const unsigned char *sign, u32 *out, int ml_out) {
+  size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const bool neg = sign && sign[e];
+  u32 carry = 1;
+  for (int i = 0; i < ml_out; i++) {
+    u32 w = i < ml ? mag[(size_t)i * n + e] : 0u;
+    if (neg) { u32 v = ~w + carry; carry = (carry && v == 0) ? 1u : 0u; w = v; }
+    int hi = k - 32 * i;  // bits of this limb below 2^k
+    if (hi <= 0) w = 0;
+    else if (hi < 32) w &= (1u << hi) - 1u;
+    out[(size_t)i * n + e] = w;
+  }
+}
+int cofhe_b200_plaintexts_mod2k(cofhe_b200_ctx *ctx, size_t n, const uint32_t *mag, uint32_t ml, const uint8_t *sign, uint32_t *out,
+                                uint32_t ml_out, void *stream) {
+  if (!ctx || (n && (!mag || !out)) || ml == 0 || ml_out == 0) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme || ctx->k <= 0) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  k_pt_mod2k<<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(n, ctx->k, mag, (int)ml, sign, out, (int)ml_out);
+  return check_launch(ctx);
+}
+
 int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_t ml, const uint32_t *r, uint32_t el, int shared_r,
                        uint32_t *out, void *stream) {
   if (!ctx || (n && (!m || !out)) || !r || ml == 0 || el == 0 || n >> 30) return COFHE_B200_EINVAL;
@@ -928,6 +960,150 @@ int cofhe_b200_beaver_close(cofhe_b200_ctx *ctx, size_t n, const uint32_t *pt1, 
   return launch_op(ctx, 0, 2, n, t1, out, out, 0, nullptr, 0, 0, nullptr, 0, st);
 }
 
+// pt3[.][3 i + c] = (a_i, b_i, a_i * b_i mod 2^(32 ml)) for c = 0, 1, 2: the [n, 3] plaintext tensor of
+// BeaversTripletGenerator::generate (reference include/smpc/beavers_triplet_generation.hpp:19-27), row-major
+__global__ void __launch_bounds__(kBlock) k_triplet_rows(size_t n, int ml, const u32 *a, const u32 *b, u32 *pt3) {
+  size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  u32 r[16];
+  for (int i = 0; i < ml; i++) r[i] = 0;
+  for (int i = 0; i < ml; i++) {
+    unsigned long long c = 0;
+    u32 ai = a[(size_t)i * n + e];
+    for (int j = 0; i + j < ml; j++) {
+      c += (unsigned long long)ai * b[(size_t)j * n + e] + r[i + j];
+      r[i + j] = (u32)c;
+      c >>= 32;
+    }
+  }
+  for (int i = 0; i < ml; i++) {
+    pt3[(size_t)i * 3 * n + 3 * e] = a[(size_t)i * n + e];
+    pt3[(size_t)i * 3 * n + 3 * e + 1] = b[(size_t)i * n + e];
+    pt3[(size_t)i * 3 * n + 3 * e + 2] = r[i];
+  }
+}
+/* Beaver triplets: out = encrypt_tensor([[a_i, b_i, a_i b_i]]) -- 3n ciphertexts in the reference's [n, 3] row-major order,
+ * ONE randomness for the tensor (reference include/smpc/beavers_triplet_generation.hpp:17-37; the cache of
+ * include/smpc/smpc_client.hpp:17,218 is filled by calls of this). */
+int cofhe_b200_beaver_triplets(cofhe_b200_ctx *ctx, size_t n, const uint32_t *a, const uint32_t *b, uint32_t ml, const uint32_t *r, uint32_t el,
+                               uint32_t *out, void *stream) {
+  if (!ctx || (n && (!a || !b || !out)) || !r || ml == 0 || ml > 16 || el == 0 || (3 * n) >> 30) return COFHE_B200_EINVAL;
+  if (!ctx->fb_set || !ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  {
+    Enter g(ctx, (cudaStream_t)stream);
+    if (!g.ok) return COFHE_B200_ECUDA;
+    int rc = ensure_work(ctx, (size_t)ml * 3 * n * sizeof(u32));
+    if (rc != COFHE_B200_OK) return rc;
+    k_triplet_rows<<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(n, (int)ml, a, b, ctx->d_work);
+    rc = check_launch(ctx);
+    if (rc != COFHE_B200_OK) return rc;
+  }
+  return cofhe_b200_encrypt(ctx, 3 * n, ctx->d_work, ml, r, el, 1, out, stream);
+}
+
+// ---- ciphertext x ciphertext MATRIX product: the n*m*p expansion around the Beaver multiplication and the reduction of
+// its n*m*p products (reference include/smpc/ciphertext_multiplications.hpp:51-110) -------------------------------------
+// out1[(i*m + j)*p + k] = ct1[i*m + j], out2[(i*m + j)*p + k] = ct2[j*p + k]   (rows = 2 * form limbs; :58-70)
+__global__ void __launch_bounds__(kBlock) k_ctmm_expand(int rows, size_t n, size_t m, size_t p, const u32 *ct1, const u32 *ct2, u32 *out1,
+                                                        u32 *out2) {
+  const size_t nmp = n * m * p;
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)rows * nmp) return;
+  size_t r = t / nmp, e = t % nmp, ij = e / p, k = e % p, j = ij % m;
+  out1[t] = ct1[r * (n * m) + ij];
+  out2[t] = ct2[r * (m * p) + j * p + k];
+}
+// slab j of the products (the n*p elements (i, k) of inner index j) into a batch of `cnt` slabs starting at slab j0:
+// dst[r][(j - j0)*np + i*p + k] = prod[r][(i*m + j)*p + k]
+__global__ void __launch_bounds__(kBlock) k_ctmm_slabs(int rows, size_t n, size_t m, size_t p, size_t j0, size_t cnt, const u32 *prod, u32 *dst) {
+  const size_t np = n * p, tot = cnt * np;
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)rows * tot) return;
+  size_t r = t / tot, e = t % tot, j = j0 + e / np, ik = e % np, i = ik / p, k = ik % p;
+  dst[t] = prod[r * (n * m * p) + (i * m + j) * p + k];
+}
+// dst[r][e] (row stride dst_n) = src[r][src_off + e] (row stride src_n) for e < cnt: a range of elements as its own batch
+__global__ void __launch_bounds__(kBlock) k_cols_copy(int rows, size_t cnt, u32 *dst, size_t dst_n, const u32 *src, size_t src_n, size_t src_off) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)rows * cnt) return;
+  size_t r = t / cnt, e = t % cnt;
+  dst[r * dst_n + e] = src[r * src_n + src_off + e];
+}
+
+int cofhe_b200_ct_matmul_expand(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out1,
+                                uint32_t *out2, void *stream) {
+  if (!ctx || !ct1 || !ct2 || !out1 || !out2 || n == 0 || m == 0 || p == 0 || (n * m * p) >> 30) return COFHE_B200_EINVAL;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  int rows = (int)(2 * (2 * ctx->na + ctx->nc));
+  size_t tot = (size_t)rows * n * m * p;
+  k_ctmm_expand<<<(unsigned)((tot + kBlock - 1) / kBlock), kBlock, 0, (cudaStream_t)stream>>>(rows, n, m, p, ct1, ct2, out1, out2);
+  return check_launch(ctx);
+}
+
+// out[i*p + k] = init o prod_j prod[(i*m + j)*p + k]: a balanced tree over j -- every level is ONE batched composition launch over
+// half of the remaining slabs (log2 m launches of decreasing size instead of m launches of n*p elements)
+int cofhe_b200_ct_matmul_reduce(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *prod, const uint32_t *init, uint32_t *out,
+                                void *stream) {
+  if (!ctx || !prod || !init || !out || n == 0 || m == 0 || p == 0 || (n * m * p) >> 30) return COFHE_B200_EINVAL;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int rows = (int)(2 * (2 * ctx->na + ctx->nc));
+  const size_t np = n * p, half = (m + 1) / 2;
+  // work: A | B | C (each up to `half` slabs) | E (the slab left over at odd levels, accumulated) | Z (init broadcast)
+  int rc = ensure_work(ctx, ((size_t)rows * (3 * half + 2) * np) * sizeof(u32));
+  if (rc != COFHE_B200_OK) return rc;
+  u32 *A = ctx->d_work, *B = A + (size_t)rows * half * np, *C = B + (size_t)rows * half * np, *E = C + (size_t)rows * half * np,
+      *Z = E + (size_t)rows * np;
+  auto blocks = [](size_t tot) { return (unsigned)((tot + kBlock - 1) / kBlock); };
+  k_bcast<<<grid_for(np), kBlock, 0, st>>>(np, rows, init, Z);
+  ctx->launches++;
+  bool have_e = false;
+  size_t cur = m;
+  const u32 *src = nullptr;  // level input: nullptr = the products themselves
+  size_t src_n = 0;
+  while (cur > 1) {
+    size_t h = cur / 2;
+    if (!src) {
+      k_ctmm_slabs<<<blocks((size_t)rows * h * np), kBlock, 0, st>>>(rows, n, m, p, 0, h, prod, A);
+      k_ctmm_slabs<<<blocks((size_t)rows * h * np), kBlock, 0, st>>>(rows, n, m, p, h, h, prod, B);
+    } else {
+      k_cols_copy<<<blocks((size_t)rows * h * np), kBlock, 0, st>>>(rows, h * np, A, h * np, src, src_n, 0);
+      k_cols_copy<<<blocks((size_t)rows * h * np), kBlock, 0, st>>>(rows, h * np, B, h * np, src, src_n, h * np);
+    }
+    ctx->launches += 2;
+    if (cur & 1) {
+      // the odd slab out joins the side accumulator
+      u32 *tmp = have_e ? (u32 *)out : E;  // out is free until the end: use it as the landing buffer of the slab
+      if (!src) k_ctmm_slabs<<<blocks((size_t)rows * np), kBlock, 0, st>>>(rows, n, m, p, 2 * h, 1, prod, tmp);
+      else k_cols_copy<<<blocks((size_t)rows * np), kBlock, 0, st>>>(rows, np, tmp, np, src, src_n, 2 * h * np);
+      ctx->launches++;
+      if (have_e) {
+        rc = launch_op(ctx, 0, 2, np, E, tmp, E, 0, nullptr, 0, 0, nullptr, 0, st);
+        if (rc != COFHE_B200_OK) return rc;
+      }
+      have_e = true;
+    }
+    rc = launch_op(ctx, 0, 2, h * np, A, B, C, 0, nullptr, 0, 0, nullptr, 0, st);
+    if (rc != COFHE_B200_OK) return rc;
+    src = C; src_n = h * np;
+    cur = h;
+  }
+  const u32 *last = src;
+  if (!src) {  // m == 1: the products are the single slab
+    k_ctmm_slabs<<<blocks((size_t)rows * np), kBlock, 0, st>>>(rows, n, m, p, 0, 1, prod, A);
+    ctx->launches++;
+    last = A;
+  }
+  rc = launch_op(ctx, 0, 2, np, Z, last, Z, 0, nullptr, 0, 0, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  if (have_e) return launch_op(ctx, 0, 2, np, Z, E, out, 0, nullptr, 0, 0, nullptr, 0, st);
+  k_cols_copy<<<blocks((size_t)rows * np), kBlock, 0, st>>>(rows, np, out, np, Z, np, 0);
+  return check_launch(ctx);
+}
+
 int cofhe_b200_part_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const uint32_t *share, uint32_t el, int share_neg,
                             uint32_t *out, void *stream) {
   if (!ctx || (n && (!ct || !out)) || !share || el == 0 || el > 64) return COFHE_B200_EINVAL;
@@ -991,12 +1167,49 @@ int cofhe_b200_dev_alloc(cofhe_b200_ctx *ctx, size_t bytes, void **ptr) {
   if (bytes == 0) return COFHE_B200_OK;
   DevGuard g(ctx->device);
   if (!g.ok) return COFHE_B200_ECUDA;
-  if (cudaMalloc(ptr, bytes) != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return COFHE_B200_ENOMEM; }
+  {
+    // recycled block: freed buffers are kept (cudaMalloc / cudaFree synchronise the device and cost ~0.1-1 ms each, which
+    // would dominate chained calls on device-resident tensors); work on a context is ordered (one stream at a time, stream
+    // changes wait for the previous stream), so a block handed out again is never still in use by an earlier call
+    std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+    size_t best = ctx->pool.size();
+    for (size_t i = 0; i < ctx->pool.size(); i++)
+      if (ctx->pool[i].bytes >= bytes && ctx->pool[i].bytes <= 2 * bytes + 4096 &&
+          (best == ctx->pool.size() || ctx->pool[i].bytes < ctx->pool[best].bytes)) best = i;
+    if (best != ctx->pool.size()) {
+      *ptr = ctx->pool[best].p;
+      ctx->live.push_back(ctx->pool[best]);
+      ctx->pool_bytes -= ctx->pool[best].bytes;
+      ctx->pool.erase(ctx->pool.begin() + best);
+      return COFHE_B200_OK;
+    }
+  }
+  if (cudaMalloc(ptr, bytes) != cudaSuccess) {
+    cudaGetLastError();
+    // out of memory: drop the recycled blocks and try once more
+    {
+      std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+      for (auto &b : ctx->pool) cudaFree(b.p);
+      ctx->pool.clear(); ctx->pool_bytes = 0;
+    }
+    if (cudaMalloc(ptr, bytes) != cudaSuccess) { cudaGetLastError(); *ptr = nullptr; return COFHE_B200_ENOMEM; }
+  }
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  ctx->live.push_back({*ptr, bytes});
   return COFHE_B200_OK;
 }
 void cofhe_b200_dev_free(cofhe_b200_ctx *ctx, void *ptr) {
   if (!ctx || !ptr) return;
   DevGuard g(ctx->device);
+  std::lock_guard<std::recursive_mutex> lk(ctx->mu);
+  for (size_t i = 0; i < ctx->live.size(); i++)
+    if (ctx->live[i].p == ptr) {
+      cofhe_b200_ctx::Block b = ctx->live[i];
+      ctx->live.erase(ctx->live.begin() + i);
+      if (ctx->pool_bytes + b.bytes <= ((size_t)4 << 30) && ctx->pool.size() < 64) { ctx->pool.push_back(b); ctx->pool_bytes += b.bytes; }
+      else cudaFree(b.p);
+      return;
+    }
   cudaFree(ptr);
 }
 int cofhe_b200_host_alloc(size_t bytes, void **ptr) {
@@ -1024,6 +1237,14 @@ int cofhe_b200_download(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t 
   CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
   return COFHE_B200_OK;
 }
+int cofhe_b200_copy(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream) {
+  if (!ctx || (bytes && (!dst || !src))) return COFHE_B200_EINVAL;
+  if (bytes == 0) return COFHE_B200_OK;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return COFHE_B200_OK;
+}
 int cofhe_b200_device_count(void) {
   int c = 0;
   if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -1044,43 +1265,56 @@ int cofhe_b200_wire_header(const uint8_t *wire, size_t bytes, uint32_t *ndim, ui
     if (d && cnt > ((size_t)1 << 40) / d) return COFHE_B200_EINVAL;
     cnt *= d;
   }
-  if (bytes < 4 + 4 * (size_t)nd + 48 * cnt) return COFHE_B200_EINVAL;
+  if (bytes < 4 + 4 * (size_t)nd + 8 * cnt) return COFHE_B200_EINVAL;  // at least one table entry per element
   *ndim = nd;
   *n = cnt;
   return COFHE_B200_OK;
 }
 
-size_t cofhe_b200_wire_bound(const cofhe_b200_ctx *ctx, uint32_t ndim, size_t n) {
-  if (!ctx) return 0;
-  return 4 + 4 * (size_t)ndim + n * (48 + 4 * (size_t)(4 * ctx->na + 1) + 2 * (size_t)(4 * ctx->nc + 1));
-}
+static int wire_slots_of(int kind) { return kind == 0 ? 6 : (kind == 1 ? 3 : 1); }
 
-int cofhe_b200_wire_to_cts(cofhe_b200_ctx *ctx, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
-                           void *stream) {
-  if (!ctx || (n && (!wire || !out))) return COFHE_B200_EINVAL;
+size_t cofhe_b200_wire_bound_kind(const cofhe_b200_ctx *ctx, int kind, uint32_t ndim, size_t n, uint32_t ml) {
+  if (!ctx || kind < 0 || kind > 2) return 0;
+  size_t per;
+  if (kind == 2) per = 8 + (4 * (size_t)ml + 1);
+  else per = (size_t)(kind == 0 ? 2 : 1) * (24 + 2 * (size_t)(4 * ctx->na + 1) + (size_t)(4 * ctx->nc + 1));
+  return 4 + 4 * (size_t)ndim + n * per;
+}
+size_t cofhe_b200_wire_bound(const cofhe_b200_ctx *ctx, uint32_t ndim, size_t n) { return cofhe_b200_wire_bound_kind(ctx, 0, ndim, n, 0); }
+
+int cofhe_b200_wire_to_batch(cofhe_b200_ctx *ctx, int kind, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
+                             uint32_t ml, uint8_t *sign_out, void *stream) {
+  if (!ctx || kind < 0 || kind > 2 || (n && (!wire || !out)) || (kind == 2 && (ml == 0 || ml > 4096))) return COFHE_B200_EINVAL;
+  const size_t S = wire_slots_of(kind);
   size_t head = 4 + 4 * (size_t)ndim;
-  if (bytes < head + 48 * n) return COFHE_B200_EINVAL;
+  if (bytes < head + 8 * S * n) return COFHE_B200_EINVAL;
   if (n == 0) return COFHE_B200_OK;
   Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
-  WireShape s{(int)ctx->na, (int)ctx->nc, n};
-  unsigned blocks = (unsigned)((6 * n + kWireBlock - 1) / kWireBlock);
-  k_wire_read<<<blocks, kWireBlock, 0, (cudaStream_t)stream>>>(s, wire + head, wire + head + 48 * n, (unsigned long long)(bytes - head - 48 * n),
-                                                             out, ctx->d_err);
+  WireShape s{(int)ctx->na, (int)ctx->nc, n, kind, (int)ml};
+  unsigned blocks = (unsigned)((S * n + kWireBlock - 1) / kWireBlock);
+  k_wire_read<<<blocks, kWireBlock, 0, (cudaStream_t)stream>>>(s, wire + head, wire + head + 8 * S * n,
+                                                             (unsigned long long)(bytes - head - 8 * S * n), out, sign_out, ctx->d_err);
   return check_launch(ctx);
 }
+int cofhe_b200_wire_to_cts(cofhe_b200_ctx *ctx, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
+                           void *stream) {
+  return cofhe_b200_wire_to_batch(ctx, 0, wire, bytes, ndim, n, out, 0, nullptr, stream);
+}
 
-int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *dims, size_t n, const uint32_t *ct, uint8_t *wire,
-                           size_t cap, size_t *written, void *stream) {
-  if (!ctx || !written || (ndim && !dims) || ndim > 8 || !wire || (n && !ct)) return COFHE_B200_EINVAL;
+int cofhe_b200_batch_to_wire(cofhe_b200_ctx *ctx, int kind, uint32_t ndim, const uint32_t *dims, size_t n, const uint32_t *in, uint32_t ml,
+                             const uint8_t *sign_in, uint8_t *wire, size_t cap, size_t *written, void *stream) {
+  if (!ctx || kind < 0 || kind > 2 || !written || (ndim && !dims) || ndim > 8 || !wire || (n && !in) || (kind == 2 && (ml == 0 || ml > 4096)))
+    return COFHE_B200_EINVAL;
   size_t cnt = 1;
   for (uint32_t i = 0; i < ndim; i++) cnt *= dims[i];
   if (cnt != n) return COFHE_B200_EINVAL;
   Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
+  const size_t S = wire_slots_of(kind);
   size_t head = 4 + 4 * (size_t)ndim;
-  *written = head + 48 * n;
+  *written = head + 8 * S * n;
   if (cap < *written) return COFHE_B200_EINVAL;
   uint32_t hb[9];
   hb[0] = ndim;
@@ -1088,16 +1322,16 @@ int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *d
   CUDA_TRY(cudaMemcpyAsync(wire, hb, head, cudaMemcpyHostToDevice, st));
   CUDA_TRY(cudaStreamSynchronize(st));  // hb is a stack buffer
   if (n == 0) return COFHE_B200_OK;
-  // scratch: offsets u64[6n] | block totals u64[nb] | sum u64 | sizes u32[6n] | flags u8[6n]
-  size_t m = 6 * n, nb = (m + kScanBlock - 1) / kScanBlock;
+  // scratch: offsets u64[m] | block totals u64[nb] | sum u64 | sizes u32[m] | flags u8[m]
+  size_t m = S * n, nb = (m + kScanBlock - 1) / kScanBlock;
   int rc = ensure_work(ctx, (m + nb + 1) * 8 + m * 4 + m);
   if (rc != COFHE_B200_OK) return rc;
   unsigned long long *offs = (unsigned long long *)ctx->d_work, *totals = offs + m, *sum = totals + nb;
   u32 *sizes = (u32 *)(sum + 1);
   unsigned char *flags = (unsigned char *)(sizes + m);
-  WireShape s{(int)ctx->na, (int)ctx->nc, n};
+  WireShape s{(int)ctx->na, (int)ctx->nc, n, kind, (int)ml};
   unsigned blocks = (unsigned)((m + kWireBlock - 1) / kWireBlock);
-  k_wire_sizes<<<blocks, kWireBlock, 0, st>>>(s, ct, sizes, flags);
+  k_wire_sizes<<<blocks, kWireBlock, 0, st>>>(s, in, sign_in, sizes, flags);
   ctx->launches++;
   k_scan_blocks<<<(unsigned)nb, kScanBlock, 0, st>>>(m, sizes, offs, totals);
   ctx->launches++;
@@ -1107,10 +1341,14 @@ int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *d
   unsigned long long body = 0;
   CUDA_TRY(cudaMemcpyAsync(&body, sum, 8, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
-  *written = head + 48 * n + (size_t)body;
+  *written = head + 8 * S * n + (size_t)body;
   if (cap < *written) return COFHE_B200_EINVAL;  // *written tells the caller what is needed
-  k_wire_write<<<blocks, kWireBlock, 0, st>>>(s, ct, sizes, flags, offs, totals, wire + head, wire + head + 48 * n);
+  k_wire_write<<<blocks, kWireBlock, 0, st>>>(s, in, sizes, flags, offs, totals, wire + head, wire + head + 8 * S * n);
   return check_launch(ctx);
+}
+int cofhe_b200_cts_to_wire(cofhe_b200_ctx *ctx, uint32_t ndim, const uint32_t *dims, size_t n, const uint32_t *ct, uint8_t *wire,
+                           size_t cap, size_t *written, void *stream) {
+  return cofhe_b200_batch_to_wire(ctx, 0, ndim, dims, n, ct, 0, nullptr, wire, cap, written, stream);
 }
 
 }  // extern "C"

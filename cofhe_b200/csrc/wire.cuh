@@ -16,13 +16,23 @@
 
 namespace cofhe {
 
+// The three tensor formats of the reference share this layout and differ in the integers per element:
+//   kind 0  ciphertext tensor   6 per element: c1.a c1.b c1.c c2.a c2.b c2.c   (cpu_cryptosystem.inl:322-520)
+//   kind 1  part-decryption-result tensor (forms)   3 per element: a b c      (cpu_cryptosystem.inl:510-635)
+//   kind 2  plaintext tensor    1 per element, any sign                        (cpu_cryptosystem.inl:229-318)
+// SoA side: ciphertext batch [2][2na+nc][n]; form batch [2na+nc][n]; plaintexts as magnitudes [ml][n] plus one sign byte
+// per element (plaintexts are not reduced modulo 2^k by the reference: sums and products of plaintexts travel too).
 struct WireShape {
   int na, nc;       // limbs of a / b and of c in the SoA batch
-  size_t n;         // ciphertexts
+  size_t n;         // elements
+  int kind;         // 0 ciphertexts, 1 forms, 2 plaintexts
+  int ml;           // limbs per plaintext magnitude (kind 2)
 };
+QF_HD int wire_slots(const WireShape &s) { return s.kind == 0 ? 6 : (s.kind == 1 ? 3 : 1); }
 
-// (row offset inside a ciphertext batch [2][2 na + nc][n], limb count, is-b) of coefficient j in 0..5
+// (row offset inside the batch, limb count, two's complement?) of integer j of an element
 QF_HD void wire_slot(const WireShape &s, int j, size_t *row, int *limbs, bool *is_b) {
+  if (s.kind == 2) { *row = 0; *limbs = s.ml; *is_b = false; return; }
   int f = j / 3, c = j % 3, fl = 2 * s.na + s.nc;
   *row = (size_t)f * fl + (c == 0 ? 0 : c == 1 ? s.na : 2 * s.na);
   *limbs = c == 2 ? s.nc : s.na;
@@ -33,9 +43,10 @@ QF_HD void wire_slot(const WireShape &s, int j, size_t *row, int *limbs, bool *i
 constexpr int kWireBlock = 256;
 
 // 1. per slot (wire order k = 6 i + j): reserved size and sign flag
-__global__ void __launch_bounds__(kWireBlock) k_wire_sizes(WireShape s, const u32 *ct, u32 *sizes, unsigned char *flags) {
+__global__ void __launch_bounds__(kWireBlock) k_wire_sizes(WireShape s, const u32 *ct, const unsigned char *sgn, u32 *sizes, unsigned char *flags) {
+  const int S = wire_slots(s);
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 6 * s.n) return;
+  if (t >= S * s.n) return;
   int j = (int)(t / s.n);
   size_t i = t % s.n, row;
   int nl;
@@ -52,9 +63,9 @@ __global__ void __launch_bounds__(kWireBlock) k_wire_sizes(WireShape s, const u3
     if (neg) { u32 v = ~w + carry; carry = (carry && v == 0) ? 1u : 0u; w = v; }
     if (w) { bits = 32 * l + 32 - __clz(w); nonzero = true; }
   }
-  size_t k = 6 * i + j;
+  size_t k = (size_t)S * i + j;
   sizes[k] = (u32)((bits > 0 ? bits : 1) / 8 + 1);
-  flags[k] = (neg || !nonzero) ? 1 : 0;
+  flags[k] = (neg || !nonzero || (s.kind == 2 && sgn && sgn[i])) ? 1 : 0;
 }
 
 // 2. exclusive prefix sum of u32 sizes into u64 offsets: per-block scan, scan of the block totals, add.
@@ -103,14 +114,15 @@ __global__ void __launch_bounds__(kScanBlock) k_scan_totals(size_t nb, unsigned 
 __global__ void __launch_bounds__(kWireBlock) k_wire_write(WireShape s, const u32 *ct, const u32 *sizes, const unsigned char *flags,
                                                            const unsigned long long *offs, const unsigned long long *totals,
                                                            unsigned char *table, unsigned char *body) {
+  const int S = wire_slots(s);
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 6 * s.n) return;
+  if (t >= S * s.n) return;
   int j = (int)(t / s.n);
   size_t i = t % s.n, row;
   int nl;
   bool is_b;
   wire_slot(s, j, &row, &nl, &is_b);
-  size_t k = 6 * i + j;
+  size_t k = (size_t)S * i + j;
   unsigned long long off = offs[k] + totals[k / kScanBlock];
   unsigned long long entry = off | ((unsigned long long)flags[k] << 63);
   for (int b = 0; b < 8; b++) table[8 * k + b] = (unsigned char)(entry >> (8 * b));
@@ -131,20 +143,22 @@ __global__ void __launch_bounds__(kWireBlock) k_wire_write(WireShape s, const u3
 
 // wire -> SoA.  table/body as above, body_len = bytes of the magnitude area.  err: 1 = an integer does not fit its limbs
 __global__ void __launch_bounds__(kWireBlock) k_wire_read(WireShape s, const unsigned char *table, const unsigned char *body,
-                                                          unsigned long long body_len, u32 *ct, int *err) {
+                                                          unsigned long long body_len, u32 *ct, unsigned char *sgn, int *err) {
+  const int S = wire_slots(s);
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 6 * s.n) return;
+  if (t >= S * s.n) return;
   int j = (int)(t / s.n);
   size_t i = t % s.n, row;
   int nl;
   bool is_b;
   wire_slot(s, j, &row, &nl, &is_b);
-  size_t k = 6 * i + j;
+  size_t k = (size_t)S * i + j;
+  const size_t last = (size_t)S * s.n;
   unsigned long long e0 = 0, e1 = 0;
   for (int b = 0; b < 8; b++) e0 |= (unsigned long long)table[8 * k + b] << (8 * b);
-  if (k + 1 < 6 * s.n) { for (int b = 0; b < 8; b++) e1 |= (unsigned long long)table[8 * (k + 1) + b] << (8 * b); }
+  if (k + 1 < last) { for (int b = 0; b < 8; b++) e1 |= (unsigned long long)table[8 * (k + 1) + b] << (8 * b); }
   const unsigned long long mask = ~(1ull << 63);
-  unsigned long long lo = e0 & mask, hi = (k + 1 < 6 * s.n) ? (e1 & mask) : body_len;
+  unsigned long long lo = e0 & mask, hi = (k + 1 < last) ? (e1 & mask) : body_len;
   bool flag = (e0 >> 63) != 0, bad = hi < lo || hi > body_len;
   unsigned long long len = bad ? 0 : hi - lo;
   const unsigned char *src = body + lo;
@@ -169,6 +183,12 @@ __global__ void __launch_bounds__(kWireBlock) k_wire_read(WireShape s, const uns
     bool zero_mag = carry != 0 && neg;  // ~0 + 1 rippled through every limb: the magnitude was 0
     if (!neg && msb) bad = true;
     if (neg && !zero_mag && !msb) bad = true;
+  } else if (s.kind == 2) {
+    // plaintexts are sign-magnitude on the SoA side: the flag with a non-zero magnitude is a negative value
+    bool any = false;
+    for (int l = 0; l < nl; l++) any = any || p[(size_t)l * s.n] != 0;
+    if (sgn) sgn[i] = (flag && any) ? 1 : 0;
+    else if (flag && any) bad = true;  // the caller has no room for signs
   } else if (!is_b && flag && !bad) {
     // a and c are positive in every valid form; the flag can only mean zero
     bool any = false;

@@ -175,6 +175,47 @@ class ClassGroupB200:
                                                    _stream()), "cts_to_wire")
         return bytes(dev[:written.value].cpu().numpy())
 
+    def _wire_in(self, kind, data, ml=0, signs=False):
+        buf = np.frombuffer(bytes(data), dtype=np.uint8)
+        ndim, n = ctypes.c_uint32(), ctypes.c_size_t()
+        dims = (ctypes.c_uint32 * 8)()
+        capi.check(self.lib.cofhe_b200_wire_header(buf.ctypes.data_as(ctypes.c_void_p), buf.size, ctypes.byref(ndim), dims, 8,
+                                                   ctypes.byref(n)), "wire_header")
+        dev = torch.from_numpy(buf.copy()).to(self.device)
+        rows = {0: (2, self.fl), 1: (self.fl,), 2: (ml,)}[kind]
+        out = torch.empty(rows + (n.value,), dtype=torch.int32, device=self.device)
+        sg = torch.zeros(max(1, n.value), dtype=torch.uint8, device=self.device) if signs else None
+        capi.check(self.lib.cofhe_b200_wire_to_batch(self.h, kind, _ptr(dev), buf.size, ndim.value, n.value, _ptr(out), ml,
+                                                     _ptr(sg) if sg is not None else None, _stream()), "wire_to_batch")
+        torch.cuda.current_stream().synchronize()  # `dev` must outlive the kernel
+        return [int(dims[i]) for i in range(ndim.value)], out, sg
+
+    def _wire_out(self, kind, shape, batch, ml=0, signs=None):
+        n = batch.shape[-1]
+        cap = int(self.lib.cofhe_b200_wire_bound_kind(self.h, kind, len(shape), n, ml))
+        dev = torch.empty(cap, dtype=torch.uint8, device=self.device)
+        dims = (ctypes.c_uint32 * max(1, len(shape)))(*shape)
+        written = ctypes.c_size_t()
+        capi.check(self.lib.cofhe_b200_batch_to_wire(self.h, kind, len(shape), dims, n, _ptr(batch), ml,
+                                                     _ptr(signs) if signs is not None else None, _ptr(dev), cap, ctypes.byref(written),
+                                                     _stream()), "batch_to_wire")
+        return bytes(dev[:written.value].cpu().numpy())
+
+    def wire_to_forms(self, data):
+        """bytes of serialize_part_decryption_result_tensor -> (shape, device form batch [fl, n])"""
+        shape, out, _ = self._wire_in(1, data)
+        return shape, out
+
+    def forms_to_wire(self, shape, forms):
+        return self._wire_out(1, shape, forms)
+
+    def wire_to_plaintexts(self, data, ml):
+        """bytes of serialize_plaintext_tensor -> (shape, magnitudes [ml, n], sign bytes [n]) on the device"""
+        return self._wire_in(2, data, ml, signs=True)
+
+    def plaintexts_to_wire(self, shape, mags, signs=None):
+        return self._wire_out(2, shape, mags, mags.shape[0], signs)
+
     # ---- CL_HSM2k scheme level (mirrors CPUCryptoSystem's batched entry points on SoA device tensors) --------------
     def set_scheme(self, k, N):
         nN = (int(N).bit_length() + 31) // 32
@@ -265,6 +306,27 @@ class ClassGroupB200:
         out = torch.empty_like(a)
         capi.check(self.lib.cofhe_b200_beaver_close(self.h, n, _ptr(pt1), _ptr(pt2), pt1.shape[0], _ptr(a), _ptr(b), _ptr(c), _ptr(rr),
                                                     rr.shape[0], _ptr(out), _stream()), "beaver_close")
+        return out
+
+    def beaver_triplets(self, a, b, r):
+        """encrypt_tensor([[a_i, b_i, a_i b_i]]) with the one randomness r: 3n ciphertexts, reference row-major order"""
+        ad, bd = (x if torch.is_tensor(x) else self.ints(x, self.ml) for x in (a, b))
+        n = ad.shape[-1]
+        rr = self.ints([r], self.el_r)
+        out = torch.empty((2, self.fl, 3 * n), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_beaver_triplets(self.h, n, _ptr(ad), _ptr(bd), ad.shape[0], _ptr(rr), rr.shape[0], _ptr(out), _stream()),
+                   "beaver_triplets")
+        return out
+
+    def ct_matmul_expand(self, ct1, ct2, n, m, p):
+        o1 = torch.empty((2, self.fl, n * m * p), dtype=torch.int32, device=self.device)
+        o2 = torch.empty_like(o1)
+        capi.check(self.lib.cofhe_b200_ct_matmul_expand(self.h, n, m, p, _ptr(ct1), _ptr(ct2), _ptr(o1), _ptr(o2), _stream()), "ct_matmul_expand")
+        return o1, o2
+
+    def ct_matmul_reduce(self, prod, init, n, m, p):
+        out = torch.empty((2, self.fl, n * p), dtype=torch.int32, device=self.device)
+        capi.check(self.lib.cofhe_b200_ct_matmul_reduce(self.h, n, m, p, _ptr(prod), _ptr(init), _ptr(out), _stream()), "ct_matmul_reduce")
         return out
 
     def _host_exp(self, e):

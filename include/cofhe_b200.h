@@ -135,6 +135,23 @@ int cofhe_b200_beaver_open(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, c
 int cofhe_b200_beaver_close(cofhe_b200_ctx *ctx, size_t n, const uint32_t *pt1, const uint32_t *pt2, uint32_t ml, const uint32_t *a,
                             const uint32_t *b, const uint32_t *c, const uint32_t *r, uint32_t el, uint32_t *out, void *stream);
 
+/* Beaver triplets: out = encrypt_tensor of the [n, 3] plaintext tensor (a_i, b_i, a_i * b_i), 3n ciphertexts in row-major
+ * order, ONE randomness r (device memory, el limbs) for the whole tensor: BeaversTripletGenerator::generate (reference
+ * include/smpc/beavers_triplet_generation.hpp:17-37), which fills the client's triplet cache (include/smpc/smpc_client.hpp
+ * :17,218).  a, b: plaintexts [ml][n] drawn by the caller's RandGen (cpu_cryptosystem.inl:36-47). */
+int cofhe_b200_beaver_triplets(cofhe_b200_ctx *ctx, size_t n, const uint32_t *a, const uint32_t *b, uint32_t ml, const uint32_t *r, uint32_t el,
+                               uint32_t *out, void *stream);
+/* Ciphertext x ciphertext MATRIX product around the Beaver multiplication (reference
+ * include/smpc/ciphertext_multiplications.hpp:51-110), ct1: n x m, ct2: m x p:
+ *   expand: out1[(i*m + j)*p + k] = ct1[i*m + j], out2[(i*m + j)*p + k] = ct2[j*p + k]   (:58-70; n*m*p elements each) --
+ *           the two operands of cofhe_b200_beaver_open / _close on n*m*p elements;
+ *   reduce: out[i*p + k] = init o prod_j prod[(i*m + j)*p + k]   (:79-100: zero = encrypt(pk, 0), then the direct nucomp
+ *           accumulation over j), as a balanced tree: log2(m) batched composition launches. */
+int cofhe_b200_ct_matmul_expand(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out1,
+                                uint32_t *out2, void *stream);
+int cofhe_b200_ct_matmul_reduce(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *prod, const uint32_t *init, uint32_t *out,
+                                void *stream);
+
 /* ---- Binary tensor wire format <-> SoA batches on the device.
  * The format is the one of CPUCryptoSystem::serialize_ciphertext_tensor / deserialize_ciphertext_tensor (reference
  * include/x86_64/cpu_cryptosystem.inl:322-391 and :393-520): u32 ndim | u32 dims[ndim] | u64 table[6n] | magnitudes;
@@ -150,6 +167,23 @@ int cofhe_b200_beaver_close(cofhe_b200_ctx *ctx, size_t n, const uint32_t *pt1, 
  * cofhe_b200_cts_to_wire: ciphertext batch -> wire bytes in device memory; blocking for the size (one 8-byte read-back),
  *                         *written = bytes produced, or needed when `cap` is too small (COFHE_B200_EINVAL). */
 int cofhe_b200_wire_header(const uint8_t *wire, size_t bytes, uint32_t *ndim, uint32_t *dims, uint32_t max_dims, size_t *n);
+/* The same layout carries the reference's other two tensor formats; `kind` selects the integers per element:
+ *   COFHE_B200_WIRE_CIPHERTEXTS (6: c1.a c1.b c1.c c2.a c2.b c2.c; batch [2][2na+nc][n])
+ *   COFHE_B200_WIRE_FORMS       (3: a b c; serialize / deserialize_part_decryption_result_tensor, reference
+ *                                include/x86_64/cpu_cryptosystem.inl:510-635; batch [2na+nc][n])
+ *   COFHE_B200_WIRE_PLAINTEXTS  (1; serialize / deserialize_plaintext_tensor, cpu_cryptosystem.inl:229-318; magnitudes [ml][n] plus
+ *                                one sign byte per element -- the reference ships unreduced, possibly negative plaintexts)
+ * These replace the mpz_import / mpz_export loops of include/node/compute_request_handler.hpp:414-431, 562-578 and
+ * include/node/partial_decryption_request_handler.hpp:143-158.  ml / sign buffers are used by the plaintext kind only
+ * (sign_out == NULL: negative values raise the element status; sign_in == NULL: all non-negative). */
+#define COFHE_B200_WIRE_CIPHERTEXTS 0
+#define COFHE_B200_WIRE_FORMS 1
+#define COFHE_B200_WIRE_PLAINTEXTS 2
+size_t cofhe_b200_wire_bound_kind(const cofhe_b200_ctx *ctx, int kind, uint32_t ndim, size_t n, uint32_t ml);
+int cofhe_b200_wire_to_batch(cofhe_b200_ctx *ctx, int kind, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
+                             uint32_t ml, uint8_t *sign_out, void *stream);
+int cofhe_b200_batch_to_wire(cofhe_b200_ctx *ctx, int kind, uint32_t ndim, const uint32_t *dims, size_t n, const uint32_t *in, uint32_t ml,
+                             const uint8_t *sign_in, uint8_t *wire, size_t cap, size_t *written, void *stream);
 size_t cofhe_b200_wire_bound(const cofhe_b200_ctx *ctx, uint32_t ndim, size_t n);
 int cofhe_b200_wire_to_cts(cofhe_b200_ctx *ctx, const uint8_t *wire, size_t bytes, uint32_t ndim, size_t n, uint32_t *out,
                            void *stream);
@@ -220,6 +254,12 @@ void cofhe_b200_host_free(void *ptr);
 void *cofhe_b200_stream(cofhe_b200_ctx *ctx);
 int cofhe_b200_upload(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream);
 int cofhe_b200_download(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream);
+int cofhe_b200_copy(cofhe_b200_ctx *ctx, void *dst, const void *src, size_t bytes, void *stream); /* device to device */
+/* out[.][e] = (sign[e] ? -mag[e] : mag[e]) mod 2^k, ml_out limb rows: the reduction CPUCryptoSystem applies to a plaintext
+ * before it encrypts it (to_plaintext -> CL_HSM_ClearText, reference thirdparty/bicycl/src/bicycl/CL_HSM_utils.inl:107-121),
+ * for plaintext batches in the sign-magnitude layout of the wire kernels.  sign may be NULL.  Needs set_scheme. */
+int cofhe_b200_plaintexts_mod2k(cofhe_b200_ctx *ctx, size_t n, const uint32_t *mag, uint32_t ml, const uint8_t *sign, uint32_t *out,
+                                uint32_t ml_out, void *stream);
 
 /* Measurement helper (no reference counterpart): sustained rate of independent 32x32->64-bit multiply-accumulates
  * (wide != 0: IMAD.WIDE.U32) or 32-bit multiply-adds (wide == 0: IMAD) over all SMs of `device`, in MACs/s.

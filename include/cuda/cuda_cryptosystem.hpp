@@ -63,54 +63,141 @@ namespace CoFHE
             throw std::runtime_error(msg);
         }
 
-        // limb i of element idx lives at dst[i*stride + idx]; signed values are two's complement over nl limbs
+        // limb i of element idx lives at dst[i*stride + idx]; signed values are two's complement over nl limbs.  The limbs
+        // are read straight from the mpz (no mpz_export / temporary buffer): this loop is the host side of every call
         inline void put_mpz(const BICYCL::Mpz &z, uint32_t *dst, size_t nl, size_t stride, bool twos)
         {
             if (z.nbits() > 32 * nl - (twos ? 1 : 0))
                 throw std::range_error("cofhe_b200: integer does not fit the limb shape");
-            uint32_t tmp[2 * 216 + 4];
-            size_t cnt = 0;
-            std::memset(tmp, 0, (nl + 1) * sizeof(uint32_t));
-            mpz_export(tmp, &cnt, -1, 4, 0, 0, (mpz_srcptr)z);
-            if (z.sgn() < 0)
+            mpz_srcptr zp = (mpz_srcptr)z;
+            const mp_limb_t *p = mpz_limbs_read(zp);
+            const size_t sz = mpz_size(zp);
+            const bool neg = z.sgn() < 0;
+            if (neg && !twos)
+                throw std::range_error("cofhe_b200: negative value where an unsigned one is required");
+            uint64_t c = 1;
+            for (size_t i = 0; i < nl; i++)
             {
-                if (!twos)
-                    throw std::range_error("cofhe_b200: negative value where an unsigned one is required");
-                uint64_t c = 1;
-                for (size_t i = 0; i < nl; i++)
+                uint32_t w = (i / 2 < sz) ? (uint32_t)(p[i / 2] >> (32 * (i & 1))) : 0u;
+                if (neg)
                 {
-                    uint64_t v = (uint64_t)(uint32_t)~tmp[i] + c;
-                    tmp[i] = (uint32_t)v;
+                    uint64_t v = (uint64_t)(uint32_t)~w + c;
+                    w = (uint32_t)v;
                     c = v >> 32;
                 }
+                dst[i * stride] = w;
             }
-            for (size_t i = 0; i < nl; i++)
-                dst[i * stride] = tmp[i];
         }
+        // the limbs are written straight into a fresh mpz (one allocation, no mpz_import)
         inline BICYCL::Mpz get_mpz(const uint32_t *src, size_t nl, size_t stride, bool twos)
         {
-            uint32_t tmp[2 * 216 + 4];
-            for (size_t i = 0; i < nl; i++)
-                tmp[i] = src[i * stride];
-            bool neg = twos && (tmp[nl - 1] >> 31);
-            if (neg)
-            {
-                uint64_t c = 1;
-                for (size_t i = 0; i < nl; i++)
-                {
-                    uint64_t v = (uint64_t)(uint32_t)~tmp[i] + c;
-                    tmp[i] = (uint32_t)v;
-                    c = v >> 32;
-                }
-            }
+            const bool neg = twos && (src[(nl - 1) * stride] >> 31);
+            const size_t n64 = (nl + 1) / 2;
             mpz_t t;
-            mpz_init(t);
-            mpz_import(t, nl, -1, 4, 0, 0, tmp);
-            if (neg)
-                mpz_neg(t, t);
+            mpz_init2(t, 64 * n64);
+            mp_limb_t *w = mpz_limbs_write(t, (mp_size_t)n64);
+            uint64_t c = 1;
+            size_t used = 0;
+            for (size_t j = 0; j < n64; j++)
+            {
+                uint64_t lim = 0;
+                for (size_t h = 0; h < 2; h++)
+                {
+                    size_t i = 2 * j + h;
+                    uint32_t x = i < nl ? src[i * stride] : (neg ? 0xffffffffu : 0u);
+                    if (neg)
+                    {
+                        uint64_t v = (uint64_t)(uint32_t)~x + c;
+                        x = (uint32_t)v;
+                        c = v >> 32;
+                    }
+                    lim |= (uint64_t)x << (32 * h);
+                }
+                w[j] = lim;
+                if (lim)
+                    used = j + 1;
+            }
+            mpz_limbs_finish(t, neg ? -(mp_size_t)used : (mp_size_t)used);
             return BICYCL::Mpz(std::move(t)); // takes ownership of the limbs (gmp_extras.inl:256-261)
         }
+        // a QFI from three freshly built coefficients without copying them (the public constructor takes const Mpz &): the
+        // coefficients are swapped into a default-constructed form through its accessors
+        inline BICYCL::QFI make_qfi(BICYCL::Mpz &&a, BICYCL::Mpz &&b, BICYCL::Mpz &&c)
+        {
+            BICYCL::QFI f;
+            BICYCL::Mpz::swap(const_cast<BICYCL::Mpz &>(f.a()), a);
+            BICYCL::Mpz::swap(const_cast<BICYCL::Mpz &>(f.b()), b);
+            BICYCL::Mpz::swap(const_cast<BICYCL::Mpz &>(f.c()), c);
+            return f;
+        }
     } // namespace b200_detail
+
+    // A tensor that lives on the device between calls (SURVEY.md 8b "device-resident handles"): the SoA limb batch of
+    // include/cofhe_b200.h plus its shape.  kind: 0 ciphertexts [2][2na+nc][n], 1 forms (part-decryption results)
+    // [2na+nc][n], 2 plaintexts (magnitudes [ml][n] + one sign byte per element).  Move-only; frees its buffers through
+    // the context it was made with, which must outlive it.  Produced and consumed by the B200CryptoSystem overloads
+    // below, so that chained calls (benchmarks/local.cpp:101-104, 179-182) and deserialize -> compute -> serialize
+    // (include/node/compute_request_handler.hpp:414-431, 562-578) never build BICYCL objects in between.
+    class DeviceBatch
+    {
+    public:
+        DeviceBatch() = default;
+        DeviceBatch(const DeviceBatch &) = delete;
+        DeviceBatch &operator=(const DeviceBatch &) = delete;
+        DeviceBatch(DeviceBatch &&o) noexcept { steal(o); }
+        DeviceBatch &operator=(DeviceBatch &&o) noexcept
+        {
+            if (this != &o)
+            {
+                release();
+                steal(o);
+            }
+            return *this;
+        }
+        ~DeviceBatch() { release(); }
+        int kind() const { return kind_; }
+        size_t num_elements() const { return n_; }
+        const Vector<size_t> &shape() const { return shape_; }
+        uint32_t limbs() const { return ml_; } // plaintext magnitudes
+        const uint32_t *data() const { return d_; }
+        uint32_t *data() { return d_; }
+        const uint8_t *signs() const { return sg_; }
+        uint8_t *signs() { return sg_; }
+        void reshape(const Vector<size_t> &sh)
+        {
+            size_t c = 1;
+            for (size_t d : sh)
+                c *= d;
+            if (c != n_)
+                throw std::invalid_argument("DeviceBatch::reshape: element count differs");
+            shape_ = sh;
+        }
+
+    private:
+        friend class B200CryptoSystem;
+        cofhe_b200_ctx *ctx_ = nullptr;
+        int kind_ = 0;
+        size_t n_ = 0;
+        uint32_t ml_ = 0;
+        uint32_t bits_ = 0;  // plaintexts: upper bound of the bit length when known (0: unknown)
+        bool neg_ = false;   // plaintexts: a negative value is present (when known)
+        Vector<size_t> shape_;
+        uint32_t *d_ = nullptr;
+        uint8_t *sg_ = nullptr;
+        void steal(DeviceBatch &o)
+        {
+            ctx_ = o.ctx_; kind_ = o.kind_; n_ = o.n_; ml_ = o.ml_; bits_ = o.bits_; neg_ = o.neg_; shape_ = std::move(o.shape_); d_ = o.d_; sg_ = o.sg_;
+            o.d_ = nullptr; o.sg_ = nullptr; o.n_ = 0;
+        }
+        void release()
+        {
+            if (ctx_ && d_)
+                cofhe_b200_dev_free(ctx_, d_);
+            if (ctx_ && sg_)
+                cofhe_b200_dev_free(ctx_, sg_);
+            d_ = nullptr; sg_ = nullptr;
+        }
+    };
 
     class B200CryptoSystem
     {
@@ -191,9 +278,9 @@ namespace CoFHE
         String serialize_plaintext(const PlainText &pt) const { return host_.serialize_plaintext(pt); }
         String serialize_ciphertext(const CipherText &ct) const { return host_.serialize_ciphertext(ct); }
         String serialize_part_decryption_result(const PartDecryptionResult &pdr) const { return host_.serialize_part_decryption_result(pdr); }
-        String serialize_plaintext_tensor(const Tensor<PlainText *> &t) const { return host_.serialize_plaintext_tensor(t); }
-        String serialize_ciphertext_tensor(const Tensor<CipherText *> &t) const { return host_.serialize_ciphertext_tensor(t); }
-        String serialize_part_decryption_result_tensor(const Tensor<PartDecryptionResult *> &t) const { return host_.serialize_part_decryption_result_tensor(t); }
+        String serialize_plaintext_tensor(const Tensor<PlainText *> &t) const { return serialize_tensor(upload_plaintexts(t, 0)); }
+        String serialize_ciphertext_tensor(const Tensor<CipherText *> &t) const { return serialize_tensor(upload_ciphertexts(t)); }
+        String serialize_part_decryption_result_tensor(const Tensor<PartDecryptionResult *> &t) const { return serialize_tensor(upload_part_decryption_results(t)); }
         static B200CryptoSystem deserialize(const String &data) { return B200CryptoSystem(b200_detail::HostCS::deserialize(data)); }
         SecretKey deserialize_secret_key(const String &d) const { return host_.deserialize_secret_key(d); }
         SecretKeyShare deserialize_secret_key_share(const String &d) const { return host_.deserialize_secret_key_share(d); }
@@ -201,9 +288,15 @@ namespace CoFHE
         PlainText deserialize_plaintext(const String &d) const { return host_.deserialize_plaintext(d); }
         CipherText deserialize_ciphertext(const String &d) const { return host_.deserialize_ciphertext(d); }
         PartDecryptionResult deserialize_part_decryption_result(const String &d) const { return host_.deserialize_part_decryption_result(d); }
-        Tensor<PlainText *> deserialize_plaintext_tensor(const String &d) const { return host_.deserialize_plaintext_tensor(d); }
-        Tensor<CipherText *> deserialize_ciphertext_tensor(const String &d) const { return host_.deserialize_ciphertext_tensor(d); }
-        Tensor<PartDecryptionResult *> deserialize_part_decryption_result_tensor(const String &d) const { return host_.deserialize_part_decryption_result_tensor(d); }
+        // (the reference returns this tensor flattened: cpu_cryptosystem.inl:292-317 never reshapes it back; kept)
+        Tensor<PlainText *> deserialize_plaintext_tensor(const String &d) const
+        {
+            DeviceBatch b = deserialize_tensor_device(d, 2, 0);
+            b.reshape({b.num_elements()});
+            return download_plaintexts(b);
+        }
+        Tensor<CipherText *> deserialize_ciphertext_tensor(const String &d) const { return download_ciphertexts(deserialize_tensor_device(d, 0, 0)); }
+        Tensor<PartDecryptionResult *> deserialize_part_decryption_result_tensor(const String &d) const { return download_part_decryption_results(deserialize_tensor_device(d, 1, 0)); }
 
         BICYCL::RandGen &get_rand_gen() { return host_.get_rand_gen(); }
         const BICYCL::CL_HSM2k &get_hsm2k() const { return host_.get_hsm2k(); }
@@ -226,6 +319,26 @@ namespace CoFHE
         Tensor<CipherText *> scal_ciphertext_tensors(const PublicKey &pk, const Tensor<PlainText *> &s, const Tensor<CipherText *> &ct) const;
         Tensor<CipherText *> negate_ciphertext_tensor(const PublicKey &pk, const Tensor<CipherText *> &ct) const;
 
+        // ---- device-resident tensors (extension of the reference surface; same results, no BICYCL objects in between) --
+        DeviceBatch upload_ciphertexts(const Tensor<CipherText *> &t) const;
+        DeviceBatch upload_part_decryption_results(const Tensor<PartDecryptionResult *> &t) const;
+        DeviceBatch upload_plaintexts(const Tensor<PlainText *> &t, uint32_t limbs /* 0: as wide as the widest value */) const;
+        Tensor<CipherText *> download_ciphertexts(const DeviceBatch &b) const;
+        Tensor<PartDecryptionResult *> download_part_decryption_results(const DeviceBatch &b) const;
+        Tensor<PlainText *> download_plaintexts(const DeviceBatch &b) const;
+        // the reference's binary tensor formats <-> device batches (kind: 0 ciphertexts, 1 part-decryption results, 2 plaintexts;
+        // limbs: plaintext width, 0 = derived from the buffer size)
+        DeviceBatch deserialize_tensor_device(const String &data, int kind, uint32_t limbs) const;
+        String serialize_tensor(const DeviceBatch &b) const;
+        // batched operations on device batches: the overloads mirror the Tensor<T*> entry points (same shapes, same draws)
+        DeviceBatch encrypt_tensor(const PublicKey &pk, const DeviceBatch &pt) const;
+        DeviceBatch decrypt_tensor(const SecretKey &sk, const DeviceBatch &ct) const;
+        DeviceBatch part_decrypt_tensor(const SecretKeyShare &sks, const DeviceBatch &ct) const;
+        DeviceBatch combine_part_decryption_results_tensor(const DeviceBatch &ct, const Vector<const DeviceBatch *> &pdrs) const;
+        DeviceBatch add_ciphertext_tensors(const PublicKey &pk, const DeviceBatch &ct1, const DeviceBatch &ct2) const;
+        DeviceBatch scal_ciphertext_tensors(const PublicKey &pk, const DeviceBatch &s, const DeviceBatch &ct) const;
+        DeviceBatch negate_ciphertext_tensor(const PublicKey &pk, const DeviceBatch &ct) const;
+
         // wrap an existing reference object (used by deserialize)
         explicit B200CryptoSystem(b200_detail::HostCS host, int device = 0) : host_(std::move(host)), device_(device)
         {
@@ -247,8 +360,39 @@ namespace CoFHE
         mutable uint32_t *h_arena_ = nullptr;
         mutable uint32_t *d_arena_ = nullptr;
         mutable size_t arena_words_ = 0;
+        mutable std::vector<uint8_t> zero_bytes_;
 
         size_t fl() const { return 2 * (size_t)na_ + nc_; }
+        DeviceBatch make_batch(int kind, const Vector<size_t> &shape, uint32_t ml) const
+        {
+            DeviceBatch b;
+            b.ctx_ = ctx_; b.kind_ = kind; b.shape_ = shape; b.ml_ = ml;
+            size_t n = 1;
+            for (size_t d : shape)
+                n *= d;
+            b.n_ = n;
+            size_t rows = kind == 0 ? 2 * fl() : (kind == 1 ? fl() : ml);
+            void *p = nullptr;
+            b200_detail::check(cofhe_b200_dev_alloc(ctx_, std::max<size_t>(1, rows * n) * 4, &p), "dev_alloc");
+            b.d_ = (uint32_t *)p;
+            if (kind == 2)
+            {
+                b200_detail::check(cofhe_b200_dev_alloc(ctx_, std::max<size_t>(4, (n + 3) / 4 * 4), &p), "dev_alloc");
+                b.sg_ = (uint8_t *)p;
+            }
+            return b;
+        }
+        const uint8_t *zeros(size_t n) const
+        {
+            if (zero_bytes_.size() < n)
+                zero_bytes_.assign(n, 0);
+            return zero_bytes_.data();
+        }
+        void want_kind(const DeviceBatch &b, int kind, const char *what) const
+        {
+            if (b.ctx_ != ctx_ || b.kind_ != kind)
+                throw std::invalid_argument(std::string("B200CryptoSystem: wrong kind of device batch for ") + what);
+        }
 
         void open()
         {
@@ -323,8 +467,8 @@ namespace CoFHE
         }
         BICYCL::QFI get_form(const uint32_t *buf, size_t idx, size_t n) const
         {
-            return BICYCL::QFI(b200_detail::get_mpz(buf + idx, na_, n, false), b200_detail::get_mpz(buf + (size_t)na_ * n + idx, na_, n, true),
-                               b200_detail::get_mpz(buf + (size_t)2 * na_ * n + idx, nc_, n, false), true);
+            return b200_detail::make_qfi(b200_detail::get_mpz(buf + idx, na_, n, false), b200_detail::get_mpz(buf + (size_t)na_ * n + idx, na_, n, true),
+                                         b200_detail::get_mpz(buf + (size_t)2 * na_ * n + idx, nc_, n, false));
         }
         template <class Cts> // anything indexable yielding CipherText*
         void put_cts(const Cts &cts, size_t n, uint32_t *buf) const
@@ -821,6 +965,375 @@ namespace CoFHE
         }
         res.reshape({n, p});
         return res;
+    }
+
+
+    // =================================================================================================================
+    // device-resident tensors
+    // =================================================================================================================
+    inline DeviceBatch B200CryptoSystem::upload_ciphertexts(const Tensor<CipherText *> &t) const
+    {
+        using namespace b200_detail;
+        auto flat = t;
+        flat.flatten();
+        std::lock_guard<std::mutex> lock(mu_);
+        size_t n = t.num_elements(), cw = 2 * fl() * n;
+        DeviceBatch b = make_batch(0, t.shape(), 0);
+        if (n == 0)
+            return b;
+        reserve(cw);
+        put_cts(flat, n, h_arena_);
+        check(cofhe_b200_upload(ctx_, b.d_, h_arena_, cw * 4, cofhe_b200_stream(ctx_)), "upload");
+        check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "upload");
+        return b;
+    }
+    inline DeviceBatch B200CryptoSystem::upload_part_decryption_results(const Tensor<PartDecryptionResult *> &t) const
+    {
+        using namespace b200_detail;
+        auto flat = t;
+        flat.flatten();
+        std::lock_guard<std::mutex> lock(mu_);
+        size_t n = t.num_elements(), w = fl() * n;
+        DeviceBatch b = make_batch(1, t.shape(), 0);
+        if (n == 0)
+            return b;
+        reserve(w);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) put_form(*flat[i], h_arena_, i, n);
+        check(cofhe_b200_upload(ctx_, b.d_, h_arena_, w * 4, cofhe_b200_stream(ctx_)), "upload");
+        check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "upload");
+        return b;
+    }
+    inline DeviceBatch B200CryptoSystem::upload_plaintexts(const Tensor<PlainText *> &t, uint32_t limbs) const
+    {
+        using namespace b200_detail;
+        auto flat = t;
+        flat.flatten();
+        size_t n = t.num_elements();
+        uint32_t ml = limbs;
+        if (ml == 0)
+        {
+            ml = 1;
+            for (size_t i = 0; i < n; i++)
+                ml = std::max(ml, limbs_of(*flat[i]));
+        }
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch b = make_batch(2, t.shape(), ml);
+        if (n == 0)
+            return b;
+        size_t mw = (size_t)ml * n, sw = (n + 3) / 4;
+        reserve(mw + sw);
+        uint8_t *hs = (uint8_t *)(h_arena_ + mw);
+        size_t bits = 1;
+        bool neg = false;
+        for (size_t i = 0; i < n; i++)
+        {
+            BICYCL::Mpz mag(*flat[i]);
+            hs[i] = mag.sgn() < 0;
+            neg = neg || hs[i];
+            BICYCL::Mpz::abs(mag, mag);
+            bits = std::max(bits, (size_t)mag.nbits());
+            put_mpz(mag, h_arena_ + i, ml, n, false);
+        }
+        b.bits_ = (uint32_t)bits;
+        b.neg_ = neg;
+        check(cofhe_b200_upload(ctx_, b.d_, h_arena_, mw * 4, cofhe_b200_stream(ctx_)), "upload");
+        check(cofhe_b200_upload(ctx_, b.sg_, hs, n, cofhe_b200_stream(ctx_)), "upload");
+        check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "upload");
+        return b;
+    }
+    inline Tensor<B200CryptoSystem::CipherText *> B200CryptoSystem::download_ciphertexts(const DeviceBatch &b) const
+    {
+        using namespace b200_detail;
+        want_kind(b, 0, "download_ciphertexts");
+        size_t n = b.n_;
+        Tensor<CipherText *> res({n}, nullptr);
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (n)
+            {
+                reserve(2 * fl() * n);
+                check(cofhe_b200_download(ctx_, h_arena_, b.d_, 2 * fl() * n * 4, cofhe_b200_stream(ctx_)), "download");
+                check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "device arithmetic");
+                CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) res[i] = get_ct(h_arena_, i, n);
+            }
+        }
+        res.reshape(b.shape_);
+        return res;
+    }
+    inline Tensor<B200CryptoSystem::PartDecryptionResult *> B200CryptoSystem::download_part_decryption_results(const DeviceBatch &b) const
+    {
+        using namespace b200_detail;
+        want_kind(b, 1, "download_part_decryption_results");
+        size_t n = b.n_;
+        Tensor<PartDecryptionResult *> res({n}, nullptr);
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (n)
+            {
+                reserve(fl() * n);
+                check(cofhe_b200_download(ctx_, h_arena_, b.d_, fl() * n * 4, cofhe_b200_stream(ctx_)), "download");
+                check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "device arithmetic");
+                CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) res[i] = new PartDecryptionResult(get_form(h_arena_, i, n));
+            }
+        }
+        res.reshape(b.shape_);
+        return res;
+    }
+    inline Tensor<B200CryptoSystem::PlainText *> B200CryptoSystem::download_plaintexts(const DeviceBatch &b) const
+    {
+        using namespace b200_detail;
+        want_kind(b, 2, "download_plaintexts");
+        size_t n = b.n_;
+        Tensor<PlainText *> res({n}, nullptr);
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (n)
+            {
+                size_t mw = (size_t)b.ml_ * n, sw = (n + 3) / 4;
+                reserve(mw + sw);
+                uint8_t *hs = (uint8_t *)(h_arena_ + mw);
+                check(cofhe_b200_download(ctx_, h_arena_, b.d_, mw * 4, cofhe_b200_stream(ctx_)), "download");
+                check(cofhe_b200_download(ctx_, hs, b.sg_, n, cofhe_b200_stream(ctx_)), "download");
+                check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "device arithmetic");
+                CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++)
+                {
+                    res[i] = new PlainText(get_mpz(h_arena_ + i, b.ml_, n, false));
+                    if (hs[i])
+                        res[i]->neg();
+                }
+            }
+        }
+        res.reshape(b.shape_);
+        return res;
+    }
+    // wire bytes -> device batch through the wire kernels (csrc/wire.cuh): no mpz_t is built
+    inline DeviceBatch B200CryptoSystem::deserialize_tensor_device(const String &data, int kind, uint32_t limbs) const
+    {
+        using namespace b200_detail;
+        uint32_t ndim = 0, dims[8];
+        size_t n = 0;
+        check(cofhe_b200_wire_header((const uint8_t *)data.data(), data.size(), &ndim, dims, 8, &n), "wire_header");
+        Vector<size_t> shape(dims, dims + ndim);
+        const size_t S = kind == 0 ? 6 : (kind == 1 ? 3 : 1), head = 4 + 4 * (size_t)ndim;
+        if (data.size() < head + 8 * S * n)
+            throw std::invalid_argument("cofhe_b200: tensor buffer shorter than its offset table");
+        uint32_t ml = limbs, bits = 0;
+        if (kind == 2 && ml == 0)
+        {
+            // widest integer = largest distance between consecutive offsets (8n bytes of table, read on the host)
+            const uint64_t mask = ~((uint64_t)1 << 63);
+            uint64_t prev = 0, mx = 1, body = data.size() - head - 8 * n;
+            for (size_t i = 0; i <= n; i++)
+            {
+                uint64_t cur = body;
+                if (i < n)
+                {
+                    std::memcpy(&cur, data.data() + head + 8 * i, 8);
+                    cur &= mask;
+                }
+                if (i && cur >= prev)
+                    mx = std::max(mx, cur - prev);
+                prev = cur;
+            }
+            ml = (uint32_t)((mx + 3) / 4);
+            bits = (uint32_t)std::min<uint64_t>(8 * mx, 32 * (uint64_t)ml);
+        }
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch b = make_batch(kind, shape, ml);
+        b.bits_ = bits;
+        if (n == 0)
+            return b;
+        size_t words = (data.size() + 3) / 4;
+        reserve(words);
+        std::memcpy(h_arena_, data.data(), data.size());
+        void *dw = nullptr, *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_dev_alloc(ctx_, words * 4, &dw), "dev_alloc");
+        int rc = cofhe_b200_upload(ctx_, dw, h_arena_, data.size(), st);
+        if (rc == COFHE_B200_OK)
+            rc = cofhe_b200_wire_to_batch(ctx_, kind, (const uint8_t *)dw, data.size(), ndim, n, b.d_, ml, b.sg_, st);
+        int rs = cofhe_b200_status(ctx_, st);
+        cofhe_b200_dev_free(ctx_, dw);
+        check(rc, "wire_to_batch");
+        check(rs, "malformed tensor buffer");
+        return b;
+    }
+    inline String B200CryptoSystem::serialize_tensor(const DeviceBatch &b) const
+    {
+        using namespace b200_detail;
+        if (b.ctx_ != ctx_)
+            throw std::invalid_argument("B200CryptoSystem: device batch of another context");
+        std::lock_guard<std::mutex> lock(mu_);
+        uint32_t dims[8];
+        if (b.shape_.size() > 8)
+            throw std::invalid_argument("cofhe_b200: more than 8 dimensions");
+        for (size_t i = 0; i < b.shape_.size(); i++)
+            dims[i] = (uint32_t)b.shape_[i];
+        size_t cap = cofhe_b200_wire_bound_kind(ctx_, b.kind_, (uint32_t)b.shape_.size(), b.n_, b.ml_), written = 0;
+        void *dw = nullptr, *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_dev_alloc(ctx_, cap, &dw), "dev_alloc");
+        int rc = cofhe_b200_batch_to_wire(ctx_, b.kind_, (uint32_t)b.shape_.size(), dims, b.n_, b.d_, b.ml_, b.sg_, (uint8_t *)dw, cap, &written, st);
+        String out;
+        if (rc == COFHE_B200_OK)
+        {
+            out.resize(written);
+            rc = cofhe_b200_download(ctx_, out.data(), dw, written, st);
+        }
+        int rs = cofhe_b200_status(ctx_, st);
+        cofhe_b200_dev_free(ctx_, dw);
+        check(rc, "batch_to_wire");
+        check(rs, "device arithmetic");
+        return out;
+    }
+    // ---- batched operations, device batches in and out: asynchronous on the context's stream; element errors surface at
+    // the next download / serialize (cofhe_b200_status)
+    inline DeviceBatch B200CryptoSystem::add_ciphertext_tensors(const PublicKey &, const DeviceBatch &a, const DeviceBatch &b) const
+    {
+        using namespace b200_detail;
+        want_kind(a, 0, "add_ciphertext_tensors");
+        want_kind(b, 0, "add_ciphertext_tensors");
+        if (a.shape_ != b.shape_)
+            throw std::invalid_argument("Tensor shapes must be equal");
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch r = make_batch(0, a.shape_, 0);
+        check(cofhe_b200_add_ciphertexts(ctx_, a.n_, a.d_, b.d_, r.d_, cofhe_b200_stream(ctx_)), "add_ciphertexts");
+        return r;
+    }
+    inline DeviceBatch B200CryptoSystem::negate_ciphertext_tensor(const PublicKey &, const DeviceBatch &a) const
+    {
+        using namespace b200_detail;
+        want_kind(a, 0, "negate_ciphertext_tensor");
+        PlainText s = this->make_plaintext(-1); // 2^k - 1
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch r = make_batch(0, a.shape_, 0);
+        uint32_t el = limbs_of(s);
+        reserve(el);
+        put_mpz(s, h_arena_, el, 1, false);
+        up(h_arena_, el);
+        check(cofhe_b200_scal_ciphertexts(ctx_, a.n_, a.d_, dev(h_arena_), el, 0, nullptr, 0, r.d_, cofhe_b200_stream(ctx_)), "scal_ciphertexts");
+        check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "device arithmetic"); // the exponent sits in the shared arena
+        return r;
+    }
+    // 1-D: (c1^s_i, c2^s_i) elementwise; 2-D: res[i,k] = zero o prod_j ct[i,j]^{s[j,k]}, zero = encrypt(pk, 0) (1 draw)
+    inline DeviceBatch B200CryptoSystem::scal_ciphertext_tensors(const PublicKey &pk, const DeviceBatch &s, const DeviceBatch &ct) const
+    {
+        using namespace b200_detail;
+        want_kind(s, 2, "scal_ciphertext_tensors");
+        want_kind(ct, 0, "scal_ciphertext_tensors");
+        if (s.shape_.size() > 2 || ct.shape_.size() > 2)
+            throw std::invalid_argument("Tensors must be 0D, 1D or 2D for now");
+        if (s.shape_.size() == 1 && ct.shape_.size() == 1)
+        {
+            if (s.n_ != ct.n_)
+                throw std::invalid_argument("Vector sizes must be equal");
+            std::lock_guard<std::mutex> lock(mu_);
+            DeviceBatch r = make_batch(0, ct.shape_, 0);
+            check(cofhe_b200_scal_ciphertexts(ctx_, ct.n_, ct.d_, s.d_, s.ml_, 1, s.sg_, 0, r.d_, cofhe_b200_stream(ctx_)), "scal_ciphertexts");
+            return r;
+        }
+        if (s.shape_.size() != 2 || ct.shape_.size() != 2 || s.shape_[0] != ct.shape_[1])
+            throw std::invalid_argument("Tensor shapes must be compatible for matrix multiplication");
+        if (s.neg_)
+            throw std::invalid_argument("matmul scalars must be non-negative");
+        size_t n = ct.shape_[0], m = ct.shape_[1], p = s.shape_[1];
+        CipherText zero = this->encrypt(pk, this->make_plaintext(0)); // the call's single draw, as the reference
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch r = make_batch(0, {n, p}, 0);
+        reserve(2 * fl());
+        put_form(zero.c1(), h_arena_, 0, 1);
+        put_form(zero.c2(), h_arena_ + fl(), 0, 1);
+        up(h_arena_, 2 * fl());
+        uint32_t ebits = s.bits_ ? s.bits_ : 32 * s.ml_;
+        check(cofhe_b200_scal_matmul(ctx_, n, m, p, ct.d_, s.d_, s.ml_, ebits, dev(h_arena_), r.d_, cofhe_b200_stream(ctx_)), "scal_matmul");
+        check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "device arithmetic"); // `zero` sits in the shared arena
+        return r;
+    }
+    inline DeviceBatch B200CryptoSystem::encrypt_tensor(const PublicKey &pk, const DeviceBatch &pt) const
+    {
+        using namespace b200_detail;
+        want_kind(pt, 2, "encrypt_tensor");
+        std::lock_guard<std::mutex> lock(mu_);
+        const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
+        BICYCL::Mpz rr = host_.get_rand_gen().random_mpz(H.encrypt_randomness_bound()); // the call's single draw
+        DeviceBatch r = make_batch(0, pt.shape_, 0);
+        if (pt.n_ == 0)
+            return r;
+        ensure_pk(pk);
+        DeviceBatch m = make_batch(2, pt.shape_, ml_);
+        void *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_plaintexts_mod2k(ctx_, pt.n_, pt.d_, pt.ml_, pt.sg_, m.d_, ml_, st), "plaintexts_mod2k");
+        reserve(el_r_);
+        put_mpz(rr, h_arena_, el_r_, 1, false);
+        up(h_arena_, el_r_);
+        check(cofhe_b200_encrypt(ctx_, pt.n_, m.d_, ml_, dev(h_arena_), el_r_, 1, r.d_, st), "encrypt");
+        check(cofhe_b200_status(ctx_, st), "device arithmetic");
+        return r;
+    }
+    inline DeviceBatch B200CryptoSystem::decrypt_tensor(const SecretKey &sk, const DeviceBatch &ct) const
+    {
+        using namespace b200_detail;
+        want_kind(ct, 0, "decrypt_tensor");
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch r = make_batch(2, ct.shape_, ml_);
+        r.bits_ = (uint32_t)host_.get_hsm2k().k();
+        if (ct.n_ == 0)
+            return r;
+        uint32_t el = limbs_of(sk);
+        std::vector<uint32_t> e(el);
+        put_mpz(sk, e.data(), el, 1, false);
+        void *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_decrypt(ctx_, ct.n_, ct.d_, e.data(), el, r.d_, ml_, st), "decrypt");
+        check(cofhe_b200_upload(ctx_, r.sg_, zeros(ct.n_), ct.n_, st), "signs");
+        check(cofhe_b200_status(ctx_, st), "device arithmetic");
+        return r;
+    }
+    inline DeviceBatch B200CryptoSystem::part_decrypt_tensor(const SecretKeyShare &sks, const DeviceBatch &ct) const
+    {
+        using namespace b200_detail;
+        want_kind(ct, 0, "part_decrypt_tensor");
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch r = make_batch(1, ct.shape_, 0);
+        if (ct.n_ == 0)
+            return r;
+        BICYCL::Mpz mag(sks);
+        BICYCL::Mpz::abs(mag, mag);
+        uint32_t el = limbs_of(mag);
+        std::vector<uint32_t> e(el);
+        put_mpz(mag, e.data(), el, 1, false);
+        check(cofhe_b200_part_decrypt(ctx_, ct.n_, ct.d_, e.data(), el, sks.sgn() < 0, r.d_, cofhe_b200_stream(ctx_)), "part_decrypt");
+        return r;
+    }
+    inline DeviceBatch B200CryptoSystem::combine_part_decryption_results_tensor(const DeviceBatch &ct, const Vector<const DeviceBatch *> &pdrs) const
+    {
+        using namespace b200_detail;
+        want_kind(ct, 0, "combine_part_decryption_results_tensor");
+        if (pdrs.empty())
+            throw std::invalid_argument("No partial decryption results");
+        for (const DeviceBatch *d : pdrs)
+        {
+            want_kind(*d, 1, "combine_part_decryption_results_tensor");
+            if (d->n_ != ct.n_)
+                throw std::invalid_argument("Tensor shapes must be equal");
+        }
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch r = make_batch(2, pdrs[0]->shape_, ml_);
+        r.bits_ = (uint32_t)host_.get_hsm2k().k();
+        size_t n = ct.n_, t = pdrs.size();
+        if (n == 0)
+            return r;
+        void *ds = nullptr, *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_dev_alloc(ctx_, t * fl() * n * 4, &ds), "dev_alloc");
+        int rc = COFHE_B200_OK;
+        for (size_t j = 0; j < t && rc == COFHE_B200_OK; j++)
+            rc = cofhe_b200_copy(ctx_, (uint32_t *)ds + j * fl() * n, pdrs[j]->d_, fl() * n * 4, st);
+        if (rc == COFHE_B200_OK)
+            rc = cofhe_b200_combine(ctx_, n, (uint32_t)t, ct.d_, (const uint32_t *)ds, r.d_, ml_, st);
+        if (rc == COFHE_B200_OK)
+            rc = cofhe_b200_upload(ctx_, r.sg_, zeros(n), n, st);
+        int rs = cofhe_b200_status(ctx_, st);
+        cofhe_b200_dev_free(ctx_, ds);
+        check(rc, "combine");
+        check(rs, "device arithmetic");
+        return r;
     }
 
     // ---- factory: a B200 backend on CUDA device `device` (the reference's make_cryptosystem ignores its Device

@@ -375,3 +375,40 @@ def deserialize_ciphertext_tensor(data):
         ints.append(-v if t >> 63 else v)
     cts = [(tuple(ints[6 * i:6 * i + 3]), tuple(ints[6 * i + 3:6 * i + 6])) for i in range(n)]
     return shape, cts
+
+
+def serialize_int_tensor(shape, ints):
+    """The shared layout of the reference's binary tensor formats for a flat list of integers: serialize_plaintext_tensor
+    (include/x86_64/cpu_cryptosystem.inl:229-271; one integer per element) and, with (a, b, c) per element,
+    serialize_part_decryption_result_tensor (:510-560)."""
+    import struct
+    head = struct.pack("<I", len(shape)) + b"".join(struct.pack("<I", d) for d in shape)
+    table, blobs, off = [], [], 0
+    for x in ints:
+        table.append(off | ((1 << 63) if x <= 0 else 0))
+        sz = _wire_size(x)
+        blobs.append(abs(x).to_bytes(sz, "little"))
+        off += sz
+    return head + b"".join(struct.pack("<Q", t) for t in table) + b"".join(blobs)
+
+
+def deserialize_int_tensor(data, per_element):
+    """deserialize_plaintext_tensor (cpu_cryptosystem.inl:273-318, per_element = 1) / deserialize_part_decryption_result_tensor
+    (:562-635, per_element = 3).  -> (shape, flat integers)"""
+    import struct
+    ndim = struct.unpack_from("<I", data, 0)[0]
+    shape = list(struct.unpack_from("<%dI" % ndim, data, 4))
+    n = 1
+    for d in shape:
+        n *= d
+    base = 4 + 4 * ndim
+    table = struct.unpack_from("<%dQ" % (per_element * n), data, base)
+    body = base + 8 * per_element * n
+    mask = (1 << 63) - 1
+    ints = []
+    for i, t in enumerate(table):
+        lo = t & mask
+        hi = (table[i + 1] & mask) if i + 1 < len(table) else len(data) - body
+        v = int.from_bytes(data[body + lo:body + hi], "little")
+        ints.append(-v if t >> 63 else v)
+    return shape, ints

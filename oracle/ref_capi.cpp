@@ -179,6 +179,40 @@ std::string call(Ref &R, const std::string &op, const std::vector<Mpz> &a) {
     for (size_t i = 0; i < t.ndim(); i++) o << t.shape()[i] << ' ';
     t.flatten();
     for (size_t i = 0; i < t.num_elements(); i++) { put(o, *t.at(i)); delete t.at(i); }
+  } else if (op == "serialize_pdr_tensor") {  // rows cols forms... -> bytes of serialize_part_decryption_result_tensor
+    size_t r = to_sz(a[0]), c = to_sz(a[1]), n = r * c;
+    auto t = make_tensor<CS::PartDecryptionResult>(r, c); t.flatten();
+    for (size_t i = 0; i < n; i++) t.at(i) = new CS::PartDecryptionResult(a[2 + 3 * i], a[3 + 3 * i], a[4 + 3 * i], true);
+    t.reshape({r, c});
+    std::string bytes = R.cs.serialize_part_decryption_result_tensor(t);
+    t.flatten();
+    for (size_t i = 0; i < n; i++) delete t.at(i);
+    for (unsigned char ch : bytes) o << (unsigned)ch << ' ';
+  } else if (op == "deserialize_pdr_tensor") {  // bytes... -> ndim dims... forms...
+    std::string bytes(a.size(), 0);
+    for (size_t i = 0; i < a.size(); i++) bytes[i] = (char)to_sz(a[i]);
+    auto t = R.cs.deserialize_part_decryption_result_tensor(bytes);
+    o << t.ndim() << ' ';
+    for (size_t i = 0; i < t.ndim(); i++) o << t.shape()[i] << ' ';
+    t.flatten();
+    for (size_t i = 0; i < t.num_elements(); i++) { put(o, *t.at(i)); delete t.at(i); }
+  } else if (op == "serialize_pt_tensor") {  // rows cols ints... -> bytes of serialize_plaintext_tensor
+    size_t r = to_sz(a[0]), c = to_sz(a[1]), n = r * c;
+    auto t = make_tensor<CS::PlainText>(r, c); t.flatten();
+    for (size_t i = 0; i < n; i++) t.at(i) = new CS::PlainText(a[2 + i]);
+    t.reshape({r, c});
+    std::string bytes = R.cs.serialize_plaintext_tensor(t);
+    t.flatten();
+    for (size_t i = 0; i < n; i++) delete t.at(i);
+    for (unsigned char ch : bytes) o << (unsigned)ch << ' ';
+  } else if (op == "deserialize_pt_tensor") {  // bytes... -> ndim dims... ints...
+    std::string bytes(a.size(), 0);
+    for (size_t i = 0; i < a.size(); i++) bytes[i] = (char)to_sz(a[i]);
+    auto t = R.cs.deserialize_plaintext_tensor(bytes);
+    o << t.ndim() << ' ';
+    for (size_t i = 0; i < t.ndim(); i++) o << t.shape()[i] << ' ';
+    t.flatten();
+    for (size_t i = 0; i < t.num_elements(); i++) { put(o, *t.at(i)); delete t.at(i); }
   } else {
     throw std::invalid_argument("unknown op " + op);
   }

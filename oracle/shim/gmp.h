@@ -75,6 +75,8 @@ void __gmpz_import (mpz_ptr, size_t, int, size_t, int, size_t, const void *);
 void *__gmpz_export (void *, size_t *, int, size_t, int, size_t, mpz_srcptr);
 #define mpz_sizeinbase __gmpz_sizeinbase
 size_t __gmpz_sizeinbase (mpz_srcptr, int);
+#define mpz_init2 __gmpz_init2
+void __gmpz_init2 (mpz_ptr, mp_bitcnt_t);
 #define mpz_size __gmpz_size
 size_t __gmpz_size (mpz_srcptr);
 #define mpz_getlimbn __gmpz_getlimbn

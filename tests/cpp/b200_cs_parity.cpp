@@ -70,7 +70,7 @@ int bench(int argc, char** argv) {
   auto sk = cs.keygen(); auto pk = cs.keygen(sk);
   auto sk2 = ref.keygen(); auto pk2 = ref.keygen(sk2);
   size_t bad = 0;
-  double tb = 0, tc = 0;
+  double tb = 0, tc = 0, tdev = 0;
   size_t units = 0;
   Tensor<CT*> gk(1, nullptr), ck(1, nullptr);
   if (!mm) {
@@ -82,6 +82,20 @@ int bench(int argc, char** argv) {
     tb = chain([&](const Tensor<CT*>& x) { return cs.add_ciphertext_tensors(pk, x, ct2); }, ct1, iters, cpu_iters, &gk);
     if (cpu_iters) tc = chain([&](const Tensor<CT*>& x) { return ref.add_ciphertext_tensors(pk2, x, rt2); }, rt1, cpu_iters, cpu_iters, &ck);
     units = a1 * a2;
+    // the same chain with the tensors resident on the device: one upload of the operands, `iters` adds, one download
+    {
+      double t0 = now();
+      DeviceBatch d1 = cs.upload_ciphertexts(ct1), d2 = cs.upload_ciphertexts(ct2);
+      DeviceBatch acc = cs.add_ciphertext_tensors(pk, d1, d2);
+      for (size_t i = 1; i < iters; i++) acc = cs.add_ciphertext_tensors(pk, acc, d2);
+      auto fin = cs.download_ciphertexts(acc);
+      tdev = now() - t0;
+      // compare with the class-API chain at the last step
+      Tensor<CT*> last(1, nullptr);
+      chain([&](const Tensor<CT*>& x) { return cs.add_ciphertext_tensors(pk, x, ct2); }, ct1, iters, iters, &last);
+      bad += diff(fin, last);
+      free_cts(fin); free_cts(last);
+    }
   } else {
     auto pt1 = pattern(a1, a2), pt2 = pattern(a2, a3);
     auto ct1 = cs.encrypt_tensor(pk, pt1);
@@ -95,6 +109,7 @@ int bench(int argc, char** argv) {
   std::cout << "{\"op\": \"" << op << "\", \"shape\": [" << a1 << ", " << a2 << ", " << a3 << "], \"iters\": " << iters
             << ", \"b200_s\": " << tb << ", \"b200_units_per_s\": " << units * iters / tb << ", \"cpu_iters\": " << cpu_iters
             << ", \"cpu_s\": " << tc << ", \"cpu_units_per_s\": " << (cpu_iters ? units * cpu_iters / tc : 0.0)
+            << ", \"b200_resident_s\": " << tdev << ", \"b200_resident_units_per_s\": " << (tdev > 0 ? units * iters / tdev : 0.0)
             << ", \"cpu_threads\": " << omp_get_max_threads() << ", \"mismatches\": " << bad << ", \"launches\": " << cs.gpu_launches() << "}" << std::endl;
   return bad != 0;
 }
@@ -169,6 +184,68 @@ int main(int argc, char** argv) {
     auto zs = cs.add_ciphertext_tensors(pk, z1, z2); auto ys = ref.add_ciphertext_tensors(pk2, y1, y2);
     bad += !same(*zs.get_value(), *ys.get_value());
   } catch (const std::exception& e) { std::cout << "single-ciphertext block threw: " << e.what() << " after " << bad << " mismatches" << std::endl; bad += 1000; }
+  // the reference's binary tensor formats through the device wire kernels: byte-identical to the reference's own
+  // serialisers, and back; then the same tensors kept on the device across chained calls
+  try {
+    ct.reshape({n, m}); ct2.reshape({n, m});
+    std::string wb = cs.serialize_ciphertext_tensor(ct), wr = ref.serialize_ciphertext_tensor(ct2);
+    { size_t _b = (size_t)(wb != wr); if (_b) std::cerr << "wire-block check 1 failed (" << _b << "): wb != wr" << std::endl; bad += _b; }
+    auto back = cs.deserialize_ciphertext_tensor(wr); back.flatten(); ct.flatten();
+    for (size_t i = 0; i < n*m; i++) bad += !(back.at(i)->c1() == ct.at(i)->c1() && back.at(i)->c2() == ct.at(i)->c2());
+    ct.reshape({n, m});
+    mm.reshape({n, p});
+    std::string pb = cs.serialize_part_decryption_result_tensor(pd[0]), pr = ref.serialize_part_decryption_result_tensor(pd[0]);
+    { size_t _b = (size_t)(pb != pr); if (_b) std::cerr << "wire-block check 2 failed (" << _b << "): pb != pr" << std::endl; bad += _b; }
+    auto pback = cs.deserialize_part_decryption_result_tensor(pr); pback.flatten();
+    auto pd0 = pd[0]; pd0.flatten();
+    for (size_t i = 0; i < n*p; i++) bad += !(*pback.at(i) == *pd0.at(i));
+    Tensor<B200CryptoSystem::PlainText*> mixed(2, 3, nullptr); mixed.flatten();
+    long vals[6] = {0, -7, 123456789, -1, 65536, 255};
+    for (int i = 0; i < 6; i++) mixed.at(i) = new B200CryptoSystem::PlainText(vals[i]);
+    mixed.reshape({2, 3});
+    std::string tb = cs.serialize_plaintext_tensor(mixed), tr = ref.serialize_plaintext_tensor(mixed);
+    { size_t _b = (size_t)(tb != tr); if (_b) std::cerr << "wire-block check 3 failed (" << _b << "): tb != tr" << std::endl; bad += _b; }
+    auto tback = cs.deserialize_plaintext_tensor(tr); auto tref = ref.deserialize_plaintext_tensor(tr);
+    { size_t _b = (size_t)(tback.shape() != tref.shape()); if (_b) std::cerr << "wire-block check 4 failed (" << _b << "): tback.shape() != tref.shape()" << std::endl; bad += _b; }
+    tback.flatten(); tref.flatten();
+    for (size_t i = 0; i < 6; i++) bad += !(*tback.at(i) == *tref.at(i));
+    // device-resident chain: wire -> device -> 5 chained adds + matmul + threshold decryption -> wire, no BICYCL object in between
+    DeviceBatch dct = cs.deserialize_tensor_device(wr, 0, 0);
+    DeviceBatch acc = cs.add_ciphertext_tensors(pk, dct, dct);
+    auto hacc = ref.add_ciphertext_tensors(pk2, ct2, ct2);
+    for (int it = 0; it < 4; it++) {
+      acc = cs.add_ciphertext_tensors(pk, acc, dct);
+      auto nx = ref.add_ciphertext_tensors(pk2, hacc, ct2); free_cts(hacc); hacc = nx;
+    }
+    { size_t _b = (size_t)(cs.serialize_tensor(acc) != ref.serialize_ciphertext_tensor(hacc)); if (_b) std::cerr << "wire-block check 5 failed (" << _b << "): cs.serialize_tensor(acc) != ref.serialize_ciphertext_tensor(" << std::endl; bad += _b; }
+    DeviceBatch ds = cs.upload_plaintexts(s, 0);
+    DeviceBatch dmm = cs.scal_ciphertext_tensors(pk, ds, acc);
+    auto hmm = ref.scal_ciphertext_tensors(pk2, s, hacc);
+    { size_t _b = (size_t)(cs.serialize_tensor(dmm) != ref.serialize_ciphertext_tensor(hmm)); if (_b) std::cerr << "wire-block check 6 failed (" << _b << "): cs.serialize_tensor(dmm) != ref.serialize_ciphertext_tensor(" << std::endl; bad += _b; }
+    DeviceBatch dneg = cs.negate_ciphertext_tensor(pk, dmm);
+    auto hneg = ref.negate_ciphertext_tensor(pk2, hmm);
+    { size_t _b = (size_t)(cs.serialize_tensor(dneg) != ref.serialize_ciphertext_tensor(hneg)); if (_b) std::cerr << "wire-block check 7 failed (" << _b << "): cs.serialize_tensor(dneg) != ref.serialize_ciphertext_tensor" << std::endl; bad += _b; }
+    DeviceBatch dp0 = cs.part_decrypt_tensor(shares[0][0], dneg), dp1 = cs.part_decrypt_tensor(shares[1][0], dneg), dp2 = cs.part_decrypt_tensor(shares[2][0], dneg);
+    { size_t _b = (size_t)(cs.serialize_tensor(dp0) != ref.serialize_part_decryption_result_tensor(ref.part_decrypt_tensor(shares[0][0], hneg))); if (_b) std::cerr << "wire-block check 8 failed (" << _b << "): cs.serialize_tensor(dp0) != ref.serialize_part_decryption_re" << std::endl; bad += _b; }
+    Vector<const DeviceBatch*> dps; dps.push_back(&dp0); dps.push_back(&dp1); dps.push_back(&dp2);
+    DeviceBatch dplain = cs.combine_part_decryption_results_tensor(dneg, dps);
+    auto hplain = ref.decrypt_tensor(sk2, hneg);
+    { size_t _b = (size_t)(cs.serialize_tensor(dplain) != ref.serialize_plaintext_tensor(hplain)); if (_b) std::cerr << "wire-block check 9 failed (" << _b << "): cs.serialize_tensor(dplain) != ref.serialize_plaintext_tenso" << std::endl; bad += _b; }
+    DeviceBatch ddec = cs.decrypt_tensor(sk, dneg);
+    { size_t _b = (size_t)(cs.serialize_tensor(ddec) != ref.serialize_plaintext_tensor(hplain)); if (_b) std::cerr << "wire-block check 10 failed (" << _b << "): cs.serialize_tensor(ddec) != ref.serialize_plaintext_tensor(" << std::endl; bad += _b; }
+    // encrypt_tensor from a device plaintext batch: same draw on both sides.  Non-negative values only: the reference hands a
+    // negative plaintext to power_of_f unreduced, and for some of them (-1) the result is a ciphertext that the reference
+    // itself cannot decrypt ("the form is not in the kernel"); the device reduces modulo 2^k first, like Mpz::mod would
+    for (int i = 0; i < 6; i++) { delete mixed.at(i / 3, i % 3); mixed.at(i / 3, i % 3) = new B200CryptoSystem::PlainText((unsigned long)(vals[i] < 0 ? -vals[i] * 1000003 : vals[i])); }
+    DeviceBatch dpt = cs.upload_plaintexts(mixed, 0);
+    DeviceBatch denc = cs.encrypt_tensor(pk, dpt);
+    auto henc = ref.encrypt_tensor(pk2, mixed);
+    { size_t _b = (size_t)(cs.serialize_tensor(denc) != ref.serialize_ciphertext_tensor(henc)); if (_b) std::cerr << "wire-block check 11 failed (" << _b << "): cs.serialize_tensor(denc) != ref.serialize_ciphertext_tensor" << std::endl; bad += _b; }
+    auto dl = cs.download_ciphertexts(denc);
+    { auto x = dl, y = henc; x.flatten(); y.flatten();
+      for (size_t i = 0; i < x.num_elements(); i++) if (!(x.at(i)->c1() == y.at(i)->c1() && x.at(i)->c2() == y.at(i)->c2())) std::cerr << "encrypt_tensor(device plaintexts): element " << i << " differs (c1 equal: " << (x.at(i)->c1() == y.at(i)->c1()) << ")" << std::endl; }
+    bad += diff(dl, henc);
+  } catch (const std::exception& e) { std::cout << "wire / device-resident block threw: " << e.what() << " after " << bad << " mismatches" << std::endl; bad += 1000; }
   std::cout << "mismatches " << bad << " launches " << cs.gpu_launches() << std::endl;
   return bad != 0;
 }

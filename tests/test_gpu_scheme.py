@@ -163,3 +163,71 @@ def test_beaver_pipeline_and_scal(systems, tier):
         want.append(O.add_ciphertexts(acc, O.encrypt(P, pk, (e1[i] * e2[i]) % M, r)))
     assert G.cts_out(res) == want
     assert G.ints_out(G.decrypt(res, sk)) == [(x * y) % M for x, y in zip(xs, ys)]
+
+
+def test_beaver_triplets_and_ct_matmul(systems, tier):
+    """Triplet generation (include/smpc/beavers_triplet_generation.hpp:17-37) and the ciphertext x ciphertext MATRIX product
+    (include/smpc/ciphertext_multiplications.hpp:51-110: n*m*p expansion, Beaver multiplication of the expanded vectors,
+    accumulation over the inner index) as device pipelines, against the oracle's composition of the reference operations."""
+    G = systems(tier)
+    P = O.Params.from_dict({k: (I(v) if isinstance(v, list) else v if isinstance(v, bool) else int(v)) for k, v in tier["params"].items()})
+    k, sk, pk = P.k, int(tier["sk"]), I(tier["pk"])
+    rng = random.Random(99)
+    M = 1 << k
+    big = tier["tier"] == "t1"
+    n, m, p = (1, 3, 1) if big else (2, 5, 3)   # m odd: the reduction tree has a slab left over at two levels
+    nmp = n * m * p
+    # --- triplets: one randomness for the [nmp, 3] tensor, row-major (a, b, ab)
+    ta, tb = [rng.randrange(10) for _ in range(nmp)], [rng.randrange(10) for _ in range(nmp)]
+    r3 = rng.randrange(1, P.exponent_bound)
+    trip = G.beaver_triplets(ta, tb, r3)
+    G.status()
+    got = G.cts_out(trip)
+    if not big:
+        want = [O.encrypt(P, pk, v % M, r3) for a, b in zip(ta, tb) for v in (a, b, a * b)]
+        assert got == want
+    assert G.ints_out(G.decrypt(trip, sk)) == [v % M for a, b in zip(ta, tb) for v in (a, b, a * b)]
+    A, B, C = trip[:, :, 0::3].contiguous(), trip[:, :, 1::3].contiguous(), trip[:, :, 2::3].contiguous()
+    # --- operands
+    enc = lambda v: O.encrypt(P, pk, v % M, rng.randrange(1, P.exponent_bound))
+    xs, ys = [rng.randrange(1000) for _ in range(n * m)], [rng.randrange(1000) for _ in range(m * p)]
+    ct1, ct2 = [enc(x) for x in xs], [enc(y) for y in ys]
+    e1, e2 = G.ct_matmul_expand(G.cts(ct1), G.cts(ct2), n, m, p)
+    G.status()
+    x1 = [ct1[i * m + j] for i in range(n) for j in range(m) for _ in range(p)]
+    x2 = [ct2[j * p + kk] for i in range(n) for j in range(m) for kk in range(p)]
+    assert G.cts_out(e1) == x1 and G.cts_out(e2) == x2
+    # --- Beaver multiplication of the expanded vectors (the decryption between open and close is the network round)
+    o1, o2 = G.beaver_open(e1, e2, A, B)
+    p1, p2 = G.decrypt(o1, sk), G.decrypt(o2, sk)
+    rc = rng.randrange(1, P.exponent_bound)
+    prod = G.beaver_close(p1, p2, A, B, C, rc)
+    G.status()
+    assert G.ints_out(G.decrypt(prod, sk)) == [(xs[i * m + j] * ys[j * p + kk]) % M for i in range(n) for j in range(m) for kk in range(p)]
+    # --- accumulation: res[i,k] = zero o prod_j prod[i,j,k]
+    zero = O.encrypt(P, pk, 0, rng.randrange(1, P.exponent_bound))
+    res = G.ct_matmul_reduce(prod, G.cts([zero]), n, m, p)
+    G.status()
+    pl = G.cts_out(prod)
+    want = []
+    for i in range(n):
+        for kk in range(p):
+            acc = zero
+            for j in range(m):
+                acc = O.add_ciphertexts(acc, pl[(i * m + j) * p + kk])
+            want.append(acc)
+    assert G.cts_out(res) == want
+    assert G.ints_out(G.decrypt(res, sk)) == [sum(xs[i * m + j] * ys[j * p + kk] for j in range(m)) % M for i in range(n) for kk in range(p)]
+    # the reduction is a pure function of the layout: other shapes over the same products (even m, m = 1, powers of two)
+    for nn, mm, pp in ([(3, 1, 1), (1, 3, 1)] if big else [(1, 10, 3), (3, 2, 5), (30, 1, 1), (1, 30, 1), (2, 8, 1), (5, 6, 1)]):
+        cnt = nn * mm * pp
+        r2 = G.ct_matmul_reduce(prod[:, :, :cnt].contiguous(), G.cts([zero]), nn, mm, pp)
+        G.status()
+        want = []
+        for i in range(nn):
+            for kk in range(pp):
+                acc = zero
+                for j in range(mm):
+                    acc = O.add_ciphertexts(acc, pl[(i * mm + j) * pp + kk])
+                want.append(acc)
+        assert G.cts_out(r2) == want, (nn, mm, pp)

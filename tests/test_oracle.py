@@ -161,3 +161,15 @@ def test_big_fixture_heads():
         assert ct == heads[i]
         for q in range(2):
             assert O.part_decrypt(int(t["shares"][q][0]), ct) == L.limbs_to_forms(z["pd_head_%d" % q], na, nc)[i]
+
+
+def test_wire_forms_plaintexts_match_reference_bytes():
+    """the shared layout for part-decryption-result and plaintext tensors vs bytes written by the compiled reference"""
+    w = load_golden("ref_wire.json")
+    for name, t in w.items():
+        forms = [int(x) for f in t["forms"] for x in f]
+        assert O.serialize_int_tensor(t["shape"], forms) == bytes.fromhex(t["pdr_hex"]), name
+        assert O.deserialize_int_tensor(bytes.fromhex(t["pdr_hex"]), 3) == (t["shape"], forms)
+        pts = [int(x) for x in t["pts"]]
+        assert O.serialize_int_tensor(t["pt_shape"], pts) == bytes.fromhex(t["pt_hex"]), name
+        assert O.deserialize_int_tensor(bytes.fromhex(t["pt_hex"]), 1) == (t["pt_shape"], pts)

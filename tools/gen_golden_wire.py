@@ -28,8 +28,24 @@ for tier, fn in TIERS.items():
     back = r.call("deserialize_ct_tensor", list(data))
     assert back[:3] == [2, 2, 3] and [int(x) for x in back[3:]] == flat
     assert data == O.serialize_ciphertext_tensor([2, 3], cts)
+    # part-decryption-result tensor (forms) and plaintext tensor: same layout, 3 / 1 integers per element
+    forms = [ct[0] for ct in cts[:5]] + [one]
+    fflat = [x for f in forms for x in f]
+    pdr = bytes(r.call("serialize_pdr_tensor", 2, 3, fflat))
+    back = r.call("deserialize_pdr_tensor", list(pdr))
+    assert back[:3] == [2, 2, 3] and [int(x) for x in back[3:]] == fflat
+    assert pdr == O.serialize_int_tensor([2, 3], fflat) and O.deserialize_int_tensor(pdr, 3) == ([2, 3], fflat)
+    k = int(p["k"])
+    pts = [0, 1, (1 << k) - 1, -5, (1 << k) + 12345, -(1 << (k // 2)), 255, 256, (1 << 64) - 1 if k >= 64 else 77, -1, 3, (1 << (2 * k)) - 3]
+    ptb = bytes(r.call("serialize_pt_tensor", 3, 4, pts))
+    back = r.call("deserialize_pt_tensor", list(ptb))
+    # (the reference returns the deserialised plaintext tensor flattened: cpu_cryptosystem.inl:292-317 never reshapes it back)
+    assert back[:2] == [1, 12] and [int(x) for x in back[2:]] == pts
+    assert ptb == O.serialize_int_tensor([3, 4], pts) and O.deserialize_int_tensor(ptb, 1) == ([3, 4], pts)
     r.close()
-    out[tier] = {"Delta": str(D), "shape": [2, 3], "cts": [[[str(x) for x in f] for f in ct] for ct in cts], "hex": data.hex()}
+    out[tier] = {"Delta": str(D), "shape": [2, 3], "cts": [[[str(x) for x in f] for f in ct] for ct in cts], "hex": data.hex(),
+                 "forms": [[str(x) for x in f] for f in forms], "pdr_hex": pdr.hex(),
+                 "pt_shape": [3, 4], "pts": [str(x) for x in pts], "pt_hex": ptb.hex()}
 with open(os.path.join(ROOT, "tests", "golden", "ref_wire.json"), "w") as fh:
     json.dump(out, fh)
 print({k: len(v["hex"]) // 2 for k, v in out.items()})
