@@ -16,6 +16,11 @@ struct CoopKernels {
   // flags of compose: 1 = second operand inverted
   static void compose(bool dupl, unsigned ny, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2,
                       u32 *out, int flags, u32 *bail, int *nbail, int mb);
+  // out[e] = in[e]^x (x shared: exp[0..el), or per element: exp[l*n + e]; sign applied at the end); tab: scratch of
+  // pow_tab_words(ny, nc, n) words for the window tables
+  static void pow(unsigned ny, cudaStream_t st, int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el, int per_elem,
+                  const unsigned char *expneg, int shared_neg, u32 *tab, u32 *bail, int *nbail);
+  static size_t pow_tab_words(unsigned ny, int nc, size_t n);
 };
 
 }  // namespace cofhe

@@ -38,6 +38,22 @@ __global__ void __launch_bounds__(kCoopBlock, MB) k_coop_compose(int dbits, int 
   if (have && !ok && g.lane == 0) bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
 }
 
+template <int T, int L, int N, int CAP, int MB>
+__global__ void __launch_bounds__(kCoopBlock, MB) k_coop_pow(int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
+                                                           int per_elem, const unsigned char *expneg, int shared_neg, u32 *tab, u32 *bail,
+                                                           int *nbail) {
+  constexpr int GPB = kCoopBlock / T, SW = CgScratch<T, L>::words, NT = (1 << kCoopPowW) - 1;
+  __shared__ u32 scr[GPB * SW];
+  Grp<T> g = make_group<T>(scr, SW);
+  size_t idx = (size_t)blockIdx.x * GPB + threadIdx.x / T;
+  const bool have = idx < n;
+  if (!have) idx = n - 1;
+  const size_t fl = (size_t)(2 * N + nc), off = (size_t)blockIdx.y * fl * n;
+  bool ok = cq_pow<T, L, N>(g, dbits, nc, n, idx, have, in + off, out + off, tab + (size_t)blockIdx.y * NT * fl * n, exp, el, per_elem, expneg,
+                            shared_neg);
+  if (have && !ok && g.lane == 0) bail[atomicAdd(nbail, 1)] = (u32)(blockIdx.y * n + idx);
+}
+
 // mb: resident blocks per SM the kernel is compiled for (3: up to 168 registers, 4: 128, 5: 96) -- an occupancy /
 // spilling trade-off chosen per width by the caller
 template <int T, int L, int N, int CAP>
@@ -55,6 +71,18 @@ void CoopKernels<T, L, N, CAP>::compose(bool dupl, unsigned ny, cudaStream_t st,
   else if (mb == 4) COOP_LAUNCH(4);
   else COOP_LAUNCH(3);
 #undef COOP_LAUNCH
+}
+
+template <int T, int L, int N, int CAP>
+size_t CoopKernels<T, L, N, CAP>::pow_tab_words(unsigned ny, int nc, size_t n) {
+  return (size_t)ny * ((1 << kCoopPowW) - 1) * (size_t)(2 * N + nc) * n;
+}
+template <int T, int L, int N, int CAP>
+void CoopKernels<T, L, N, CAP>::pow(unsigned ny, cudaStream_t st, int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
+                                    int per_elem, const unsigned char *expneg, int shared_neg, u32 *tab, u32 *bail, int *nbail) {
+  constexpr int GPB = kCoopBlock / T;
+  dim3 grid((unsigned)((n + GPB - 1) / GPB), ny);
+  k_coop_pow<T, L, N, CAP, 3><<<grid, kCoopBlock, 0, st>>>(dbits, nc, n, in, out, exp, el, per_elem, expneg, shared_neg, tab, bail, nbail);
 }
 
 }  // namespace cofhe

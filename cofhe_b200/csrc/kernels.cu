@@ -47,6 +47,8 @@ struct cofhe_b200_ctx {
   // scratch of the composite operations (matmul tables and partial products, fixed-base digits, ...)
   u32 *d_work;
   size_t work_bytes;
+  u32 *d_powtab = nullptr;   // window tables of the cooperative exponentiation kernel
+  size_t powtab_bytes = 0;
   u32 *d_tmp;         // form / ciphertext temporaries of encrypt, combine, decrypt
   size_t tmp_bytes;
   // CL_HSM2k scheme (set_scheme) and fixed bases h, pk (set_bases)
@@ -303,7 +305,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
               const u32 *exp, int el, int per_elem, const unsigned char *expneg, int shared_neg, cudaStream_t st) {
   Shape s{(int)ctx->na, (int)ctx->nc};
   dim3 grid(grid_for(n), ny);
-  const bool coop = use_coop(ctx) && op < 2 && !(neg2 & 2);
+  const bool coop = use_coop(ctx) && !(neg2 & 2);
   if (!ctx->fastn && !coop) {
     CAP_DISPATCH(ctx->cap, {
       const Group<CAP> *G = (const Group<CAP> *)ctx->d_group;
@@ -321,7 +323,17 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   if (coop) {
     COOP_DISPATCH(ctx->coopn, {
       typedef CoopKernels<CT, CL, CN, CCAP> K;
-      K::compose(op == 1, ny, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+      if (op < 2) K::compose(op == 1, ny, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+      else {
+        size_t tw = K::pow_tab_words(ny, nc, n) * sizeof(u32);
+        if (tw > ctx->powtab_bytes) {
+          if (ctx->d_powtab) cudaFree(ctx->d_powtab);
+          ctx->d_powtab = nullptr; ctx->powtab_bytes = 0;
+          if (cudaMalloc(&ctx->d_powtab, tw) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+          ctx->powtab_bytes = tw;
+        }
+        K::pow(ny, st, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_powtab, ctx->d_bail, cnt);
+      }
     })
   } else {
     const int pb = pick_block((size_t)ny * n, ctx->sms);
@@ -530,6 +542,7 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_stage) cudaFree(ctx->d_stage);
   if (ctx->d_work) cudaFree(ctx->d_work);
   if (ctx->d_tmp) cudaFree(ctx->d_tmp);
+  if (ctx->d_powtab) cudaFree(ctx->d_powtab);
   if (ctx->d_scheme) cudaFree(ctx->d_scheme);
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);

@@ -97,3 +97,34 @@ def test_coop_lockstep_regression():
         G.status()
         assert torch.equal(got, want)
     G.close()
+
+
+@pytest.mark.parametrize("name", ["t0", "node", "t1"])
+def test_coop_pow_equals_other_path(groups, name):
+    """exponentiation on the cooperative kernels (shared and per-element exponents, negative, zero) against the register /
+    generic path and the oracle"""
+    t = load_golden("ref_%s.json" % name)
+    G = coop_group(groups, t)
+    rng = random.Random(21)
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    n = 1000 if name != "t1" else 300
+    base = [O.power(h, rng.getrandbits(40) + 1) for _ in range(6)] + [pk, O.identity(int(t["params"]["Delta"]))]
+    fs = [base[i % len(base)] for i in range(n)]
+    f = G.forms(fs)
+    sh = int(t["sk"])
+    es = [rng.getrandbits(rng.choice([1, 5, 33, 64, 128])) * rng.choice([1, -1]) for _ in range(n)]
+    es[3] = 0
+    G.set_option("coop", 0)
+    want = (G.nupow(f, shared=sh), G.nupow(f, shared=-sh), G.nupow(f, exps=es))
+    G.status()
+    G.set_option("coop", 1)
+    try:
+        got = (G.nupow(f, shared=sh), G.nupow(f, shared=-sh), G.nupow(f, exps=es))
+        G.status()
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+        out = G.forms_out(got[2])
+        for i in range(0, n, 97):
+            assert out[i] == O.power(fs[i], es[i])
+    finally:
+        G.set_option("coop", -1)

@@ -93,3 +93,39 @@ def test_coop_full_warp_case():
     assert lib.hs_coop_compose(4, 9, na, dbits, nc, n, HS.P(arr[0]), HS.P(arr[1]), HS.P(o), 0, 0, HS.P(bail)) == 0
     lib.hs_coop_groups(2)
     assert (o == arr[2]).all()
+
+
+@pytest.mark.parametrize("name,shape", [("t0", (2, 5)), ("t0", (4, 3)), ("node", (2, 7)), ("t1", (4, 9))])
+def test_coop_pow(name, shape):
+    """the exponentiation state machine on the cooperative path: shared and per-element exponents, negative exponents,
+    leading zero windows, exponent 0 (declined: the neutral form does not fit the working shape)"""
+    t = load_golden("ref_%s.json" % name)
+    D = int(t["params"]["Delta"])
+    S = CoopSim(D, *shape)
+    rng = random.Random(5)
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    n = 5 if name != "t1" else 2
+    bits = 40 if name != "t1" else 24
+    f = [O.power(h, rng.getrandbits(30) + 2) for _ in range(n - 1)] + [pk]
+    a = L.forms_to_limbs(f, S.na, S.nc)
+    lib = S.lib
+    # shared exponent, negative
+    e = rng.getrandbits(bits) | (1 << (bits - 1))
+    el = 2
+    ex = L.ints_to_limbs([e], el)[:, 0].copy()
+    o = np.zeros_like(a); bail = np.zeros(n, dtype=np.uint8)
+    nb = lib.hs_coop_pow(S.T, S.L, S.na, S.dbits, S.nc, n, HS.P(a), HS.P(o), HS.P(ex), el, 0, None, 1, HS.P(bail))
+    assert nb == 0
+    assert L.limbs_to_forms(o, S.na, S.nc) == [O.power(x, -e) for x in f]
+    # per-element exponents of different lengths (leading zero windows), one of them 0, mixed signs
+    es = [rng.getrandbits(rng.choice([3, 9, 17, bits])) + 1 for _ in range(n)]
+    es[1] = 0
+    sg = np.array([i & 1 for i in range(n)], dtype=np.uint8)
+    exs = L.ints_to_limbs(es, el)
+    o = np.zeros_like(a); bail = np.zeros(n, dtype=np.uint8)
+    nb = lib.hs_coop_pow(S.T, S.L, S.na, S.dbits, S.nc, n, HS.P(a), HS.P(o), HS.P(exs), el, 1, HS.P(sg), 0, HS.P(bail))
+    assert bail.tolist() == [1 if x == 0 else 0 for x in es]
+    got = L.limbs_to_forms(o, S.na, S.nc)
+    for i in range(n):
+        if es[i]:
+            assert got[i] == O.power(f[i], -es[i] if sg[i] else es[i]), i
