@@ -34,6 +34,8 @@ SIGNATURES = {
     "cofhe_b200_beaver_triplets": (i32, [vp, sz, vp, vp, u32, vp, u32, vp, vp]),
     "cofhe_b200_ct_matmul_expand": (i32, [vp, sz, sz, sz, vp, vp, vp, vp, vp]),
     "cofhe_b200_ct_matmul_reduce": (i32, [vp, sz, sz, sz, vp, vp, vp, vp]),
+    "cofhe_b200_make_plaintexts": (i32, [vp, sz, vp, vp, u32, vp, vp]),
+    "cofhe_b200_plaintexts_to_floats": (i32, [vp, sz, vp, u32, vp, vp, vp]),
     "cofhe_b200_copy": (i32, [vp, vp, vp, sz, vp]),
     "cofhe_b200_plaintexts_mod2k": (i32, [vp, sz, vp, u32, vp, vp, u32, vp]),
     "cofhe_b200_rerandomize": (i32, [vp, sz, vp, vp, u32, i32, vp, vp]),

@@ -14,6 +14,7 @@
 
 #include "cofhe_b200.h"
 #include "coop_launch.cuh"
+#include "codec.cuh"
 #include "fast_launch.cuh"
 #include "fast_ops.cuh"
 #include "matmul.cuh"
@@ -410,6 +411,14 @@ int fb_pow(cofhe_b200_ctx *ctx, size_t n, const u32 *exps, u32 el, u32 *out, u32
   if ((int)el > s.el) return COFHE_B200_EINVAL;  // exponent wider than the tables were built for
   s.p = (unsigned)n;
   s.el = (int)el;
+  if (!ctx->fastn && use_coop(ctx)) {
+    // no table kernels at this width: (h^e, pk^e) as two exponentiations per element on the cooperative kernel
+    const int rows = (int)(2 * (2 * ctx->na + ctx->nc));
+    k_bcast<<<grid_for(n), kBlock, 0, st>>>(n, rows, ctx->d_fb_bases, out);
+    int rc = check_launch(ctx);
+    if (rc != COFHE_B200_OK) return rc;
+    return launch_op(ctx, 2, 2, n, out, out, out, 0, exps, (int)el, 1, nullptr, 0, st);
+  }
   if (!ctx->fastn) return mm_robust_all(ctx, s, ctx->d_fb_bases, exps, nullptr, out, st);
   return mm_eval(ctx, s, ctx->d_fb_bases, exps, nullptr, out, ctx->d_fb_tab, part, st);
 }
@@ -844,6 +853,48 @@ int cofhe_b200_plaintexts_mod2k(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m
   Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   k_pt_mod2k<<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(n, ctx->k, mag, (int)ml, sign, out, (int)ml_out);
+  return check_launch(ctx);
+}
+
+// ---- float codec (codec.cuh): make_plaintext / get_float_from_plaintext of the reference, one thread per element -----
+__global__ void __launch_bounds__(kBlock) k_codec_make(size_t n, int k, const float *x, u32 *mag, int ml, unsigned char *sign, int *err) {
+  size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  u32 m[16];
+  float v = x[e];
+  if (!(v - v == 0.0f)) { atomicMax(err, 1); v = 0.0f; }  // NaN / infinity: the reference's mpf_set_d is undefined there
+  int nl = ml < 16 ? ml : 16;
+  int sg = codec_make_plaintext(v, k, m, 16);
+  for (int i = nl; i < 16; i++) if (m[i]) atomicMax(err, 1);  // wider than the caller's limbs
+  for (int i = 0; i < ml; i++) mag[(size_t)i * n + e] = i < 16 ? m[i] : 0u;
+  if (sign) sign[e] = (unsigned char)sg;
+  else if (sg) atomicMax(err, 1);
+}
+__global__ void __launch_bounds__(kBlock) k_codec_get(size_t n, int k, const u32 *mag, int ml, const unsigned char *sign, float *out) {
+  size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  u32 m[64];
+  int nl = ml < 64 ? ml : 64;
+  for (int i = 0; i < nl; i++) m[i] = mag[(size_t)i * n + e];
+  out[e] = codec_get_float(m, nl, sign ? sign[e] : 0, k);
+}
+int cofhe_b200_make_plaintexts(cofhe_b200_ctx *ctx, size_t n, const float *x, uint32_t *mag, uint32_t ml, uint8_t *sign, void *stream) {
+  if (!ctx || (n && (!x || !mag)) || ml == 0) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme || ctx->k <= 0) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  k_codec_make<<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(n, ctx->k, x, mag, (int)ml, sign, ctx->d_err);
+  return check_launch(ctx);
+}
+int cofhe_b200_plaintexts_to_floats(cofhe_b200_ctx *ctx, size_t n, const uint32_t *mag, uint32_t ml, const uint8_t *sign, float *out,
+                                    void *stream) {
+  if (!ctx || (n && (!mag || !out)) || ml == 0 || ml > 64) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme || ctx->k <= 0) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  k_codec_get<<<grid_for(n), kBlock, 0, (cudaStream_t)stream>>>(n, ctx->k, mag, (int)ml, sign, out);
   return check_launch(ctx);
 }
 

@@ -329,6 +329,22 @@ class ClassGroupB200:
         capi.check(self.lib.cofhe_b200_ct_matmul_reduce(self.h, n, m, p, _ptr(prod), _ptr(init), _ptr(out), _stream()), "ct_matmul_reduce")
         return out
 
+    def make_plaintexts(self, x, ml=5):
+        """float32 device tensor -> (magnitudes [ml, n], signs [n]) = CPUCryptoSystem::make_plaintext of every element"""
+        x = x.to(self.device, torch.float32).contiguous()
+        n = x.numel()
+        mag = torch.empty((ml, n), dtype=torch.int32, device=self.device)
+        sg = torch.empty(max(1, n), dtype=torch.uint8, device=self.device)
+        capi.check(self.lib.cofhe_b200_make_plaintexts(self.h, n, _ptr(x), _ptr(mag), ml, _ptr(sg), _stream()), "make_plaintexts")
+        return mag, sg[:n]
+
+    def plaintexts_to_floats(self, mag, signs=None):
+        n = mag.shape[-1]
+        out = torch.empty(n, dtype=torch.float32, device=self.device)
+        capi.check(self.lib.cofhe_b200_plaintexts_to_floats(self.h, n, _ptr(mag), mag.shape[0], _ptr(signs) if signs is not None else None,
+                                                            _ptr(out), _stream()), "plaintexts_to_floats")
+        return out
+
     def _host_exp(self, e):
         el = max(1, (abs(int(e)).bit_length() + 31) // 32)
         return L.ints_to_limbs([abs(int(e))], el)[:, 0].copy(), el

@@ -222,6 +222,15 @@ int cofhe_b200_power_of_f(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint
 /* m[.][e] = dlog_F(f[e]) in [0, 2^k), ml limb rows (CL_HSM2k::dlog_in_F, CL_HSM2k.inl:408-455; both the
  * large-message branch through QFI::kernel_representative_2exp, qfi.inl:396-435, and the small-message branch). */
 int cofhe_b200_dlog(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *m, uint32_t ml, void *stream);
+/* The float <-> plaintext codec, batched: mag[.][e] / sign[e] = CPUCryptoSystem::make_plaintext(x[e]) and
+ * out[e] = get_float_from_plaintext(plaintext e) (reference include/x86_64/cpu_cryptosystem.inl:49-87, 114-122), bit for bit
+ * including what GMP's default-precision mpf arithmetic does to negative and fractional values (csrc/codec.cuh).  x and out
+ * are DEVICE float arrays; plaintexts are sign-magnitude ([ml][n] limbs + one sign byte per element, as the wire kernels
+ * produce them; sign == NULL: non-negative).  make: a value that does not fit ml limbs (ml >= 5 always fits), NaN or
+ * infinity raises the element status.  Needs set_scheme (k). */
+int cofhe_b200_make_plaintexts(cofhe_b200_ctx *ctx, size_t n, const float *x, uint32_t *mag, uint32_t ml, uint8_t *sign, void *stream);
+int cofhe_b200_plaintexts_to_floats(cofhe_b200_ctx *ctx, size_t n, const uint32_t *mag, uint32_t ml, const uint8_t *sign, float *out,
+                                    void *stream);
 /* out[e] = (h^r, pk^r o f^m[e]).  shared_r != 0: ONE exponent r[0..el) for the whole batch, as
  * CPUCryptoSystem::encrypt_tensor / encrypt_vector do (reference include/x86_64/cpu_cryptosystem_tensor_ops.inl:1-19,
  * CL_HSM_utils.inl:248-255); shared_r == 0: r[.][e] per element, as N calls of CPUCryptoSystem::encrypt

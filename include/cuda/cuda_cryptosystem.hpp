@@ -339,6 +339,11 @@ namespace CoFHE
         DeviceBatch scal_ciphertext_tensors(const PublicKey &pk, const DeviceBatch &s, const DeviceBatch &ct) const;
         DeviceBatch negate_ciphertext_tensor(const PublicKey &pk, const DeviceBatch &ct) const;
 
+        // the float codec, batched on the device (make_plaintext / get_float_from_plaintext of every element: csrc/codec.cuh
+        // reproduces the reference's mpf arithmetic bit for bit); the scalar calls above stay on the host object
+        DeviceBatch make_plaintext_tensor(const Tensor<float> &values) const;
+        Tensor<float> get_float_tensor(const DeviceBatch &pt) const;
+
         // wrap an existing reference object (used by deserialize)
         explicit B200CryptoSystem(b200_detail::HostCS host, int device = 0) : host_(std::move(host)), device_(device)
         {
@@ -1334,6 +1339,50 @@ namespace CoFHE
         check(rc, "combine");
         check(rs, "device arithmetic");
         return r;
+    }
+
+    inline DeviceBatch B200CryptoSystem::make_plaintext_tensor(const Tensor<float> &values) const
+    {
+        using namespace b200_detail;
+        auto flat = values;
+        flat.flatten();
+        size_t n = values.num_elements();
+        const uint32_t ml = std::max<uint32_t>(5, ml_ + 1); // 2^k itself occurs (a negative value below GMP's precision)
+        std::lock_guard<std::mutex> lock(mu_);
+        DeviceBatch b = make_batch(2, values.shape(), ml);
+        if (n == 0)
+            return b;
+        reserve(n);
+        float *hx = (float *)h_arena_;
+        for (size_t i = 0; i < n; i++)
+            hx[i] = flat[i];
+        up(h_arena_, n);
+        void *st = cofhe_b200_stream(ctx_);
+        check(cofhe_b200_make_plaintexts(ctx_, n, (const float *)dev(h_arena_), b.d_, ml, b.sg_, st), "make_plaintexts");
+        check(cofhe_b200_status(ctx_, st), "make_plaintexts: NaN, infinity or a value wider than the plaintext limbs");
+        return b;
+    }
+    inline Tensor<float> B200CryptoSystem::get_float_tensor(const DeviceBatch &pt) const
+    {
+        using namespace b200_detail;
+        want_kind(pt, 2, "get_float_tensor");
+        size_t n = pt.n_;
+        Tensor<float> res({n}, 0.0f);
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (n)
+            {
+                reserve(n);
+                void *st = cofhe_b200_stream(ctx_);
+                check(cofhe_b200_plaintexts_to_floats(ctx_, n, pt.d_, pt.ml_, pt.sg_, (float *)dev(h_arena_), st), "plaintexts_to_floats");
+                down(h_arena_, n);
+                const float *hx = (const float *)h_arena_;
+                for (size_t i = 0; i < n; i++)
+                    res[i] = hx[i];
+            }
+        }
+        res.reshape(pt.shape_);
+        return res;
     }
 
     // ---- factory: a B200 backend on CUDA device `device` (the reference's make_cryptosystem ignores its Device

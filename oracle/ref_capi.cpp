@@ -179,6 +179,10 @@ std::string call(Ref &R, const std::string &op, const std::vector<Mpz> &a) {
     for (size_t i = 0; i < t.ndim(); i++) o << t.shape()[i] << ' ';
     t.flatten();
     for (size_t i = 0; i < t.num_elements(); i++) { put(o, *t.at(i)); delete t.at(i); }
+  } else if (op == "make_plaintext_bits") {  // IEEE-754 bit patterns of floats... -> make_plaintext of each
+    for (auto &z : a) { uint32_t b = (uint32_t)to_sz(z); float x; memcpy(&x, &b, 4); put(o, R.cs.make_plaintext(x)); }
+  } else if (op == "get_float_bits") {       // plaintexts... -> bit patterns of get_float_from_plaintext
+    for (auto &z : a) { float x = R.cs.get_float_from_plaintext(z); uint32_t b; memcpy(&b, &x, 4); o << b << ' '; }
   } else if (op == "serialize_pdr_tensor") {  // rows cols forms... -> bytes of serialize_part_decryption_result_tensor
     size_t r = to_sz(a[0]), c = to_sz(a[1]), n = r * c;
     auto t = make_tensor<CS::PartDecryptionResult>(r, c); t.flatten();

@@ -245,6 +245,18 @@ int main(int argc, char** argv) {
     { auto x = dl, y = henc; x.flatten(); y.flatten();
       for (size_t i = 0; i < x.num_elements(); i++) if (!(x.at(i)->c1() == y.at(i)->c1() && x.at(i)->c2() == y.at(i)->c2())) std::cerr << "encrypt_tensor(device plaintexts): element " << i << " differs (c1 equal: " << (x.at(i)->c1() == y.at(i)->c1()) << ")" << std::endl; }
     bad += diff(dl, henc);
+    // float codec on the device against the host object's scalar codec (= the reference's)
+    {
+      float fv[8] = {0.0f, 1.0f, -1.0f, 2.5f, -2.5f, 123456.0f, -65536.75f, 1e20f};
+      Tensor<float> ft(2, 4, 0.0f); ft.flatten();
+      for (int i = 0; i < 8; i++) ft.at(i) = fv[i];
+      ft.reshape({2, 4});
+      DeviceBatch fp = cs.make_plaintext_tensor(ft);
+      auto fpt = cs.download_plaintexts(fp); fpt.flatten();
+      for (int i = 0; i < 8; i++) { size_t _b = !(*fpt.at(i) == ref.make_plaintext(fv[i])); if (_b) std::cerr << "make_plaintext_tensor differs at " << i << std::endl; bad += _b; }
+      auto fb = cs.get_float_tensor(fp); fb.flatten();
+      for (int i = 0; i < 8; i++) { size_t _b = !(fb.at(i) == ref.get_float_from_plaintext(*fpt.at(i))); if (_b) std::cerr << "get_float_tensor differs at " << i << std::endl; bad += _b; }
+    }
   } catch (const std::exception& e) { std::cout << "wire / device-resident block threw: " << e.what() << " after " << bad << " mismatches" << std::endl; bad += 1000; }
   std::cout << "mismatches " << bad << " launches " << cs.gpu_launches() << std::endl;
   return bad != 0;

@@ -7,6 +7,7 @@
 #include "ops.cuh"
 #include "hostsim_extra.inc"
 #include "coop_sim.inc"
+#include "codec.cuh"
 
 using namespace cofhe;
 
@@ -69,3 +70,18 @@ int hs_pow(int cap, const u32 *absD, int nd, int na, int nc, size_t n, const u32
 }
 
 }  // extern "C"
+
+// float codec (cofhe_b200/csrc/codec.cuh) on the host: bit patterns in, sign-magnitude limbs out, and back
+extern "C" void hs_codec_make(int k, size_t n, const unsigned *bits, int nl, unsigned *mag /* [n][nl] */, unsigned char *sign) {
+  for (size_t i = 0; i < n; i++) {
+    float x;
+    memcpy(&x, &bits[i], 4);
+    sign[i] = (unsigned char)cofhe::codec_make_plaintext(x, k, mag + i * nl, nl);
+  }
+}
+extern "C" void hs_codec_get(int k, size_t n, int nl, const unsigned *mag /* [n][nl] */, const unsigned char *sign, unsigned *bits) {
+  for (size_t i = 0; i < n; i++) {
+    float f = cofhe::codec_get_float(mag + i * nl, nl, sign[i], k);
+    memcpy(&bits[i], &f, 4);
+  }
+}

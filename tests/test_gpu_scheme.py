@@ -231,3 +231,49 @@ def test_beaver_triplets_and_ct_matmul(systems, tier):
                     acc = O.add_ciphertexts(acc, pl[(i * mm + j) * pp + kk])
                 want.append(acc)
         assert G.cts_out(r2) == want, (nn, mm, pp)
+
+
+def test_float_codec(systems, tier):
+    """make_plaintext / get_float_from_plaintext as device kernels against vectors written by the compiled reference
+    (tests/golden/codec.json) for this tier's k"""
+    import json
+    import os
+    import numpy as np
+    import torch
+    from conftest import GOLDEN
+    G = systems(tier)
+    with open(os.path.join(GOLDEN, "codec.json")) as fh:
+        g = json.load(fh)
+    k = int(tier["params"]["k"])
+    if str(k) not in g["k"]:
+        pytest.skip("no codec vectors for k = %d" % k)
+    t = g["k"][str(k)]
+    fb = np.array(g["float_bits"], dtype=np.uint32)
+    x = torch.from_numpy(fb.view(np.float32).copy()).to(G.device)
+    nl = 12
+    mag, sg = G.make_plaintexts(x, ml=nl)
+    G.status()
+    hm, hs = mag.cpu().numpy().view(np.uint32), sg.cpu().numpy()
+    got = [(-1 if hs[i] else 1) * sum(int(hm[j, i]) << (32 * j) for j in range(nl)) for i in range(len(fb))]
+    assert got == [int(v) for v in t["made"]]
+    f = G.plaintexts_to_floats(mag, sg)
+    assert [int(v) for v in f.cpu().numpy().view(np.uint32)] == t["floats_of_made"]
+    zs = [int(v) for v in t["ints"]]
+    zm = G.ints([abs(z) for z in zs], nl)
+    zsg = torch.tensor([1 if z < 0 else 0 for z in zs], dtype=torch.uint8, device=G.device)
+    f = G.plaintexts_to_floats(zm, zsg)
+    G.status()
+    assert [int(v) for v in f.cpu().numpy().view(np.uint32)] == t["floats_of_ints"]
+    # end to end: float -> plaintext -> encrypt -> decrypt -> float for small signed integers
+    vals = torch.tensor([0.0, 1.0, -1.0, 42.0, -42.0, 65535.0, -12345.0], dtype=torch.float32)
+    w = max(5, k // 32 + 1)  # 2^k itself occurs (negative values below GMP's precision at k >= 192)
+    m2, s2 = G.make_plaintexts(vals, ml=w)
+    red = torch.empty((G.ml, vals.numel()), dtype=torch.int32, device=G.device)
+    from cofhe_b200 import capi
+    from cofhe_b200.group import _ptr, _stream
+    capi.check(G.lib.cofhe_b200_plaintexts_mod2k(G.h, vals.numel(), _ptr(m2), w, _ptr(s2), _ptr(red), G.ml, _stream()), "mod2k")
+    ct = G.encrypt(red, 424242)
+    back = G.plaintexts_to_floats(G.decrypt(ct, int(tier["sk"])))
+    G.status()
+    if k >= 32 and k <= 128:
+        assert back.cpu().tolist() == vals.tolist()
