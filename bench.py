@@ -184,7 +184,7 @@ def run_reference(args):
         return
     from oracle import ref as R
     if not R.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libcofhe_ref.so (compiled reference) missing or libgmp.so.10 not loadable"}))
+        emit_line({"impl": "reference", "unavailable": "oracle/_ref/libcofhe_ref.so (compiled reference) missing or libgmp.so.10 not loadable"})
         return
     ref = open_reference(args.tier)
     cores = ref.threads()
@@ -214,7 +214,7 @@ def run_reference(args):
         except Exception as e:  # the second metric must not take the headline down
             line["form_exps"] = {"error": str(e)[:160]}
     ref.close()
-    print(json.dumps(line))
+    emit_line(line)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -744,7 +744,29 @@ def emit(args, G, fx, s, world, n, kern_ms, e2e_ms, e2e_steps, launches, clocks,
         line["form_exps"] = form_exps
     if extra is not None:
         line["extra"] = extra
-    print(json.dumps(line))
+    emit_line(line)
+
+
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """Keep stdout for the one JSON line: libraries (NCCL's version banner, torchrun notices) that write to file descriptor 1
+    are sent to stderr for the rest of the run; emit_line() writes to the original descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(obj):
+    data = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -758,6 +780,7 @@ def main():
     ap.add_argument("--no-extra", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    guard_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
