@@ -421,12 +421,14 @@ def matmul_metric(args, G, fx, s, world, rank, imad_peak):
     from cofhe_b200 import shard as S
     from cofhe_b200.group import to_device, to_host
     n, m, p = MM
+    if not G.reg:
+        n = 8 * world  # no table kernels at this width (generic path): 8 ct rows per GPU of the same 256-wide problem
     rows = n // world
     units = 2 * n * m * p
     sc = [i + 1 for i in range(m * p)]
     ebits = max(x.bit_length() for x in sc)
     scd = G.ints(sc, (ebits + 31) // 32)
-    out = {"metric": "form exponentiations/sec (scal_matmul %dx%d . %dx%d)" % (n, m, m, p), "unit": "form_exps/s", "scaling": "strong",
+    out = {"metric": "form exponentiations/sec (scal_matmul %dx%d . %dx%d)" % (MM[0], m, m, p), "unit": "form_exps/s", "scaling": "strong",
            "workload": "scal_ciphertext_tensors matmul: ct %dx%d = encrypt_tensor(pt[i]=i+1), scalars %dx%d = i+1 (<= %d bits), "
                        "%d ct rows per GPU, one NCCL all-gather of the result rows; 1 unit = one form raised to one scalar incl. its "
                        "accumulate composition = %d units" % (n, m, m, p, ebits, rows, units)}

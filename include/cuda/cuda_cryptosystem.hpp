@@ -20,7 +20,11 @@
 
 #include <cstdint>
 #include <cstring>
+#include <cstdlib>
+#include <exception>
+#include <memory>
 #include <mutex>
+#include <thread>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -130,6 +134,21 @@ namespace CoFHE
             BICYCL::Mpz::swap(const_cast<BICYCL::Mpz &>(f.c()), c);
             return f;
         }
+        // a contiguous share [off, off + ...) of an indexable container, read-only and writable
+        template <class C>
+        struct SliceIn
+        {
+            const C *c;
+            size_t off;
+            auto operator[](size_t i) const -> decltype((*c)[0]) { return (*c)[off + i]; }
+        };
+        template <class C>
+        struct SliceOut
+        {
+            C *c;
+            size_t off;
+            auto operator[](size_t i) -> decltype((*c)[0]) { return (*c)[off + i]; }
+        };
     } // namespace b200_detail
 
     // A tensor that lives on the device between calls (SURVEY.md 8b "device-resident handles"): the SoA limb batch of
@@ -219,10 +238,19 @@ namespace CoFHE
                 throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
             open();
         }
+        // several GPUs of one box behind one object: batched calls split their elements (matmul: its ct rows) into one
+        // contiguous share per device, constants are replicated, no exchange.  The environment variable
+        // COFHE_B200_DEVICES="0,1,2,3" does the same for the two-argument constructor the reference's callers use.
+        B200CryptoSystem(uint32_t security_level, uint32_t k, const std::vector<int> &devices)
+            : host_(security_level, k, false), device_(devices.empty() ? 0 : devices[0]), devices_(devices)
+        {
+            open();
+        }
+        size_t num_devices() const { return 1 + peers_.size(); }
         // copies re-create the RandGen exactly as the reference does (cpu_cryptosystem.hpp:37-68) and own a fresh
         // device context (contexts are not shared between objects: each serialises its own calls)
-        B200CryptoSystem(const B200CryptoSystem &o) : host_(o.host_), device_(o.device_) { open(); }
-        B200CryptoSystem(B200CryptoSystem &&o) : host_(std::move(o.host_)), device_(o.device_) { open(); }
+        B200CryptoSystem(const B200CryptoSystem &o) : host_(o.host_), device_(o.device_), devices_(o.devices_) { open(); }
+        B200CryptoSystem(B200CryptoSystem &&o) : host_(std::move(o.host_)), device_(o.device_), devices_(o.devices_) { open(); }
         B200CryptoSystem &operator=(const B200CryptoSystem &o)
         {
             if (this != &o)
@@ -230,6 +258,7 @@ namespace CoFHE
                 close();
                 host_ = o.host_;
                 device_ = o.device_;
+                devices_ = o.devices_;
                 open();
             }
             return *this;
@@ -241,6 +270,7 @@ namespace CoFHE
                 close();
                 host_ = std::move(o.host_);
                 device_ = o.device_;
+                devices_ = o.devices_;
                 open();
             }
             return *this;
@@ -345,7 +375,7 @@ namespace CoFHE
         Tensor<float> get_float_tensor(const DeviceBatch &pt) const;
 
         // wrap an existing reference object (used by deserialize)
-        explicit B200CryptoSystem(b200_detail::HostCS host, int device = 0) : host_(std::move(host)), device_(device)
+        explicit B200CryptoSystem(b200_detail::HostCS host, int device = 0, bool peer = false) : host_(std::move(host)), device_(device), is_peer_(peer)
         {
             if (host_.get_hsm2k().compact_variant())
                 throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
@@ -355,6 +385,9 @@ namespace CoFHE
     private:
         mutable b200_detail::HostCS host_; // RandGen lives here; draws happen in the reference's call order
         int device_;
+        std::vector<int> devices_;                                    // all devices of this object (empty: device_ only)
+        mutable std::vector<std::unique_ptr<B200CryptoSystem>> peers_; // one single-device object per further device
+        bool is_peer_ = false;
         cofhe_b200_ctx *ctx_ = nullptr;
         uint32_t na_ = 0, nc_ = 0, nd_ = 0, ml_ = 0, el_r_ = 0;
         mutable std::mutex mu_;        // one call at a time per context (the reference's methods are const and are
@@ -415,9 +448,36 @@ namespace CoFHE
             ml_ = ((uint32_t)H.k() + 31) / 32;
             el_r_ = (uint32_t)((H.encrypt_randomness_bound().nbits() + 31) / 32);
             pk_set_ = false;
+            if (is_peer_)
+                return;
+            if (devices_.empty())
+            {
+                const char *env = std::getenv("COFHE_B200_DEVICES");
+                if (env && device_ == 0)
+                {
+                    std::string e(env);
+                    size_t pos = 0;
+                    while (pos <= e.size())
+                    {
+                        size_t c = e.find(',', pos);
+                        std::string tok = e.substr(pos, c == std::string::npos ? std::string::npos : c - pos);
+                        if (!tok.empty())
+                            devices_.push_back(std::atoi(tok.c_str()));
+                        if (c == std::string::npos)
+                            break;
+                        pos = c + 1;
+                    }
+                    if (!devices_.empty() && devices_[0] != device_)
+                        devices_.clear(); // the list must start with this object's own device
+                }
+            }
+            peers_.clear();
+            for (size_t i = 1; i < devices_.size(); i++)
+                peers_.emplace_back(new B200CryptoSystem(host_, devices_[i], true));
         }
         void close()
         {
+            peers_.clear();
             if (ctx_)
             {
                 if (d_arena_)
@@ -501,7 +561,8 @@ namespace CoFHE
         uint32_t *dev(const uint32_t *h) const { return d_arena_ + (h - h_arena_); }
         static uint32_t limbs_of(const BICYCL::Mpz &z) { return z.nbits() ? (uint32_t)((z.nbits() + 31) / 32) : 1; }
 
-        // shared bodies (flat index ranges; the tensor / vector entry points only differ in their containers)
+        // shared bodies (flat index ranges; the tensor / vector entry points only differ in their containers).  *_flat split
+        // the range over this object's device and its peers (one contiguous share each); *_one run one share
         template <class Pts, class Out>
         void encrypt_flat(const PublicKey &pk, const Pts &pts, size_t n, Out &out) const;
         template <class Cts, class Out>
@@ -512,6 +573,45 @@ namespace CoFHE
         void add_flat(const Cts &a, const Cts &b, size_t n, Out &out) const;
         template <class Cts, class Exps, class Out>
         void pow_flat(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const;
+        template <class Pts, class Out>
+        void encrypt_one(const PublicKey &pk, const Pts &pts, size_t n, Out &out, const BICYCL::Mpz &r) const;
+        template <class Cts, class Out>
+        void decrypt_one(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const;
+        template <class Cts, class Out>
+        void part_decrypt_one(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const;
+        template <class Cts, class Out>
+        void add_one(const Cts &a, const Cts &b, size_t n, Out &out) const;
+        template <class Cts, class Exps, class Out>
+        void pow_one(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const;
+        template <class Sc, class Cts, class Out>
+        void matmul_one(const Sc &sflat, const Cts &cflat, size_t n, size_t m, size_t p, size_t ebits, const CipherText &zero, Out &out) const;
+
+        // run body(object, lo, hi) for a contiguous share of [0, n) on this object and on every peer, one thread per device
+        template <class Body>
+        void shard(size_t n, Body body) const
+        {
+            const size_t G = 1 + peers_.size();
+            if (G == 1 || n < G)
+            {
+                body(*this, (size_t)0, n);
+                return;
+            }
+            std::vector<std::exception_ptr> errs(G);
+            std::vector<std::thread> th;
+            for (size_t g = 0; g < G; g++)
+            {
+                const B200CryptoSystem *o = g == 0 ? this : peers_[g - 1].get();
+                size_t lo = n * g / G, hi = n * (g + 1) / G;
+                th.emplace_back([&, o, lo, hi, g]() {
+                    try { body(*o, lo, hi); } catch (...) { errs[g] = std::current_exception(); }
+                });
+            }
+            for (auto &t : th)
+                t.join();
+            for (auto &e : errs)
+                if (e)
+                    std::rethrow_exception(e);
+        }
     };
 
     // =================================================================================================================
@@ -520,12 +620,11 @@ namespace CoFHE
     // encrypt_tensor / encrypt_vector: ONE r per call, c1 = h^r shared, c2_i = pk^r o f^{m_i}
     // (reference cpu_cryptosystem_tensor_ops.inl:1-19, cpu_cryptosystem_vector_ops.inl:4-18)
     template <class Pts, class Out>
-    inline void B200CryptoSystem::encrypt_flat(const PublicKey &pk, const Pts &pts, size_t n, Out &out) const
+    inline void B200CryptoSystem::encrypt_one(const PublicKey &pk, const Pts &pts, size_t n, Out &out, const BICYCL::Mpz &r) const
     {
         using namespace b200_detail;
         std::lock_guard<std::mutex> lock(mu_);
         const BICYCL::CL_HSM2k &H = host_.get_hsm2k();
-        BICYCL::Mpz r = host_.get_rand_gen().random_mpz(H.encrypt_randomness_bound()); // the call's single draw
         if (n == 0)
             return;
         ensure_pk(pk);
@@ -547,7 +646,7 @@ namespace CoFHE
 
     // decrypt_tensor / decrypt_vector (cpu_cryptosystem_tensor_ops.inl:21-33)
     template <class Cts, class Out>
-    inline void B200CryptoSystem::decrypt_flat(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const
+    inline void B200CryptoSystem::decrypt_one(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const
     {
         using namespace b200_detail;
         std::lock_guard<std::mutex> lock(mu_);
@@ -568,7 +667,7 @@ namespace CoFHE
 
     // part_decrypt_tensor / part_decrypt_vector: d_i = c1_i^share (cpu_cryptosystem_tensor_ops.inl:35-47)
     template <class Cts, class Out>
-    inline void B200CryptoSystem::part_decrypt_flat(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const
+    inline void B200CryptoSystem::part_decrypt_one(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const
     {
         using namespace b200_detail;
         std::lock_guard<std::mutex> lock(mu_);
@@ -591,7 +690,7 @@ namespace CoFHE
 
     // add_ciphertext_tensors / add_ciphertext_vectors: no randomness (cpu_cryptosystem_tensor_ops.inl:242-264)
     template <class Cts, class Out>
-    inline void B200CryptoSystem::add_flat(const Cts &a, const Cts &b, size_t n, Out &out) const
+    inline void B200CryptoSystem::add_one(const Cts &a, const Cts &b, size_t n, Out &out) const
     {
         using namespace b200_detail;
         std::lock_guard<std::mutex> lock(mu_);
@@ -611,7 +710,7 @@ namespace CoFHE
     // (c1^s, c2^s) with one shared scalar or one scalar per element; no randomness in the batched reference paths
     // (cpu_cryptosystem_tensor_ops.inl:135-195 negate, :280-340 1-D scal; cpu_cryptosystem_vector_ops.inl:122-242)
     template <class Cts, class Exps, class Out>
-    inline void B200CryptoSystem::pow_flat(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const
+    inline void B200CryptoSystem::pow_one(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const
     {
         using namespace b200_detail;
         std::lock_guard<std::mutex> lock(mu_);
@@ -655,6 +754,93 @@ namespace CoFHE
         CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = get_ct(ho, i, n);
     }
 
+
+    // =================================================================================================================
+    // sharding over the devices of this object (its own and its peers'): contiguous index ranges, no exchange
+    // =================================================================================================================
+    template <class Pts, class Out>
+    inline void B200CryptoSystem::encrypt_flat(const PublicKey &pk, const Pts &pts, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        BICYCL::Mpz r;
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            r = host_.get_rand_gen().random_mpz(host_.get_hsm2k().encrypt_randomness_bound()); // the call's single draw
+        }
+        shard(n, [&](const B200CryptoSystem &o, size_t lo, size_t hi) {
+            SliceIn<Pts> in{&pts, lo};
+            SliceOut<Out> os{&out, lo};
+            o.encrypt_one(pk, in, hi - lo, os, r);
+        });
+    }
+    template <class Cts, class Out>
+    inline void B200CryptoSystem::decrypt_flat(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        shard(n, [&](const B200CryptoSystem &o, size_t lo, size_t hi) {
+            SliceIn<Cts> in{&cts, lo};
+            SliceOut<Out> os{&out, lo};
+            o.decrypt_one(sk, in, hi - lo, os);
+        });
+    }
+    template <class Cts, class Out>
+    inline void B200CryptoSystem::part_decrypt_flat(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        shard(n, [&](const B200CryptoSystem &o, size_t lo, size_t hi) {
+            SliceIn<Cts> in{&cts, lo};
+            SliceOut<Out> os{&out, lo};
+            o.part_decrypt_one(sks, in, hi - lo, os);
+        });
+    }
+    template <class Cts, class Out>
+    inline void B200CryptoSystem::add_flat(const Cts &a, const Cts &b, size_t n, Out &out) const
+    {
+        using namespace b200_detail;
+        shard(n, [&](const B200CryptoSystem &o, size_t lo, size_t hi) {
+            SliceIn<Cts> ia{&a, lo}, ib{&b, lo};
+            SliceOut<Out> os{&out, lo};
+            o.add_one(ia, ib, hi - lo, os);
+        });
+    }
+    template <class Cts, class Exps, class Out>
+    inline void B200CryptoSystem::pow_flat(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const
+    {
+        using namespace b200_detail;
+        shard(n, [&](const B200CryptoSystem &o, size_t lo, size_t hi) {
+            SliceIn<Cts> in{&cts, lo};
+            SliceOut<Out> os{&out, lo};
+            if (per_elem)
+            {
+                SliceIn<Exps> ex{per_elem, lo};
+                o.pow_one(in, hi - lo, &ex, shared, os);
+            }
+            else
+                o.pow_one(in, hi - lo, (const SliceIn<Exps> *)nullptr, shared, os);
+        });
+    }
+    // res[i,k] = zero o prod_j ct[i,j]^{s[j,k]} for the n ct rows of `cflat` (row-major n x m), scalars m x p
+    template <class Sc, class Cts, class Out>
+    inline void B200CryptoSystem::matmul_one(const Sc &sflat, const Cts &cflat, size_t n, size_t m, size_t p, size_t ebits, const CipherText &zero,
+                                             Out &out) const
+    {
+        using namespace b200_detail;
+        std::lock_guard<std::mutex> lock(mu_);
+        if (n == 0)
+            return;
+        uint32_t el = (uint32_t)((ebits + 31) / 32);
+        size_t cw = 2 * fl() * n * m, sw = (size_t)el * m * p, zw = 2 * fl(), ow = 2 * fl() * n * p;
+        reserve(cw + sw + zw + ow);
+        uint32_t *hc = h_arena_, *hs = hc + cw, *hz = hs + sw, *ho = hz + zw;
+        put_cts(cflat, n * m, hc);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < m * p; i++) put_mpz(*sflat[i], hs + i, el, m * p, false);
+        put_form(zero.c1(), hz, 0, 1);
+        put_form(zero.c2(), hz + fl(), 0, 1);
+        up(hc, cw + sw + zw);
+        check(cofhe_b200_scal_matmul(ctx_, n, m, p, dev(hc), dev(hs), el, (uint32_t)ebits, dev(hz), dev(ho), cofhe_b200_stream(ctx_)), "scal_matmul");
+        down(ho, ow);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n * p; i++) out[i] = get_ct(ho, i, n * p);
+    }
 
     // =================================================================================================================
     // single-element entry points: the same device paths with n = 1 (no computation is left to the host object)
@@ -945,29 +1131,19 @@ namespace CoFHE
         Tensor<CipherText *> res({n, p}, nullptr);
         res.flatten();
         CipherText zero = this->encrypt(pk, this->make_plaintext(0)); // the call's single draw, as the reference
+        size_t ebits = 1;
+        for (size_t i = 0; i < m * p; i++)
         {
-            std::lock_guard<std::mutex> lock(mu_);
-            uint32_t el = 1;
-            size_t ebits = 1;
-            for (size_t i = 0; i < m * p; i++)
-            {
-                if (sflat[i]->sgn() < 0)
-                    throw std::invalid_argument("matmul scalars must be non-negative");
-                ebits = std::max(ebits, (size_t)sflat[i]->nbits());
-            }
-            el = (uint32_t)((ebits + 31) / 32);
-            size_t cw = 2 * fl() * n * m, sw = (size_t)el * m * p, zw = 2 * fl(), ow = 2 * fl() * n * p;
-            reserve(cw + sw + zw + ow);
-            uint32_t *hc = h_arena_, *hs = hc + cw, *hz = hs + sw, *ho = hz + zw;
-            put_cts(cflat, n * m, hc);
-            CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < m * p; i++) put_mpz(*sflat[i], hs + i, el, m * p, false);
-            put_form(zero.c1(), hz, 0, 1);
-            put_form(zero.c2(), hz + fl(), 0, 1);
-            up(hc, cw + sw + zw);
-            check(cofhe_b200_scal_matmul(ctx_, n, m, p, dev(hc), dev(hs), el, (uint32_t)ebits, dev(hz), dev(ho), cofhe_b200_stream(ctx_)), "scal_matmul");
-            down(ho, ow);
-            CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n * p; i++) res[i] = get_ct(ho, i, n * p);
+            if (sflat[i]->sgn() < 0)
+                throw std::invalid_argument("matmul scalars must be non-negative");
+            ebits = std::max(ebits, (size_t)sflat[i]->nbits());
         }
+        // rows of ct (and of the result) are independent (cpu_cryptosystem_tensor_ops.inl:396-417): one share of rows per device
+        shard(n, [&](const B200CryptoSystem &o, size_t lo, size_t hi) {
+            SliceIn<Tensor<CipherText *>> in{&cflat, lo * m};
+            SliceOut<Tensor<CipherText *>> os{&res, lo * p};
+            o.matmul_one(sflat, in, hi - lo, m, p, ebits, zero, os);
+        });
         res.reshape({n, p});
         return res;
     }
