@@ -588,10 +588,10 @@ namespace CoFHE
 
         // run body(object, lo, hi) for a contiguous share of [0, n) on this object and on every peer, one thread per device
         template <class Body>
-        void shard(size_t n, Body body) const
+        void shard(size_t n, Body body, size_t min_per_device = 1) const
         {
             const size_t G = 1 + peers_.size();
-            if (G == 1 || n < G)
+            if (G == 1 || n < G * min_per_device)
             {
                 body(*this, (size_t)0, n);
                 return;
@@ -771,7 +771,7 @@ namespace CoFHE
             SliceIn<Pts> in{&pts, lo};
             SliceOut<Out> os{&out, lo};
             o.encrypt_one(pk, in, hi - lo, os, r);
-        });
+        }, 4096);
     }
     template <class Cts, class Out>
     inline void B200CryptoSystem::decrypt_flat(const SecretKey &sk, const Cts &cts, size_t n, Out &out) const
@@ -781,7 +781,7 @@ namespace CoFHE
             SliceIn<Cts> in{&cts, lo};
             SliceOut<Out> os{&out, lo};
             o.decrypt_one(sk, in, hi - lo, os);
-        });
+        }, 256);
     }
     template <class Cts, class Out>
     inline void B200CryptoSystem::part_decrypt_flat(const SecretKeyShare &sks, const Cts &cts, size_t n, Out &out) const
@@ -791,7 +791,7 @@ namespace CoFHE
             SliceIn<Cts> in{&cts, lo};
             SliceOut<Out> os{&out, lo};
             o.part_decrypt_one(sks, in, hi - lo, os);
-        });
+        }, 256);
     }
     template <class Cts, class Out>
     inline void B200CryptoSystem::add_flat(const Cts &a, const Cts &b, size_t n, Out &out) const
@@ -801,7 +801,7 @@ namespace CoFHE
             SliceIn<Cts> ia{&a, lo}, ib{&b, lo};
             SliceOut<Out> os{&out, lo};
             o.add_one(ia, ib, hi - lo, os);
-        });
+        }, (size_t)1 << 16); // an add is cheaper on the device than its marshalling on the host: only very large tensors are split
     }
     template <class Cts, class Exps, class Out>
     inline void B200CryptoSystem::pow_flat(const Cts &cts, size_t n, const Exps *per_elem, const BICYCL::Mpz *shared, Out &out) const
@@ -817,7 +817,7 @@ namespace CoFHE
             }
             else
                 o.pow_one(in, hi - lo, (const SliceIn<Exps> *)nullptr, shared, os);
-        });
+        }, 256);
     }
     // res[i,k] = zero o prod_j ct[i,j]^{s[j,k]} for the n ct rows of `cflat` (row-major n x m), scalars m x p
     template <class Sc, class Cts, class Out>
