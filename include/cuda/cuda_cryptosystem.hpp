@@ -18,6 +18,7 @@
 #ifndef COFHE_B200_CUDA_CRYPTO_SYSTEM_HPP_INCLUDED
 #define COFHE_B200_CUDA_CRYPTO_SYSTEM_HPP_INCLUDED
 
+#include <atomic>
 #include <cstdint>
 #include <cstring>
 #include <cstdlib>
@@ -390,6 +391,7 @@ namespace CoFHE
         bool is_peer_ = false;
         cofhe_b200_ctx *ctx_ = nullptr;
         uint32_t na_ = 0, nc_ = 0, nd_ = 0, ml_ = 0, el_r_ = 0;
+        mutable std::atomic<bool> marshal_err_{false}; // set by put_int inside OpenMP loops, thrown by check_marshal
         mutable std::mutex mu_;        // one call at a time per context (the reference's methods are const and are
                                        // called from 8 server threads: node/server.hpp:16,187-196)
         mutable bool pk_set_ = false;
@@ -524,11 +526,32 @@ namespace CoFHE
         }
 
         // ---- marshalling between BICYCL objects and the SoA limb layout (include/cofhe_b200.h "Layout") -----------
+        // put_mpz for use inside the OpenMP marshalling loops: an exception must not leave a parallel region, so a value
+        // that does not fit (a form of another discriminant, an oversized integer) is written as zero and flagged; the
+        // next up() / upload check turns the flag into std::invalid_argument before anything reaches the device
+        void put_int(const BICYCL::Mpz &z, uint32_t *dst, size_t nl, size_t stride, bool twos) const
+        {
+            try
+            {
+                b200_detail::put_mpz(z, dst, nl, stride, twos);
+            }
+            catch (const std::exception &)
+            {
+                for (size_t i = 0; i < nl; i++)
+                    dst[i * stride] = 0;
+                marshal_err_.store(true, std::memory_order_relaxed);
+            }
+        }
+        void check_marshal() const
+        {
+            if (marshal_err_.exchange(false))
+                throw std::invalid_argument("cofhe_b200: a value does not fit the limb shape of this cryptosystem (form of another discriminant?)");
+        }
         void put_form(const BICYCL::QFI &f, uint32_t *buf, size_t idx, size_t n) const
         {
-            b200_detail::put_mpz(f.a(), buf + idx, na_, n, false);
-            b200_detail::put_mpz(f.b(), buf + (size_t)na_ * n + idx, na_, n, true);
-            b200_detail::put_mpz(f.c(), buf + (size_t)2 * na_ * n + idx, nc_, n, false);
+            put_int(f.a(), buf + idx, na_, n, false);
+            put_int(f.b(), buf + (size_t)na_ * n + idx, na_, n, true);
+            put_int(f.c(), buf + (size_t)2 * na_ * n + idx, nc_, n, false);
         }
         BICYCL::QFI get_form(const uint32_t *buf, size_t idx, size_t n) const
         {
@@ -550,6 +573,7 @@ namespace CoFHE
         }
         void up(const uint32_t *h, size_t words) const
         {
+            check_marshal();
             b200_detail::check(cofhe_b200_upload(ctx_, d_arena_ + (h - h_arena_), h, words * 4, cofhe_b200_stream(ctx_)), "upload");
         }
         // download + synchronise + report element errors
@@ -635,7 +659,7 @@ namespace CoFHE
         {
             BICYCL::Mpz m;
             BICYCL::Mpz::mod(m, *pts[i], H.cleartext_bound()); // f has order 2^k: only m mod 2^k matters
-            put_mpz(m, hm + i, ml_, n, false);
+            put_int(m, hm + i, ml_, n, false);
         }
         put_mpz(r, hr, el_r_, 1, false);
         up(hm, mw + rw);
@@ -833,7 +857,7 @@ namespace CoFHE
         reserve(cw + sw + zw + ow);
         uint32_t *hc = h_arena_, *hs = hc + cw, *hz = hs + sw, *ho = hz + zw;
         put_cts(cflat, n * m, hc);
-        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < m * p; i++) put_mpz(*sflat[i], hs + i, el, m * p, false);
+        CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < m * p; i++) put_int(*sflat[i], hs + i, el, m * p, false);
         put_form(zero.c1(), hz, 0, 1);
         put_form(zero.c2(), hz + fl(), 0, 1);
         up(hc, cw + sw + zw);
@@ -1180,6 +1204,7 @@ namespace CoFHE
             return b;
         reserve(w);
         CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) put_form(*flat[i], h_arena_, i, n);
+        check_marshal();
         check(cofhe_b200_upload(ctx_, b.d_, h_arena_, w * 4, cofhe_b200_stream(ctx_)), "upload");
         check(cofhe_b200_status(ctx_, cofhe_b200_stream(ctx_)), "upload");
         return b;

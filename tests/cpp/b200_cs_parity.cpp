@@ -258,6 +258,23 @@ int main(int argc, char** argv) {
       for (int i = 0; i < 8; i++) { size_t _b = !(fb.at(i) == ref.get_float_from_plaintext(*fpt.at(i))); if (_b) std::cerr << "get_float_tensor differs at " << i << std::endl; bad += _b; }
     }
   } catch (const std::exception& e) { std::cout << "wire / device-resident block threw: " << e.what() << " after " << bad << " mismatches" << std::endl; bad += 1000; }
+  // a ciphertext of a larger discriminant does not fit the limb shape: the marshalling loops run under OpenMP, so the
+  // error must come back as std::invalid_argument from the call, not as an exception escaping a parallel region
+  if (nbits < 256) {
+    try {
+      CPUCryptoSystem other(256, kk);
+      auto osk = other.keygen(); auto opk = other.keygen(osk);
+      Tensor<B200CryptoSystem::PlainText*> opt(2, nullptr);
+      for (size_t i = 0; i < 2; i++) opt.at(i) = new B200CryptoSystem::PlainText((unsigned long)(i + 5));
+      auto oct = other.encrypt_tensor(opk, opt);
+      bool thrown = false;
+      try { auto r = cs.add_ciphertext_tensors(pk, oct, oct); } catch (const std::invalid_argument&) { thrown = true; }
+      if (!thrown) { std::cerr << "alien ciphertexts were not rejected" << std::endl; bad++; }
+      // and the object is usable afterwards
+      auto again = cs.add_ciphertext_tensors(pk, ct, ct);
+      bad += diff(again, sum2);
+    } catch (const std::exception& e) { std::cout << "alien-ciphertext block threw: " << e.what() << std::endl; bad += 1000; }
+  }
   std::cout << "mismatches " << bad << " launches " << cs.gpu_launches() << std::endl;
   return bad != 0;
 }
