@@ -6,8 +6,9 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libcofhe_b200.so")
 
-OK, EINVAL, ECUDA, EARITH, ENOMEM, ESTATE = 0, 1, 2, 3, 4, 5
-_NAMES = {1: "EINVAL", 2: "ECUDA", 3: "EARITH", 4: "ENOMEM", 5: "ESTATE"}
+OK, EINVAL, ECUDA, EARITH, ENOMEM, ESTATE, ETOOBIG = 0, 1, 2, 3, 4, 5, 6
+STATIC_MAX_N = 262144  # COFHE_B200_STATIC_MAX_N
+_NAMES = {1: "EINVAL", 2: "ECUDA", 3: "EARITH", 4: "ENOMEM", 5: "ESTATE", 6: "ETOOBIG"}
 
 
 class CofheError(RuntimeError):
@@ -54,6 +55,7 @@ SIGNATURES = {
     "cofhe_b200_nupow": (i32, [vp, sz, vp, vp, u32, i32, vp, i32, vp, vp]),
     "cofhe_b200_add_ciphertexts": (i32, [vp, sz, vp, vp, vp, vp]),
     "cofhe_b200_add_ciphertexts_host": (i32, [vp, sz, vp, vp, vp]),
+    "cofhe_b200_add_ciphertexts_static": (i32, [vp, sz, vp, vp, vp, vp]),
     "cofhe_b200_scal_matmul": (i32, [vp, sz, sz, sz, vp, vp, u32, u32, vp, vp, vp]),
     "cofhe_b200_set_scheme": (i32, [vp, u32, vp, u32]),
     "cofhe_b200_set_bases": (i32, [vp, vp, vp, u32]),

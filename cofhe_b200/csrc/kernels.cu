@@ -462,6 +462,37 @@ struct EnterHost {
 
 }  // namespace
 
+// ---- fixed scratch of cofhe_b200_add_ciphertexts_static ---------------------------------------------------------
+// The one entry point that must not allocate keeps its scratch (the two counters and the list of declined elements that
+// cofhe_b200_add_ciphertexts keeps in cudaMalloc'ed, grown-on-demand buffers) in this array.  Every GPU that loads the
+// library holds its own copy (2 MiB + 256 bytes) until the process exits.  words [0, 64): counters (only [0] and [1]
+// are used; the rest pads the list to a 256-byte boundary), words [64, 64 + 2 * COFHE_B200_STATIC_MAX_N): the list.
+static __device__ __align__(256) u32 g_static_scratch[64 + 2 * (size_t)COFHE_B200_STATIC_MAX_N];
+
+namespace {
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address on a given device
+// comes from cudaGetSymbolAddress with that device current.  Looked up once per device (cofhe_b200_create does it at
+// set-up, the entry point finds it cached) -- the lookup allocates nothing.
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+u32 *g_static_ptr[kStaticMaxDevices];
+bool g_static_tried[kStaticMaxDevices];
+// the caller has made `device` current
+int static_scratch(int device, u32 **ptr) {
+  if (device < 0 || device >= kStaticMaxDevices) return COFHE_B200_EINVAL;
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_tried[device]) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) { cudaGetLastError(); p = nullptr; }
+    else g_static_tried[device] = true;  // a failure is retried by the next call
+    g_static_ptr[device] = (u32 *)p;
+  }
+  *ptr = g_static_ptr[device];
+  return *ptr ? COFHE_B200_OK : COFHE_B200_ECUDA;
+}
+}  // namespace
+
 extern "C" {
 
 const char *cofhe_b200_version(void) { return "cofhe_b200 0.1 sm_100a"; }
@@ -537,6 +568,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
                               cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking) != cudaSuccess))
     rc = COFHE_B200_ECUDA;
   if (rc != COFHE_B200_OK) { cofhe_b200_destroy(ctx); return rc; }
+  { u32 *unused = nullptr; (void)static_scratch(device, &unused); }  // address of the fixed scratch on this device (no allocation)
   *out = ctx;
   return COFHE_B200_OK;
 }
@@ -654,6 +686,50 @@ int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct
   Enter g(ctx, (cudaStream_t)stream);
   if (!g.ok) return COFHE_B200_ECUDA;
   return launch_op(ctx, 0, 2, n, ct1, ct2, out, 0, nullptr, 0, 0, nullptr, 0, (cudaStream_t)stream);
+}
+
+// cofhe_b200_add_ciphertexts without any allocation: the same kernels, their scratch in g_static_scratch.
+int cofhe_b200_add_ciphertexts_static(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
+                                      void *stream) {
+  if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
+  if (n > (size_t)COFHE_B200_STATIC_MAX_N) return COFHE_B200_ETOOBIG;
+  if (n == 0) return COFHE_B200_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  Enter g(ctx, st);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  u32 *scr = nullptr;
+  int rc = static_scratch(ctx->device, &scr);
+  if (rc != COFHE_B200_OK) return rc;
+  int *cnt = (int *)scr, *cnt_next = cnt + 1;
+  u32 *bail = scr + 64;
+  const unsigned ny = 2;
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  dim3 grid(grid_for(n), ny);
+  const bool coop = use_coop(ctx);
+  if (!ctx->fastn && !coop) {  // the generic kernel keeps no list
+    CAP_DISPATCH(ctx->cap, k_compose<CAP><<<grid, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, ct1, ct2, out, 0, ctx->d_err))
+    return check_launch(ctx);
+  }
+  // the array keeps what the previous call left: the counters start every call at zero
+  if (cudaMemsetAsync(scr, 0, 64 * sizeof(u32), st) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ECUDA; }
+  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  if (coop) {
+    COOP_DISPATCH(ctx->coopn, {
+      typedef CoopKernels<CT, CL, CN, CCAP> K;
+      K::compose(false, ny, st, ctx->d_group, dbits, nc, n, ct1, ct2, out, 0, bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+    })
+  } else {
+    FAST_DISPATCH(ctx->fastn, {
+      typedef FastKernels<FN, FCAP> K;
+      K::compose(false, grid, st, ctx->d_group, dbits, nc, n, ct1, ct2, out, 0, bail, cnt);
+    })
+  }
+  rc = check_launch(ctx);
+  if (rc != COFHE_B200_OK) return rc;
+  unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
+  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, 0, ct1, ct2, out, 0, nullptr, 0, 0,
+                                                          nullptr, 0, bail, cnt, cnt_next, ctx->d_err))
+  return check_launch(ctx);
 }
 
 int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct, const uint32_t *scal,

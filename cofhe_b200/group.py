@@ -133,6 +133,13 @@ class ClassGroupB200:
         capi.check(self.lib.cofhe_b200_add_ciphertexts(self.h, n, _ptr(ct1), _ptr(ct2), _ptr(out), _stream()), "add")
         return out
 
+    def add_ciphertexts_static(self, ct1, ct2, out):
+        """add_ciphertexts through the entry point that allocates nothing (scratch in a fixed array inside the library, at
+        most capi.STATIC_MAX_N ciphertexts per call); `out` is the caller's, like the inputs."""
+        n = ct1.shape[-1]
+        capi.check(self.lib.cofhe_b200_add_ciphertexts_static(self.h, n, _ptr(ct1), _ptr(ct2), _ptr(out), _stream()), "add_static")
+        return out
+
     def scal_matmul(self, ct, scalars, n, m, p, init, ebits=None):
         """out[i,k] = init o prod_j ct[i,j]^{s[j,k]}: ct device tensor [2, fl, n*m]; scalars: m*p non-negative ints
         (row-major) or a device tensor [el, m*p]; init: device tensor [2, fl, 1] (the `zero` ciphertext)."""

@@ -45,6 +45,7 @@ extern "C" {
 #define COFHE_B200_EARITH 3 /* an element failed: not a form of this discriminant / does not fit the limb shape */
 #define COFHE_B200_ENOMEM 4
 #define COFHE_B200_ESTATE 5 /* scheme parameters / public key not set for an operation that needs them */
+#define COFHE_B200_ETOOBIG 6 /* batch larger than the fixed scratch of a _static entry point (COFHE_B200_STATIC_MAX_N) */
 
 typedef struct cofhe_b200_ctx cofhe_b200_ctx;
 
@@ -99,6 +100,20 @@ int cofhe_b200_nupow(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, const uin
  * (reference include/x86_64/cpu_cryptosystem_tensor_ops.inl:197-267, cpu_cryptosystem_vector_ops.inl:58-120). */
 int cofhe_b200_add_ciphertexts(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
                                void *stream);
+/* cofhe_b200_add_ciphertexts for callers that cannot tolerate an allocation inside the call (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernels, bit-identical results; the call issues one memset and the kernels on
+ * `stream` and calls no cudaMalloc / cudaFree or any other allocating routine.  The scratch that cofhe_b200_add_ciphertexts
+ * grows on demand (the list of elements handed to the robust path, and its counters) lives in ONE fixed array of device
+ * memory inside the library instead: 2 MiB + 256 bytes on every GPU that loads the library, held until the process exits.
+ *   - n > COFHE_B200_STATIC_MAX_N is refused with COFHE_B200_ETOOBIG (nothing is launched); split the batch.
+ *   - the array is shared by every call, every context and every stream of the process on that GPU: calls that overlap
+ *     on the GPU (different streams or contexts without ordering between them) race on it.  Calls on one stream, or
+ *     ordered by events, are fine -- each call clears the counters it needs at its start, on its stream.
+ * The context itself (cofhe_b200_create) allocates as before; create it ahead of the region that must not allocate. */
+#define COFHE_B200_STATIC_MAX_N 262144u /* ciphertexts per call */
+int cofhe_b200_add_ciphertexts_static(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out,
+                                      void *stream);
 /* Same, on HOST buffers, blocking (the call a CryptoSystem backend makes per add_ciphertext_tensors).  Page-locked
  * buffers (cudaHostAlloc / cudaHostRegister / cofhe_b200_host_alloc) are read and written by the kernels directly over
  * PCIe, without staging (discriminants with a register-resident instantiation, cofhe_b200_reg_limbs() != 0; the others
