@@ -58,6 +58,8 @@ SIGNATURES = {
     "cofhe_b200_add_ciphertexts_static": (i32, [vp, sz, vp, vp, vp, vp]),
     "cofhe_b200_scal_matmul": (i32, [vp, sz, sz, sz, vp, vp, u32, u32, vp, vp, vp]),
     "cofhe_b200_set_scheme": (i32, [vp, u32, vp, u32]),
+    "cofhe_b200_set_compact": (i32, [vp, i32]),
+    "cofhe_b200_lift": (i32, [vp, sz, vp, vp, vp]),
     "cofhe_b200_set_bases": (i32, [vp, vp, vp, u32]),
     "cofhe_b200_fixed_base_pow": (i32, [vp, sz, vp, u32, vp, vp]),
     "cofhe_b200_power_of_f": (i32, [vp, sz, vp, u32, vp, vp]),

@@ -25,6 +25,18 @@ typedef uint32_t u32;
 typedef uint64_t u64;
 typedef int64_t i64;
 
+// Compact variant of CL_HSM2k (reference CL_HSM2k.inl:255 `Cl_G`): the c1 half of a ciphertext -- form block 0 of a
+// ciphertext batch -- lives in Cl(DeltaK), the c2 half in Cl(Delta).  A launch over a ciphertext batch of a compact context
+// carries bits(|DeltaK|) in the high half of its `dbits` argument and the group of DeltaK right behind the group of
+// Delta in device memory; every other launch passes a plain `dbits` (high half zero) and the group it means.
+// Returns true when form block `y` is served by the second group (the caller then advances its group pointer by one).
+QF_HD bool gs_pick(int &dbits, unsigned y) {
+  const int k = dbits >> 16;
+  dbits &= 0xffff;
+  if (k && y == 0) { dbits = k; return true; }
+  return false;
+}
+
 QF_HD int clz32(u32 x) {
 #if defined(__CUDA_ARCH__)
   return __clz((int)x);

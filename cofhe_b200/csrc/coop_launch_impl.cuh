@@ -24,6 +24,7 @@ template <int T, int L, int N, int CAP, bool DUPL, int MB>
 __global__ void __launch_bounds__(kCoopBlock, MB) k_coop_compose(int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
                                                                              int neg2, u32 *bail, int *nbail) {
   constexpr int GPB = kCoopBlock / T, SW = CgScratch<T, L>::words;
+  gs_pick(dbits, blockIdx.y);  // compact variant: form block 0 (c1) lives in Cl(DeltaK)
   __shared__ u32 scr[GPB * SW];
   Grp<T> g = make_group<T>(scr, SW);
   size_t idx = (size_t)blockIdx.x * GPB + threadIdx.x / T;
@@ -43,6 +44,7 @@ __global__ void __launch_bounds__(kCoopBlock, MB) k_coop_pow(int dbits, int nc, 
                                                            int per_elem, const unsigned char *expneg, int shared_neg, u32 *tab, u32 *bail,
                                                            int *nbail) {
   constexpr int GPB = kCoopBlock / T, SW = CgScratch<T, L>::words, NT = (1 << kCoopPowW) - 1;
+  gs_pick(dbits, blockIdx.y);
   __shared__ u32 scr[GPB * SW];
   Grp<T> g = make_group<T>(scr, SW);
   size_t idx = (size_t)blockIdx.x * GPB + threadIdx.x / T;

@@ -11,6 +11,7 @@ namespace cofhe {
 template <int N, int CAP, bool DUPL>
 __global__ void __launch_bounds__(kBlock, 4) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
                                                          int neg2, u32 *bail, int *nbail) {
+  if (gs_pick(dbits, blockIdx.y)) G += 1;  // compact variant: form block 0 (c1) lives in Cl(DeltaK)
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   // threads past the end stay in the kernel (the composition contains block barriers); they redo the last element
   bool live = idx < n;
@@ -48,6 +49,7 @@ __global__ void __launch_bounds__(kPowBlock) k_fast_pow(const Group<CAP> *G, int
                                                         const u32 *exp, int el, int per_elem, const unsigned char *expneg,
                                                         int shared_neg, u32 *bail, int *nbail) {
   constexpr int W = 4;
+  if (gs_pick(dbits, blockIdx.y)) G += 1;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   // threads past the end stay in the kernel (fr_pow contains block barriers); they redo the last element and store nothing
   bool live = idx < n;

@@ -29,7 +29,14 @@ struct cofhe_b200_ctx {
   int cap;            // capacity class of the generic integer layer
   u32 na, nc, nd, dbits;
   u32 h_absd[2 * 216];  // |Delta| (host copy)
-  void *d_group;      // Group<CAP> in device memory
+  void *d_group;      // Group<CAP>[2] in device memory: the group of Delta, then the group of DeltaK (compact variant)
+  // compact variant (cofhe_b200_set_compact): c1 halves, h and pk live in Cl(DeltaK); stored in the same limb rows
+  int compact;
+  u32 dbitsK;
+  void *d_groupK;     // = &((Group<CAP>*)d_group)[1]
+  int gforce;         // > 0: the launches issued right now run entirely in Cl(DeltaK) (UseK)
+  unsigned char *d_lift = nullptr;  // chi flags of cofhe_b200_lift, one byte per element
+  size_t lift_bytes = 0;
   int *d_err;         // sticky per-context element status (max of Err codes)
   cudaStream_t xfer;  // internal stream of the _host entry points
   uint64_t launches;
@@ -106,19 +113,19 @@ inline unsigned grid_for(size_t n) { return (unsigned)((n + kBlock - 1) / kBlock
 // grid.y selects the form block inside a ciphertext batch (0: c1, 1: c2); plain form batches use grid.y == 1
 template <int CAP>
 __global__ void __launch_bounds__(kBlock) k_compose(const Group<CAP> *G, Shape s, size_t n, const u32 *in1, const u32 *in2,
-                                                    u32 *out, int neg2, int *err) {
+                                                    u32 *out, int neg2, int *err, int alt) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   size_t off = (size_t)blockIdx.y * form_limbs(s) * n;
-  int c = op_compose<CAP>(*G, s, n, idx, in1 + off, in2 + off, out + off, neg2 != 0);
+  int c = op_compose<CAP>(G[blockIdx.y == 0 ? alt : 0], s, n, idx, in1 + off, in2 + off, out + off, neg2 != 0);
   if (c) atomicMax(err, c);
 }
 template <int CAP>
-__global__ void __launch_bounds__(kBlock) k_square(const Group<CAP> *G, Shape s, size_t n, const u32 *in, u32 *out, int *err) {
+__global__ void __launch_bounds__(kBlock) k_square(const Group<CAP> *G, Shape s, size_t n, const u32 *in, u32 *out, int *err, int alt) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   size_t off = (size_t)blockIdx.y * form_limbs(s) * n;
-  int c = op_square<CAP>(*G, s, n, idx, in + off, out + off);
+  int c = op_square<CAP>(G[blockIdx.y == 0 ? alt : 0], s, n, idx, in + off, out + off);
   if (c) atomicMax(err, c);
 }
 template <int CAP>
@@ -131,11 +138,11 @@ __global__ void __launch_bounds__(kBlock) k_reduce(const Group<CAP> *G, Shape si
 }
 template <int CAP>
 __global__ void __launch_bounds__(kBlock) k_pow(const Group<CAP> *G, Shape s, size_t n, const u32 *in, u32 *out, const u32 *exp,
-                                                int el, int per_elem, const unsigned char *expneg, int shared_neg, int *err) {
+                                                int el, int per_elem, const unsigned char *expneg, int shared_neg, int *err, int alt) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   size_t off = (size_t)blockIdx.y * form_limbs(s) * n;
-  int c = op_pow<CAP>(*G, s, n, idx, in + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
+  int c = op_pow<CAP>(G[blockIdx.y == 0 ? alt : 0], s, n, idx, in + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
   if (c) atomicMax(err, c);
 }
 
@@ -146,16 +153,17 @@ template <int CAP>
 __global__ void __launch_bounds__(kBlock) k_redo(const Group<CAP> *G, Shape s, size_t n, int op, const u32 *in1, const u32 *in2,
                                                  u32 *out, int neg2, const u32 *exp, int el, int per_elem,
                                                  const unsigned char *expneg, int shared_neg, const u32 *bail, const int *nbail,
-                                                 int *nbail_next, int *err) {
+                                                 int *nbail_next, int *err, int alt) {
   int cnt = *nbail;
   if (blockIdx.x == 0 && threadIdx.x == 0) *nbail_next = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += gridDim.x * blockDim.x) {
     u32 e = bail[i];
     size_t y = e / n, idx = e % n, off = y * form_limbs(s) * n;
     int c;
-    if (op == 0) c = op_compose<CAP>(*G, s, n, idx, in1 + off, in2 + off, out + off, (neg2 & 1) != 0, (neg2 & 2) != 0);
-    else if (op == 1) c = op_square<CAP>(*G, s, n, idx, in1 + off, out + off);
-    else c = op_pow<CAP>(*G, s, n, idx, in1 + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
+    const Group<CAP> &Gy = G[y == 0 ? alt : 0];
+    if (op == 0) c = op_compose<CAP>(Gy, s, n, idx, in1 + off, in2 + off, out + off, (neg2 & 1) != 0, (neg2 & 2) != 0);
+    else if (op == 1) c = op_square<CAP>(Gy, s, n, idx, in1 + off, out + off);
+    else c = op_pow<CAP>(Gy, s, n, idx, in1 + off, out + off, exp, el, per_elem != 0, expneg, shared_neg != 0);
     if (c) atomicMax(err, c);
   }
 }
@@ -217,6 +225,21 @@ bool use_coop(const cofhe_b200_ctx *ctx) {
   return ctx->opt.coop == 1 || !ctx->fastn;
 }
 
+// Which class group serves the form blocks of a launch (compact variant: bn.cuh gs_pick).  G / dbits: what the register
+// and cooperative kernels receive; alt: what the generic kernels receive (index of the group serving form block 0).
+struct GSel { const void *G; int dbits; int alt; };
+GSel gsel(const cofhe_b200_ctx *ctx, unsigned ny) {
+  if (ctx->compact && ctx->gforce) return GSel{ctx->d_groupK, (int)ctx->dbitsK, 0};
+  if (ctx->compact && ny == 2) return GSel{ctx->d_group, (int)(ctx->dbits | (ctx->dbitsK << 16)), 1};
+  return GSel{ctx->d_group, (int)ctx->dbits, 0};
+}
+// the launches issued while one of these lives run entirely in Cl(DeltaK) (no effect outside the compact variant)
+struct UseK {
+  cofhe_b200_ctx *c;
+  explicit UseK(cofhe_b200_ctx *ctx) : c(ctx) { c->gforce++; }
+  ~UseK() { c->gforce--; }
+};
+
 int ensure_bail(cofhe_b200_ctx *ctx, size_t entries) {
   if (entries >> 32) return COFHE_B200_EINVAL;
   if (entries <= ctx->bail_cap) return COFHE_B200_OK;
@@ -244,6 +267,25 @@ __global__ void __launch_bounds__(kBlock) k_dlog(const Group<CAP> *G, const Sche
   int c = op_dlog<KL, CAP>(*G, *S, s, n, idx, in, out, ml);
   if (c) atomicMax(err, c);
 }
+// ---- compact variant: Cl(DeltaK) -> Cl(Delta) (CL_HSM2k::from_Cl_DeltaK_to_Cl_Delta, CL_HSM2k.inl:458-474): step 1 and
+// step 3 as kernels around scheme_ops.cuh's per-element bodies; step 2 (f^(2^k)) runs on the exponentiation kernels
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_lift_2exp(Shape s, size_t n, int k, const u32 *in, u32 *out, unsigned char *chi, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  int c = op_lift_2exp<CAP>(s, n, idx, k, in, out, chi);
+  if (c) atomicMax(err, c);
+}
+template <int CAP>
+__global__ void __launch_bounds__(kBlock) k_lift_fix(const Group<CAP> *G, const Scheme<CAP> *S, Shape s, size_t n, u32 *io,
+                                                     const unsigned char *chi, int *err) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  if (!chi[idx]) return;
+  int c = op_lift_fix<CAP>(*G, *S, s, n, idx, io);
+  if (c) atomicMax(err, c);
+}
+
 // out[row][idx] = in[row][0] for `rows` limb rows
 __global__ void k_bcast(size_t n, int rows, const u32 *in, u32 *out) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -307,12 +349,13 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   Shape s{(int)ctx->na, (int)ctx->nc};
   dim3 grid(grid_for(n), ny);
   const bool coop = use_coop(ctx) && !(neg2 & 2);
+  const GSel gs = gsel(ctx, ny);
   if (!ctx->fastn && !coop) {
     CAP_DISPATCH(ctx->cap, {
-      const Group<CAP> *G = (const Group<CAP> *)ctx->d_group;
-      if (op == 0) k_compose<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, in2, out, neg2 & 1, ctx->d_err);
-      else if (op == 1) k_square<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, ctx->d_err);
-      else k_pow<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_err);
+      const Group<CAP> *G = (const Group<CAP> *)gs.G;
+      if (op == 0) k_compose<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, in2, out, neg2 & 1, ctx->d_err, gs.alt);
+      else if (op == 1) k_square<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, ctx->d_err, gs.alt);
+      else k_pow<CAP><<<grid, kBlock, 0, st>>>(G, s, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_err, gs.alt);
     })
     return check_launch(ctx);
   }
@@ -320,11 +363,11 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   if (rc != COFHE_B200_OK) return rc;
   int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
   ctx->flip ^= 1;
-  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  int dbits = gs.dbits, nc = (int)ctx->nc;
   if (coop) {
     COOP_DISPATCH(ctx->coopn, {
       typedef CoopKernels<CT, CL, CN, CCAP> K;
-      if (op < 2) K::compose(op == 1, ny, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+      if (op < 2) K::compose(op == 1, ny, st, gs.G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
       else {
         size_t tw = K::pow_tab_words(ny, nc, n) * sizeof(u32);
         if (tw > ctx->powtab_bytes) {
@@ -340,16 +383,16 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
     const int pb = pick_block((size_t)ny * n, ctx->sms);
     FAST_DISPATCH(ctx->fastn, {
       typedef FastKernels<FN, FCAP> K;
-      if (op < 2) K::compose(op == 1, grid, st, ctx->d_group, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
-      else K::pow(dim3((unsigned)((n + pb - 1) / pb), ny), pb, st, ctx->d_group, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
+      if (op < 2) K::compose(op == 1, grid, st, gs.G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt);
+      else K::pow(dim3((unsigned)((n + pb - 1) / pb), ny), pb, st, gs.G, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
                   shared_neg, ctx->d_bail, cnt);
     })
   }
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
   unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
-  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, op, in1, in2, out, neg2, exp, el,
-                                                          per_elem, expneg, shared_neg, ctx->d_bail, cnt, cnt_next, ctx->d_err))
+  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)gs.G, s, n, op, in1, in2, out, neg2, exp, el,
+                                                          per_elem, expneg, shared_neg, ctx->d_bail, cnt, cnt_next, ctx->d_err, gs.alt))
   return check_launch(ctx);
 }
 
@@ -364,14 +407,15 @@ size_t mm_part_words(const cofhe_b200_ctx *ctx, const MMShape &s) {
 }
 // window tables of the n*m base ciphertexts `ct` into tab (fast tiers only)
 int mm_tables(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, u32 *tab, cudaStream_t st) {
-  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  const GSel gs = gsel(ctx, 2);
+  int dbits = gs.dbits, nc = (int)ctx->nc;
   size_t nb = (size_t)s.n * s.m;
   FAST_DISPATCH(ctx->fastn, {
     typedef FastKernels<FN, FCAP> K;
     const int b1 = pick_block(2 * nb, ctx->sms), b2 = pick_block(2 * nb * s.nwin, ctx->sms);
-    K::mm_chain(dim3((unsigned)((nb + b1 - 1) / b1), 2), b1, st, ctx->d_group, dbits, nc, s, ct, tab);
+    K::mm_chain(dim3((unsigned)((nb + b1 - 1) / b1), 2), b1, st, gs.G, dbits, nc, s, ct, tab);
     ctx->launches++;
-    K::mm_fill(dim3((unsigned)((nb * s.nwin + b2 - 1) / b2), 2), b2, st, ctx->d_group, dbits, s, tab);
+    K::mm_fill(dim3((unsigned)((nb * s.nwin + b2 - 1) / b2), 2), b2, st, gs.G, dbits, s, tab);
   })
   return check_launch(ctx);
 }
@@ -382,17 +426,18 @@ int mm_eval(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *sca
   size_t no = (size_t)s.n * s.p;
   int rc = ensure_bail(ctx, 2 * no);
   if (rc != COFHE_B200_OK) return rc;
-  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  const GSel gs = gsel(ctx, 2);
+  int dbits = gs.dbits, nc = (int)ctx->nc;
   int *cnt = ctx->d_nbail + ctx->flip, *cnt_next = ctx->d_nbail + (ctx->flip ^ 1);
   ctx->flip ^= 1;
   FAST_DISPATCH(ctx->fastn, {
     typedef FastKernels<FN, FCAP> K;
     const int ba = s.block ? s.block : pick_block(2 * no * s.chunks, ctx->sms), bf = pick_block(2 * no, ctx->sms);
-    K::mm_accum(dim3((unsigned)((no + ba - 1) / ba), 2, s.chunks), ba, st, ctx->d_group, dbits, s, scal, tab, part);
+    K::mm_accum(dim3((unsigned)((no + ba - 1) / ba), 2, s.chunks), ba, st, gs.G, dbits, s, scal, tab, part);
     ctx->launches++;
-    K::mm_final(dim3((unsigned)((no + bf - 1) / bf), 2), bf, st, ctx->d_group, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
+    K::mm_final(dim3((unsigned)((no + bf - 1) / bf), 2), bf, st, gs.G, dbits, nc, s, init, part, out, ctx->d_bail, cnt);
     ctx->launches++;
-    k_mm_robust<FCAP><<<32, 128, 0, st>>>((const Group<FCAP> *)ctx->d_group, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err);
+    k_mm_robust<FCAP><<<32, 128, 0, st>>>((const Group<FCAP> *)gs.G, sh, s, ct, scal, init, out, ctx->d_bail, cnt, cnt_next, ctx->d_err, gs.alt);
   })
   return check_launch(ctx);
 }
@@ -400,8 +445,9 @@ int mm_robust_all(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u3
   Shape sh{(int)ctx->na, (int)ctx->nc};
   size_t no = (size_t)s.n * s.p;
   unsigned blocks = (unsigned)((2 * no + 127) / 128);
-  CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, 128, 0, st>>>((const Group<CAP> *)ctx->d_group, sh, s, ct, scal, init, out,
-                                                                     nullptr, nullptr, nullptr, ctx->d_err))
+  const GSel gs = gsel(ctx, 2);
+  CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<blocks, 128, 0, st>>>((const Group<CAP> *)gs.G, sh, s, ct, scal, init, out,
+                                                                     nullptr, nullptr, nullptr, ctx->d_err, gs.alt))
   return check_launch(ctx);
 }
 
@@ -409,6 +455,7 @@ int mm_robust_all(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u3
 int fb_pow(cofhe_b200_ctx *ctx, size_t n, const u32 *exps, u32 el, u32 *out, u32 *part, cudaStream_t st) {
   MMShape s = ctx->fb;
   if ((int)el > s.el) return COFHE_B200_EINVAL;  // exponent wider than the tables were built for
+  UseK in_cl_g(ctx);  // compact variant: h and pk are elements of Cl(DeltaK) (CL_HSM2k.inl:76-80, Cl_G :255)
   s.p = (unsigned)n;
   s.el = (int)el;
   if (!ctx->fastn && use_coop(ctx)) {
@@ -421,6 +468,35 @@ int fb_pow(cofhe_b200_ctx *ctx, size_t n, const u32 *exps, u32 el, u32 *out, u32
   }
   if (!ctx->fastn) return mm_robust_all(ctx, s, ctx->d_fb_bases, exps, nullptr, out, st);
   return mm_eval(ctx, s, ctx->d_fb_bases, exps, nullptr, out, ctx->d_fb_tab, part, st);
+}
+
+// forms of Cl(DeltaK) -> Cl(Delta), batched, in place allowed (compact variant only; the caller holds the context)
+int lift_forms(cofhe_b200_ctx *ctx, size_t n, const u32 *in, u32 *out, cudaStream_t st) {
+  if (!ctx->compact || !ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n > ctx->lift_bytes) {
+    if (ctx->d_lift) cudaFree(ctx->d_lift);
+    ctx->d_lift = nullptr; ctx->lift_bytes = 0;
+    if (cudaMalloc(&ctx->d_lift, n) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+    ctx->lift_bytes = n;
+  }
+  Shape s{(int)ctx->na, (int)ctx->nc};
+  CAP_DISPATCH(ctx->cap, k_lift_2exp<CAP><<<grid_for(n), kBlock, 0, st>>>(s, n, ctx->k, in, out, ctx->d_lift, ctx->d_err))
+  int rc = check_launch(ctx);
+  if (rc != COFHE_B200_OK) return rc;
+  // raise_to_power_M (CL_HSM2k.inl:641-648: k squarings in Cl(Delta)) as one exponentiation by 2^k
+  u32 e2k[64];
+  const int el = ctx->k / 32 + 1;
+  for (int i = 0; i < el; i++) e2k[i] = 0;
+  e2k[ctx->k / 32] = 1u << (ctx->k & 31);
+  if (cudaMemcpyAsync(ctx->d_exp + 64, e2k, el * sizeof(u32), cudaMemcpyHostToDevice, st) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ECUDA; }
+  const int force = ctx->gforce;
+  ctx->gforce = 0;  // this step runs in Cl(Delta) whatever the caller is in the middle of
+  rc = launch_op(ctx, 2, 1, n, out, out, out, 0, ctx->d_exp + 64, el, 0, nullptr, 0, st);
+  ctx->gforce = force;
+  if (rc != COFHE_B200_OK) return rc;
+  CAP_DISPATCH(ctx->cap, k_lift_fix<CAP><<<grid_for(n), kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, (const Scheme<CAP> *)ctx->d_scheme,
+                                                                      s, n, out, ctx->d_lift, ctx->d_err))
+  return check_launch(ctx);
 }
 
 struct DevGuard {
@@ -543,7 +619,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->d_tmp = nullptr; ctx->tmp_bytes = 0;
   ctx->d_scheme = nullptr; ctx->k = 0; ctx->kl = 0; ctx->d_exp = nullptr;
   ctx->d_fb_bases = nullptr; ctx->d_fb_tab = nullptr; ctx->fb_set = 0;
-  ctx->d_group = nullptr;
+  ctx->d_group = nullptr; ctx->d_groupK = nullptr; ctx->compact = 0; ctx->dbitsK = 0; ctx->gforce = 0;
   ctx->d_err = nullptr;
   ctx->xfer = nullptr;
   int rc = COFHE_B200_OK;
@@ -554,15 +630,18 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
     G->absD.n = (int)n; G->absD.neg = 0;
     for (u32 i = 0; i < n; i++) G->absD.d[i] = abs_delta[i];
     G->dbits = dbits;
-    if (cudaMalloc(&ctx->d_group, sizeof(*G)) != cudaSuccess ||
-        cudaMemcpy(ctx->d_group, G, sizeof(*G), cudaMemcpyHostToDevice) != cudaSuccess)
+    // two groups back to back: Delta, then DeltaK (a copy of the first until cofhe_b200_set_compact)
+    if (cudaMalloc(&ctx->d_group, 2 * sizeof(*G)) != cudaSuccess ||
+        cudaMemcpy(ctx->d_group, G, sizeof(*G), cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy((char *)ctx->d_group + sizeof(*G), G, sizeof(*G), cudaMemcpyHostToDevice) != cudaSuccess)
       rc = COFHE_B200_ECUDA;
+    ctx->d_groupK = ctx->d_group ? (void *)((char *)ctx->d_group + sizeof(*G)) : nullptr;
     delete G;
   })
   if (rc == COFHE_B200_OK && (cudaMalloc(&ctx->d_err, sizeof(int)) != cudaSuccess ||
                               cudaMemset(ctx->d_err, 0, sizeof(int)) != cudaSuccess ||
                               cudaMalloc(&ctx->d_nbail, 2 * sizeof(int)) != cudaSuccess ||
-                              cudaMalloc(&ctx->d_exp, 64 * sizeof(u32)) != cudaSuccess ||
+                              cudaMalloc(&ctx->d_exp, 128 * sizeof(u32)) != cudaSuccess ||
                               cudaMemset(ctx->d_nbail, 0, 2 * sizeof(int)) != cudaSuccess ||
                               cudaEventCreateWithFlags(&ctx->order, cudaEventDisableTiming) != cudaSuccess ||
                               cudaStreamCreateWithFlags(&ctx->xfer, cudaStreamNonBlocking) != cudaSuccess))
@@ -584,6 +663,7 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_work) cudaFree(ctx->d_work);
   if (ctx->d_tmp) cudaFree(ctx->d_tmp);
   if (ctx->d_powtab) cudaFree(ctx->d_powtab);
+  if (ctx->d_lift) cudaFree(ctx->d_lift);
   if (ctx->d_scheme) cudaFree(ctx->d_scheme);
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
@@ -706,29 +786,30 @@ int cofhe_b200_add_ciphertexts_static(cofhe_b200_ctx *ctx, size_t n, const uint3
   Shape s{(int)ctx->na, (int)ctx->nc};
   dim3 grid(grid_for(n), ny);
   const bool coop = use_coop(ctx);
+  const GSel gs = gsel(ctx, ny);
   if (!ctx->fastn && !coop) {  // the generic kernel keeps no list
-    CAP_DISPATCH(ctx->cap, k_compose<CAP><<<grid, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, ct1, ct2, out, 0, ctx->d_err))
+    CAP_DISPATCH(ctx->cap, k_compose<CAP><<<grid, kBlock, 0, st>>>((const Group<CAP> *)gs.G, s, n, ct1, ct2, out, 0, ctx->d_err, gs.alt))
     return check_launch(ctx);
   }
   // the array keeps what the previous call left: the counters start every call at zero
   if (cudaMemsetAsync(scr, 0, 64 * sizeof(u32), st) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ECUDA; }
-  int dbits = (int)ctx->dbits, nc = (int)ctx->nc;
+  int dbits = gs.dbits, nc = (int)ctx->nc;
   if (coop) {
     COOP_DISPATCH(ctx->coopn, {
       typedef CoopKernels<CT, CL, CN, CCAP> K;
-      K::compose(false, ny, st, ctx->d_group, dbits, nc, n, ct1, ct2, out, 0, bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+      K::compose(false, ny, st, gs.G, dbits, nc, n, ct1, ct2, out, 0, bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
     })
   } else {
     FAST_DISPATCH(ctx->fastn, {
       typedef FastKernels<FN, FCAP> K;
-      K::compose(false, grid, st, ctx->d_group, dbits, nc, n, ct1, ct2, out, 0, bail, cnt);
+      K::compose(false, grid, st, gs.G, dbits, nc, n, ct1, ct2, out, 0, bail, cnt);
     })
   }
   rc = check_launch(ctx);
   if (rc != COFHE_B200_OK) return rc;
   unsigned rb = (unsigned)((size_t)ny * n < 4096 ? ((size_t)ny * n + kBlock - 1) / kBlock : 32);
-  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)ctx->d_group, s, n, 0, ct1, ct2, out, 0, nullptr, 0, 0,
-                                                          nullptr, 0, bail, cnt, cnt_next, ctx->d_err))
+  CAP_DISPATCH(ctx->cap, k_redo<CAP><<<rb, kBlock, 0, st>>>((const Group<CAP> *)gs.G, s, n, 0, ct1, ct2, out, 0, nullptr, 0, 0,
+                                                          nullptr, 0, bail, cnt, cnt_next, ctx->d_err, gs.alt))
   return check_launch(ctx);
 }
 
@@ -868,6 +949,41 @@ int cofhe_b200_dlog(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *
   return check_launch(ctx);
 }
 
+int cofhe_b200_set_compact(cofhe_b200_ctx *ctx, int on) {
+  if (!ctx) return COFHE_B200_EINVAL;
+  if (!ctx->d_scheme) return COFHE_B200_ESTATE;  // DeltaK = -8N comes from set_scheme
+  EnterHost g(ctx);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  int rc = COFHE_B200_OK;
+  CAP_DISPATCH(ctx->cap, {
+    Scheme<CAP> *S = new (std::nothrow) Scheme<CAP>();
+    Group<CAP> *G = new (std::nothrow) Group<CAP>();
+    if (!S || !G) { delete S; delete G; return COFHE_B200_ENOMEM; }
+    memset(G, 0, sizeof(*G));
+    if (cudaMemcpy(S, ctx->d_scheme, sizeof(*S), cudaMemcpyDeviceToHost) != cudaSuccess) rc = COFHE_B200_ECUDA;
+    if (rc == COFHE_B200_OK) {
+      G->absD = S->absDK;
+      G->dbits = z_bits(S->absDK);
+      if (cudaMemcpy(ctx->d_groupK, G, sizeof(*G), cudaMemcpyHostToDevice) != cudaSuccess) rc = COFHE_B200_ECUDA;
+      ctx->dbitsK = (u32)G->dbits;
+    }
+    delete S; delete G;
+  })
+  if (rc != COFHE_B200_OK) return rc;
+  ctx->compact = on ? 1 : 0;
+  ctx->fb_set = 0;  // h and pk change groups with the variant: the tables must be rebuilt (cofhe_b200_set_bases)
+  return COFHE_B200_OK;
+}
+
+int cofhe_b200_lift(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *out, void *stream) {
+  if (!ctx || (n && (!f || !out))) return COFHE_B200_EINVAL;
+  if (!ctx->compact || !ctx->d_scheme) return COFHE_B200_ESTATE;
+  if (n == 0) return COFHE_B200_OK;
+  Enter g(ctx, (cudaStream_t)stream);
+  if (!g.ok) return COFHE_B200_ECUDA;
+  return lift_forms(ctx, n, f, out, (cudaStream_t)stream);
+}
+
 int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t *pk, uint32_t ebits) {
   if (!ctx || !h || ebits == 0) return COFHE_B200_EINVAL;
   EnterHost g(ctx);
@@ -888,7 +1004,11 @@ int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t 
   if (!ctx->fastn) return COFHE_B200_OK;
   if (ctx->d_fb_tab) { cudaFree(ctx->d_fb_tab); ctx->d_fb_tab = nullptr; }
   if (cudaMalloc(&ctx->d_fb_tab, mm_tab_words(ctx, s) * sizeof(u32)) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
-  int rc = mm_tables(ctx, s, ctx->d_fb_bases, ctx->d_fb_tab, ctx->xfer);
+  int rc;
+  {
+    UseK in_cl_g(ctx);  // compact variant: h and pk are elements of Cl(DeltaK)
+    rc = mm_tables(ctx, s, ctx->d_fb_bases, ctx->d_fb_tab, ctx->xfer);
+  }
   if (rc != COFHE_B200_OK) return rc;
   return cofhe_b200_status(ctx, ctx->xfer);
 }
@@ -994,10 +1114,15 @@ int cofhe_b200_encrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *m, uint32_
   if (shared_r) {
     rc = fb_pow(ctx, 1, r, el, one, part, st);
     if (rc != COFHE_B200_OK) return rc;
+    if (ctx->compact) {  // pk^r from Cl(DeltaK) into Cl(Delta) (CL_HSM_utils.inl:178-179, cpu_cryptosystem_tensor_ops.inl:11-12)
+      rc = lift_forms(ctx, 1, one + fl, one + fl, st);
+      if (rc != COFHE_B200_OK) return rc;
+    }
     k_bcast<<<grid_for(n), kBlock, 0, st>>>(n, (int)(2 * fl), one, out);
     rc = check_launch(ctx);
   } else {
     rc = fb_pow(ctx, n, r, el, out, part, st);
+    if (rc == COFHE_B200_OK && ctx->compact) rc = lift_forms(ctx, n, out + fl * n, out + fl * n, st);
   }
   if (rc != COFHE_B200_OK) return rc;
   rc = cofhe_b200_power_of_f(ctx, n, m, ml, fm, stream);
@@ -1027,10 +1152,15 @@ int cofhe_b200_rerandomize(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, co
   if (shared_r) {
     rc = fb_pow(ctx, 1, r, el, one, part, st);
     if (rc != COFHE_B200_OK) return rc;
+    if (ctx->compact) {  // CL_HSM_utils.inl:204-205, 235-236
+      rc = lift_forms(ctx, 1, one + fl, one + fl, st);
+      if (rc != COFHE_B200_OK) return rc;
+    }
     k_bcast<<<grid_for(n), kBlock, 0, st>>>(n, (int)(2 * fl), one, hr);
     rc = check_launch(ctx);
   } else {
     rc = fb_pow(ctx, n, r, el, hr, part, st);
+    if (rc == COFHE_B200_OK && ctx->compact) rc = lift_forms(ctx, n, hr + fl * n, hr + fl * n, st);
   }
   if (rc != COFHE_B200_OK) return rc;
   return launch_op(ctx, 0, 2, n, ct, hr, out, 0, nullptr, 0, 0, nullptr, 0, st);
@@ -1252,7 +1382,15 @@ int cofhe_b200_part_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, c
   if (!g.ok) return COFHE_B200_ECUDA;
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaMemcpyAsync(ctx->d_exp, share, el * sizeof(u32), cudaMemcpyHostToDevice, st));
-  return launch_op(ctx, 2, 1, n, ct, ct, out, 0, ctx->d_exp, (int)el, 0, nullptr, share_neg, st);
+  if (!ctx->compact) return launch_op(ctx, 2, 1, n, ct, ct, out, 0, ctx->d_exp, (int)el, 0, nullptr, share_neg, st);
+  // compact variant: c1^share in Cl(DeltaK), then into Cl(Delta) (cpu_cryptosystem_distributed.inl:249-251)
+  int rc;
+  {
+    UseK in_cl_g(ctx);
+    rc = launch_op(ctx, 2, 1, n, ct, ct, out, 0, ctx->d_exp, (int)el, 0, nullptr, share_neg, st);
+  }
+  if (rc != COFHE_B200_OK) return rc;
+  return lift_forms(ctx, n, out, out, st);
 }
 
 int cofhe_b200_combine(cofhe_b200_ctx *ctx, size_t n, uint32_t t, const uint32_t *ct, const uint32_t *ds, uint32_t *m, uint32_t ml,
@@ -1293,7 +1431,11 @@ int cofhe_b200_decrypt(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct, const 
   if (rc != COFHE_B200_OK) return rc;
   u32 *x = ctx->d_tmp, *r = x + fl * n;
   CUDA_TRY(cudaMemcpyAsync(ctx->d_exp, sk, el * sizeof(u32), cudaMemcpyHostToDevice, st));
-  rc = launch_op(ctx, 2, 1, n, ct, ct, x, 0, ctx->d_exp, (int)el, 0, nullptr, 0, st);   // c1^sk
+  {
+    UseK in_cl_g(ctx);  // no effect outside the compact variant
+    rc = launch_op(ctx, 2, 1, n, ct, ct, x, 0, ctx->d_exp, (int)el, 0, nullptr, 0, st);   // c1^sk
+  }
+  if (rc == COFHE_B200_OK && ctx->compact) rc = lift_forms(ctx, n, x, x, st);            // CL_HSM_utils.inl:132-133
   if (rc != COFHE_B200_OK) return rc;
   rc = launch_op(ctx, 0, 1, n, ct + fl * n, x, r, 1, nullptr, 0, 0, nullptr, 0, st);     // c2 o (c1^sk)^-1
   if (rc != COFHE_B200_OK) return rc;
@@ -1528,6 +1670,7 @@ extern "C" {
 int cofhe_b200_add_ciphertexts_host(cofhe_b200_ctx *ctx, size_t n, const uint32_t *ct1, const uint32_t *ct2,
                                     uint32_t *out) {
   if (!ctx || (n && (!ct1 || !ct2 || !out))) return COFHE_B200_EINVAL;
+  if (ctx->compact) return COFHE_B200_ESTATE;  // compact variant: use upload + cofhe_b200_add_ciphertexts + download
   if (n == 0) return COFHE_B200_OK;
   EnterHost g(ctx);
   if (!g.ok) return COFHE_B200_ECUDA;

@@ -51,6 +51,7 @@ QF_HD void mm_store(u32 *t, const FormR<N> &f) {
 template <int N, int CAP>
 __global__ void __launch_bounds__(kMMBlock) k_mm_chain(const Group<CAP> *G, int dbits, int nc, MMShape s, const u32 *ct, u32 *tab) {
   constexpr int TE = MMLayout<N>::TE;
+  if (gs_pick(dbits, blockIdx.y)) G += 1;  // compact variant: form block 0 (c1) lives in Cl(DeltaK)
   size_t nb = (size_t)s.n * s.m;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool live = idx < nb;  // threads past the end idle inside the loop (block barriers)
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_chain(const Group<CAP> *G, int 
 template <int N, int CAP>
 __global__ void __launch_bounds__(kMMBlock) k_mm_fill(const Group<CAP> *G, int dbits, MMShape s, u32 *tab) {
   constexpr int TE = MMLayout<N>::TE;
+  if (gs_pick(dbits, blockIdx.y)) G += 1;
   size_t total = (size_t)s.n * s.m * s.nwin;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool live = idx < total;
@@ -104,6 +106,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_fill(const Group<CAP> *G, int d
 template <int N, int CAP>
 __global__ void __launch_bounds__(kMMBlock) k_mm_accum(const Group<CAP> *G, int dbits, MMShape s, const u32 *scal, const u32 *tab, u32 *part) {
   constexpr int TE = MMLayout<N>::TE;
+  if (gs_pick(dbits, blockIdx.y)) G += 1;
   size_t no = (size_t)s.n * s.p;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool live = idx < no;
@@ -143,6 +146,7 @@ template <int N, int CAP>
 __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int dbits, int nc, MMShape s, const u32 *init, const u32 *part, u32 *out,
                                                        u32 *bail, int *nbail) {
   constexpr int TE = MMLayout<N>::TE;
+  if (gs_pick(dbits, blockIdx.y)) G += 1;
   size_t no = (size_t)s.n * s.p;
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool live = idx < no;
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(kMMBlock) k_mm_final(const Group<CAP> *G, int 
 template <int CAP>
 __global__ void __launch_bounds__(128) k_mm_robust(const Group<CAP> *G, Shape sh, MMShape s, const u32 *ct, const u32 *scal,
                                                         const u32 *init, u32 *out, const u32 *bail, const int *nbail,
-                                                        int *nbail_next, int *err) {
+                                                        int *nbail_next, int *err, int alt) {
   size_t no = (size_t)s.n * s.p, nb = (size_t)s.n * s.m;
   size_t cnt = bail ? (size_t)*nbail : 2 * no;
   if (nbail_next && blockIdx.x == 0 && threadIdx.x == 0) *nbail_next = 0;
@@ -189,16 +193,17 @@ __global__ void __launch_bounds__(128) k_mm_robust(const Group<CAP> *G, Shape sh
     unsigned i = (unsigned)(idx / s.p), k = (unsigned)(idx % s.p);
     Err er; er.code = 0;
     Form<CAP> acc, f, t;
+    const Group<CAP> &Gy = G[y == 0 ? alt : 0];  // compact variant: form block 0 (c1) lives in Cl(DeltaK)
     if (init) form_load(er, acc, init + y * form_limbs(sh), sh, 1, 0);
-    else qf_identity(er, *G, acc);
+    else qf_identity(er, Gy, acc);
     for (unsigned j = 0; j < s.m && !er.code; j++) {
       const u32 *ex = scal + (size_t)j * s.p + k;
       bool zero = true;
       for (int l = 0; l < s.el; l++) zero = zero && ex[(size_t)l * s.m * s.p] == 0;
       if (zero) continue;
       form_load(er, f, ct + y * form_limbs(sh) * nb, sh, nb, (size_t)i * s.m + j);
-      qf_pow(er, *G, t, f, ex, s.el, (size_t)s.m * s.p, false);
-      qf_compose(er, *G, acc, acc, t, false, false);
+      qf_pow(er, Gy, t, f, ex, s.el, (size_t)s.m * s.p, false);
+      qf_compose(er, Gy, acc, acc, t, false, false);
     }
     form_store(er, acc, out + y * form_limbs(sh) * no, sh, no, idx);
     if (er.code) atomicMax(err, er.code);

@@ -44,4 +44,51 @@ QF_HDN int op_dlog(const Group<CAP> &G, const Scheme<CAP> &S, const Shape &s, si
   return e.code;
 }
 
+// ---- compact variant: Cl(DeltaK) -> Cl(Delta) (CL_HSM2k::from_Cl_DeltaK_to_Cl_Delta, CL_HSM2k.inl:458-474) -----------------
+// Step 1: QFI::lift_2exp(k+1) (qfi.inl:263-271) = prime_to_2exp (:590-610: make a odd), b <- b 2^(k+1), c <- c 2^(2k+2),
+// reduction; chi[idx] = 1 when a or c of the lifted reduced form is 3 mod 4 (CL_HSM2k.inl:461).
+template <int CAP>
+QF_HDN int op_lift_2exp(const Shape &s, size_t n, size_t idx, int k, const u32 *in, u32 *out, unsigned char *chi) {
+  Err e; e.code = 0;
+  Form<CAP> f;
+  form_load(e, f, in, s, n, idx);
+  if (!z_odd(f.a)) {
+    Z<CAP> t;
+    if (!z_odd(f.c)) {  // (a, b, c) -> (a + b + c, -b - 2a, a): first c <- a + b + c and b <- b + 2a, then the swap below
+      z_add(e, t, f.c, f.a);
+      z_add(e, f.c, t, f.b);
+      z_add(e, t, f.b, f.a);
+      z_add(e, f.b, t, f.a);
+    }
+    // (a, b, c) -> (c, -b, a)
+    z_neg(f.b);
+    z_copy(e, t, f.a);
+    z_copy(e, f.a, f.c);
+    z_copy(e, f.c, t);
+  }
+  z_shl(e, f.b, f.b, (unsigned)(k + 1));
+  z_shl(e, f.c, f.c, (unsigned)(2 * k + 2));
+  qf_reduce(e, f);
+  chi[idx] = (unsigned char)(((f.a.n ? f.a.d[0] & 3u : 0u) == 3u || (f.c.n ? f.c.d[0] & 3u : 0u) == 3u) ? 1 : 0);
+  form_store(e, f, out, s, n, idx);
+  return e.code;
+}
+// Step 3 (step 2 = f^(2^k), k squarings in Cl(Delta): raise_to_power_M, CL_HSM2k.inl:641-648), for the elements whose
+// chi is set: compose with g = (4, 4, 1 - DeltaK 2^(2(k-1)))  (CL_HSM2k.inl:464-473)
+template <int CAP>
+QF_HDN int op_lift_fix(const Group<CAP> &G, const Scheme<CAP> &S, const Shape &s, size_t n, size_t idx, u32 *io) {
+  Err e; e.code = 0;
+  Form<CAP> f, g;
+  form_load(e, f, io, s, n, idx);
+  z_set_u32(g.a, 4);
+  z_set_u32(g.b, 4);
+  Z<CAP> t, one;
+  z_set_u32(one, 1);
+  z_shl(e, t, S.absDK, (unsigned)(2 * (S.k - 1)));
+  z_add(e, g.c, t, one);
+  qf_compose(e, G, f, f, g, false, false);
+  form_store(e, f, io, s, n, idx);
+  return e.code;
+}
+
 }  // namespace cofhe

@@ -230,6 +230,17 @@ class ClassGroupB200:
         capi.check(self.lib.cofhe_b200_set_scheme(self.h, k, nl.ctypes.data_as(ctypes.c_void_p), nN), "set_scheme")
         self.k, self.ml = k, (k + 31) // 32
 
+    def set_compact(self, on=True):
+        """compact variant (CPUCryptoSystem(level, k, compact=true)): h, pk and the c1 halves live in Cl(DeltaK); call
+        between set_scheme and set_bases"""
+        capi.check(self.lib.cofhe_b200_set_compact(self.h, int(bool(on))), "set_compact")
+
+    def lift(self, f):
+        """forms of Cl(DeltaK) -> Cl(Delta) (CL_HSM2k::from_Cl_DeltaK_to_Cl_Delta), compact variant"""
+        out = torch.empty_like(f)
+        capi.check(self.lib.cofhe_b200_lift(self.h, f.shape[-1], _ptr(f), _ptr(out), _stream()), "lift")
+        return out
+
     def set_bases(self, h, pk, ebits):
         hl = L.forms_to_limbs([h], self.na, self.nc)[:, 0].copy()
         pl = None if pk is None else L.forms_to_limbs([pk], self.na, self.nc)[:, 0].copy()

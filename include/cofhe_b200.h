@@ -222,6 +222,20 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
  * itself -- random N, class-number bound, h -- stays on the host with the reference's RandGen).
  * Fails with COFHE_B200_EINVAL when 2^(2k+5) N is not the context's |Delta|.  Host pointers. */
 int cofhe_b200_set_scheme(cofhe_b200_ctx *ctx, uint32_t k, const uint32_t *N, uint32_t nN);
+/* The compact variant of CL_HSM2k (reference CL_HSM2k.inl:31-39, 76-80, 255: constructor argument `compact_variant`,
+ * CPUCryptoSystem(security_level, k, compact), include/x86_64/cpu_cryptosystem.hpp:33).  With on != 0 the group G of
+ * the generator is Cl(DeltaK) instead of Cl(Delta): h, pk and every c1 half are forms of discriminant DeltaK = -8N
+ * (they occupy the same limb rows of the layout, with leading zero limbs); c2 halves, f^m and part-decryption results
+ * stay in Cl(Delta).  Every ciphertext-level entry point then composes / exponentiates form block 0 in Cl(DeltaK) and
+ * form block 1 in Cl(Delta) inside the same launch; encrypt / rerandomize / part_decrypt / decrypt apply
+ * cofhe_b200_lift where the reference calls from_Cl_DeltaK_to_Cl_Delta.  Call after set_scheme and before set_bases
+ * (the tables are dropped).  cofhe_b200_add_ciphertexts_host is not available in this variant (COFHE_B200_ESTATE). */
+int cofhe_b200_set_compact(cofhe_b200_ctx *ctx, int on);
+/* out[e] = the image in Cl(Delta) of the form f[e] of Cl(DeltaK), compact variant only:
+ * CL_HSM2k::from_Cl_DeltaK_to_Cl_Delta (CL_HSM2k.inl:458-474) = QFI::lift_2exp(k+1) (qfi.inl:263-271, prime_to_2exp
+ * :590-610), k squarings in Cl(Delta) (raise_to_power_M, :641-648) and, where a or c of the lifted form is 3 mod 4,
+ * one composition with (4, 4, 1 - DeltaK 2^(2(k-1))).  Form batches of the context shape; in place allowed. */
+int cofhe_b200_lift(cofhe_b200_ctx *ctx, size_t n, const uint32_t *f, uint32_t *out, void *stream);
 /* Fixed bases for encryption: the generator h and the public key pk (host pointers to one form each, context shape;
  * pk may be NULL).  Builds their window tables on the device for exponents below 2^ebits.  Replaces the
  * precomputation of CL_HSM2k (CL_HSM2k.inl:92-102: h^(2^e), h^(2^d), h^(2^(d+e))) and of CL_HSM_PublicKey

@@ -230,13 +230,12 @@ namespace CoFHE
         using PartDecryptionResult = b200_detail::HostCS::PartDecryptionResult;
 
         // (N_bits a.k.a. security_level, k, compact): same meaning as CPUCryptoSystem (cpu_cryptosystem.hpp:33).
-        // The compact variant keeps c1 in Cl(DeltaK); the device path covers the non-compact scheme every caller
-        // of the reference uses, so compact == true is refused here instead of silently running on the host.
+        // compact == true is the compact variant of CL_HSM2k (CL_HSM2k.inl:31-39, 76-80): h, pk and every c1 live in
+        // Cl(DeltaK); the device context is switched with cofhe_b200_set_compact and every entry point below works
+        // unchanged (the c1 halves are stored in the same limb rows, with leading zero limbs).
         B200CryptoSystem(uint32_t security_level, uint32_t k, bool compact = false, int device = 0)
             : host_(security_level, k, compact), device_(device)
         {
-            if (compact)
-                throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
             open();
         }
         // several GPUs of one box behind one object: batched calls split their elements (matmul: its ct rows) into one
@@ -378,8 +377,6 @@ namespace CoFHE
         // wrap an existing reference object (used by deserialize)
         explicit B200CryptoSystem(b200_detail::HostCS host, int device = 0, bool peer = false) : host_(std::move(host)), device_(device), is_peer_(peer)
         {
-            if (host_.get_hsm2k().compact_variant())
-                throw std::invalid_argument("B200CryptoSystem: the compact variant is not supported on the device path");
             open();
         }
 
@@ -447,6 +444,8 @@ namespace CoFHE
             std::vector<uint32_t> nl((H.N().nbits() + 31) / 32);
             put_mpz(H.N(), nl.data(), nl.size(), 1, false);
             check(cofhe_b200_set_scheme(ctx_, (uint32_t)H.k(), nl.data(), (uint32_t)nl.size()), "set_scheme");
+            if (H.compact_variant())
+                check(cofhe_b200_set_compact(ctx_, 1), "set_compact");
             ml_ = ((uint32_t)H.k() + 31) / 32;
             el_r_ = (uint32_t)((H.encrypt_randomness_bound().nbits() + 31) / 32);
             pk_set_ = false;
@@ -771,9 +770,9 @@ namespace CoFHE
         }
         up(hc, cw + ew + sw);
         void *st = cofhe_b200_stream(ctx_);
-        for (int y = 0; y < 2; y++) // c1 block, c2 block
-            check(cofhe_b200_nupow(ctx_, n, dev(hc) + y * fl() * n, dev(he), el, per_elem ? 1 : 0, per_elem ? (const uint8_t *)dev(hs) : nullptr,
-                                   shared_neg, dev(ho) + y * fl() * n, st), "nupow");
+        // both form blocks in one call (compact variant: the c1 block is exponentiated in Cl(DeltaK), the c2 block in Cl(Delta))
+        check(cofhe_b200_scal_ciphertexts(ctx_, n, dev(hc), dev(he), el, per_elem ? 1 : 0, per_elem ? (const uint8_t *)dev(hs) : nullptr,
+                                          shared_neg, dev(ho), st), "scal_ciphertexts");
         down(ho, cw);
         CoFHE_PARALLEL_FOR_STATIC_SCHEDULE for (size_t i = 0; i < n; i++) out[i] = get_ct(ho, i, n);
     }

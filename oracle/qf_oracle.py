@@ -273,6 +273,46 @@ def dlog_in_F(P, fm):
     return m
 
 
+def prime_to_2exp(f):
+    """QFI::prime_to_2exp (qfi.inl:590-610): an equivalent form whose a is odd."""
+    a, b, c = f
+    if a % 2 == 0:
+        if c % 2 == 0:
+            return (a + b + c, -b - 2 * a, a)
+        return (c, -b, a)
+    return f
+
+
+def lift_to_delta(P, f):
+    """CL_HSM2k::from_Cl_DeltaK_to_Cl_Delta (CL_HSM2k.inl:458-474), compact variant: QFI::lift_2exp(k+1)
+    (qfi.inl:263-271), chi from a and c modulo 4 of the lifted reduced form, k squarings in Cl(Delta)
+    (raise_to_power_M, :641-648), and for chi = -1 one composition with (4, 4, 1 - DeltaK 2^(2(k-1)))."""
+    a, b, c = prime_to_2exp(f)
+    k = P.k
+    g = reduce_form((a, b << (k + 1), c << (2 * (k + 1))))
+    chi_neg = g[0] % 4 == 3 or g[2] % 4 == 3
+    g = power(g, 1 << k)
+    if chi_neg:
+        g = compose(g, (4, 4, 1 - (P.DeltaK << (2 * (k - 1)))))
+    return g
+
+
+def encrypt_compact(P, pk, m, r):
+    """CL_HSM_CipherText(C, pk, m, r) with C.compact_variant() (CL_HSM_utils.inl:161-185): c1 = h^r in Cl(DeltaK),
+    c2 = lift(pk^r) o f^m in Cl(Delta); P.h and pk are forms of discriminant DeltaK."""
+    return (power(P.h, r), compose(lift_to_delta(P, power(pk, r)), power_of_f(P, m)))
+
+
+def decrypt_compact(P, sk, ct):
+    """CL_HSM_ClearText(C, sk, c) with C.compact_variant() (CL_HSM_utils.inl:124-138)."""
+    return dlog_in_F(P, compose_inv(ct[1], lift_to_delta(P, power(ct[0], sk))))
+
+
+def part_decrypt_compact(P, share, ct):
+    """partDecrypt with compact_variant (cpu_cryptosystem_distributed.inl:244-254)."""
+    return lift_to_delta(P, power(ct[0], share))
+
+
 def encrypt(P, pk, m, r):
     """CL_HSM_CipherText(C, pk, m, r) (CL_HSM_utils.inl:161-185): (h^r, pk^r o f^m)."""
     c1 = power_of_h(P, r)

@@ -63,9 +63,14 @@ def _ptr(a):
 class Reference:
     """One reference CPUCryptoSystem(nbits, k) (default-seeded RandGen, deterministic) plus a key pair."""
 
-    def __init__(self, nbits=128, k=128):
+    def __init__(self, nbits=128, k=128, compact=False):
         self.lib = _load()
-        self.h = self.lib.ref_new(nbits, k)
+        if compact:
+            self.lib.ref_new_compact.restype = ctypes.c_void_p
+            self.lib.ref_new_compact.argtypes = [ctypes.c_uint, ctypes.c_uint, ctypes.c_int]
+            self.h = self.lib.ref_new_compact(nbits, k, 1)
+        else:
+            self.h = self.lib.ref_new(nbits, k)
         if not self.h:
             raise RuntimeError("reference constructor failed")
         self.nbits, self.k = nbits, k

@@ -33,7 +33,7 @@ struct Ref {
   CS cs;
   CS::SecretKey *sk = nullptr;
   CS::PublicKey *pk = nullptr;
-  Ref(unsigned nbits, unsigned k) : cs(nbits, k) {}
+  Ref(unsigned nbits, unsigned k, bool compact = false) : cs(nbits, k, compact) {}
   ~Ref() { delete sk; delete pk; }
 };
 
@@ -104,6 +104,10 @@ std::string call(Ref &R, const std::string &op, const std::vector<Mpz> &a) {
     QFI r; G.nudupl(r, form(a, 0)); put(o, r);
   } else if (op == "nupow") {
     QFI r; G.nupow(r, form(a, 0), a[3]); put(o, r);
+  } else if (op == "lift") {                 // form of Cl(DeltaK) -> Cl(Delta) (compact variant: CL_HSM2k.inl:458-474)
+    QFI f = form(a, 0); H.from_Cl_DeltaK_to_Cl_Delta(f); put(o, f);
+  } else if (op == "nucomp_delta") {         // composition in Cl(Delta) whatever the variant
+    QFI r; H.Cl_Delta().nucomp(r, form(a, 0), form(a, 3)); put(o, r);
   } else if (op == "power_of_h") {
     QFI r; H.power_of_h(r, a[0]); put(o, r);
   } else if (op == "pk_exp") {
@@ -248,6 +252,10 @@ extern "C" {
 
 void *ref_new(unsigned nbits, unsigned k) {
   try { return new Ref(nbits, k); } catch (...) { return nullptr; }
+}
+// the compact variant of CL_HSM2k (CPUCryptoSystem(security_level, k, compact), cpu_cryptosystem.hpp:33)
+void *ref_new_compact(unsigned nbits, unsigned k, int compact) {
+  try { return new Ref(nbits, k, compact != 0); } catch (...) { return nullptr; }
 }
 void ref_free(void *h) { delete (Ref *)h; }
 void ref_free_str(char *s) { free(s); }

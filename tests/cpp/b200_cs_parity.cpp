@@ -2,7 +2,7 @@
 // CoFHE::B200CryptoSystem (device) and the reference's CoFHE::CPUCryptoSystem (host), both default-seeded, and counts
 // mismatching results (ciphertext forms compared bit for bit, plaintexts as integers).  Built by tests/cpp/build.py
 // where /root/reference exists (the reference headers are needed to compile it); the binary travels to the GPU box.
-// usage: b200_cs_parity [N_bits k]
+// usage: b200_cs_parity [N_bits k [compact]]
 //        b200_cs_parity --bench matadd ROWS COLS ITERS CPU_ITERS     (benchmarks/local.cpp:65-138 at ROWS x COLS)
 //        b200_cs_parity --bench matmul N M P ITERS CPU_ITERS         (benchmarks/local.cpp:140-215)
 // The --bench modes time the chained calls of the reference's own benchmark THROUGH THE CLASS API (Tensor<CipherText*> in,
@@ -117,8 +117,10 @@ int bench(int argc, char** argv) {
 int main(int argc, char** argv) {
   if (argc > 2 && !strcmp(argv[1], "--bench")) return bench(argc, argv);
   unsigned nbits = argc > 2 ? atoi(argv[1]) : 128, kk = argc > 2 ? atoi(argv[2]) : 128;
-  B200CryptoSystem cs(nbits, kk);
-  CPUCryptoSystem ref(nbits, kk);
+  // third argument 1: the compact variant of CL_HSM2k (c1, h, pk in Cl(DeltaK)) on both sides
+  const bool compact = argc > 3 && atoi(argv[3]) != 0;
+  B200CryptoSystem cs(nbits, kk, compact);
+  CPUCryptoSystem ref(nbits, kk, compact);
   auto sk = cs.keygen(); auto pk = cs.keygen(sk);
   auto sk2 = ref.keygen(); auto pk2 = ref.keygen(sk2);
   size_t n = 4, m = 3, p = 2;
@@ -262,7 +264,7 @@ int main(int argc, char** argv) {
   // error must come back as std::invalid_argument from the call, not as an exception escaping a parallel region
   if (nbits < 256) {
     try {
-      CPUCryptoSystem other(256, kk);
+      CPUCryptoSystem other(256, kk, compact);
       auto osk = other.keygen(); auto opk = other.keygen(osk);
       Tensor<B200CryptoSystem::PlainText*> opt(2, nullptr);
       for (size_t i = 0; i < 2; i++) opt.at(i) = new B200CryptoSystem::PlainText((unsigned long)(i + 5));

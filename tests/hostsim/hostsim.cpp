@@ -4,6 +4,7 @@
 // product (libcofhe_b200.so) has no CPU execution path at all.
 #include <cstddef>
 #include <cstring>
+#include <vector>
 #include "ops.cuh"
 #include "hostsim_extra.inc"
 #include "coop_sim.inc"

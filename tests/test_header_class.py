@@ -29,6 +29,18 @@ def test_header_class_matches_reference(nbits, k):
     assert r.returncode == 0 and "mismatches 0" in r.stdout, r.stdout + r.stderr
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("nbits,k", [(128, 128), (64, 16), (256, 64)])
+def test_header_class_compact_variant_matches_reference(nbits, k):
+    """CPUCryptoSystem(level, k, compact=true) (CL_HSM2k.inl:31-39, 76-80, 458-474): every call of the parity driver --
+    encrypt, add, scal / matmul, negate, decrypt, threshold decryption, the single-ciphertext calls, the wire formats and
+    the device-resident chain -- with c1, h and pk in Cl(DeltaK), against the reference class draw for draw"""
+    if not os.path.exists(BIN):
+        pytest.skip("tests/_cpp/b200_cs_parity was not built (needs /root/reference at build time)")
+    r = subprocess.run([BIN, str(nbits), str(k), "1"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "mismatches 0" in r.stdout, r.stdout + r.stderr
+
+
 LOCAL_B200 = os.path.join(ROOT, "tests", "_cpp", "local_b200")
 LOCAL_CPU = os.path.join(ROOT, "tests", "_cpp", "local_cpu")
 
