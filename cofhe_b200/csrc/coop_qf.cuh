@@ -309,7 +309,15 @@ CG_FN bool cq_mulmod(const Grp<T> &g, u32 *r, const u32 *x, const u32 *y, const 
 
 // r = f1 o f2 (neg2: f1 o f2^-1; DUPL: f1^2, f2 ignored).  N = limbs of a reduced a or b.  `act`: this group has an
 // element.  false = declined (or no element).
-template <int T, int L, int N, bool DUPL>
+// SYNC: block barriers between the phases (only where every warp of the block makes the same number of calls: the batched
+// composition kernel).  The warps of an SM then walk through the long straight-line code together and share its
+// instruction-cache lines instead of evicting each other's (the register path does the same: qf_fast.cuh QF_PHASE).
+#if defined(__CUDACC__)
+#define CQ_PHASE() do { if (SYNC) __syncthreads(); } while (0)
+#else
+#define CQ_PHASE() ((void)0)
+#endif
+template <int T, int L, int N, bool DUPL, bool SYNC = false>
 CG_FN bool cq_compose(const Grp<T> &g, FormC<L> &r, const FormC<L> &f1, const FormC<L> &f2, bool neg2, int dbits, bool act) {
   constexpr int K = T * L;
   constexpr int M = (N + 1) / 2 + 1;  // half width of the post-Euclid quantities
@@ -339,6 +347,7 @@ CG_FN bool cq_compose(const Grp<T> &g, FormC<L> &r, const FormC<L> &f1, const Fo
   g_subm<T, L>(g, m, b2, s);
 
   CG_MARK(10);
+  CQ_PHASE();
   // ---- phases 1-3 share ONE inlined instance of the Euclid (its code is the largest single piece of the kernel):
   //   phase 1: F = gcd(a1, a2) with v*a2 == F (mod a1)   [DUPL: F = a, G = gcd(a, b) = . + y*|b|]
   //   phase 2: By = a1/G and Bx
@@ -499,6 +508,7 @@ CG_FN bool cq_compose(const Grp<T> &g, FormC<L> &r, const FormC<L> &f1, const Fo
     }
     g_zero<T, L>(C0);
     g_set_u32<T, L>(g, C1, 1);
+    CQ_PHASE();
     int stp = g_hxgcd<T, L>(g, By, Bx, C0, C1, stop, !bail, bail);  // (By, Bx) <- (R_{i-1}, R_i)
     if (ph == 0) {
       st1 = stp;
@@ -510,6 +520,7 @@ CG_FN bool cq_compose(const Grp<T> &g, FormC<L> &r, const FormC<L> &f1, const Fo
   }
 
   CG_MARK(40);
+  CQ_PHASE();
   // ---- phase 4: the C and D columns from the orthogonality relations
   // rows: x' = (Ax, Bxp) with Ax = G*C0 >= 0, Bxp = (-1)^idx R_{i-1};  y' = (Ay, Byp) with Ay = (-1)^(idx+1) G*C1, Byp = R_i
   const int idx = 1 + st;
@@ -572,6 +583,7 @@ CG_FN bool cq_compose(const Grp<T> &g, FormC<L> &r, const FormC<L> &f1, const Fo
   }
 
   CG_MARK(50);
+  CQ_PHASE();
   // ---- phase 5: the composed form (two's complement):
   //   a3 = By*Cy - Ay*Dy ; c3 = Bx*Cx - Ax*Dx ; b3 = (Ax*Dy + Ay*Dx) - (Bx*Cy + By*Cx)
   u32 ra[L], rb[L], rc[L];
@@ -605,6 +617,7 @@ CG_FN bool cq_compose(const Grp<T> &g, FormC<L> &r, const FormC<L> &f1, const Fo
   }
 
   CG_MARK(60);
+  CQ_PHASE();
   // ---- phase 6: canonical reduction
   if (!cq_reduce<T, L>(g, ra, rb, rc, dbits, !bail)) bail = true;
   if (g_bits<T, L>(g, ra) > 32 * N - 1) bail = true;  // |b| <= a: b fits N limbs signed

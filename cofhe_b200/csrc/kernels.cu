@@ -67,6 +67,10 @@ struct cofhe_b200_ctx {
   u32 *d_fb_tab;      // window tables of h and pk (fast tiers)
   MMShape fb;
   int fb_set;
+  int fb_coop = 0;    // the fixed-base tables are SoA batches for the cooperative multi-exponentiation (coop_tables)
+  size_t fb_ne = 0;   // their entries per form block
+  u32 *d_tpbail = nullptr;  // outputs the cooperative multi-exponentiation hands to the robust path: [0] counter, [1] spare, [2..] list
+  size_t tpbail_cap = 0;
   // One context may be shared by threads and streams (include/cofhe_b200.h "Threads and streams"): entry points
   // serialise on `mu`; when the caller's stream changes, the new stream is ordered after the previous one, because the
   // scratch above is shared by all calls.
@@ -79,7 +83,7 @@ struct cofhe_b200_ctx {
   struct Block { void *p; size_t bytes; };
   std::vector<Block> live, pool;
   size_t pool_bytes = 0;
-  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop, coop_mb; } opt;
+  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop, coop_mb, coop_pb; } opt;
 };
 
 namespace {
@@ -367,7 +371,9 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
   if (coop) {
     COOP_DISPATCH(ctx->coopn, {
       typedef CoopKernels<CT, CL, CN, CCAP> K;
-      if (op < 2) K::compose(op == 1, ny, st, gs.G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+      // default: block barriers between the phases; 256-thread blocks once the batch fills the machine several times over
+      if (op < 2) K::compose(op == 1, ny, st, gs.G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt,
+                             ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : ((size_t)ny * n >= 98304 ? 24 : 14));
       else {
         size_t tw = K::pow_tab_words(ny, nc, n) * sizeof(u32);
         if (tw > ctx->powtab_bytes) {
@@ -376,7 +382,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
           if (cudaMalloc(&ctx->d_powtab, tw) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
           ctx->powtab_bytes = tw;
         }
-        K::pow(ny, st, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_powtab, ctx->d_bail, cnt);
+        K::pow(ny, st, gs.G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_powtab, ctx->d_bail, cnt, ctx->opt.coop_pb == 256 ? 256 : 128);
       }
     })
   } else {
@@ -451,6 +457,85 @@ int mm_robust_all(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u3
   return check_launch(ctx);
 }
 
+// ---- the same machinery on the cooperative kernels (widths without a register instantiation: T1) ------------------------
+// Tables are plain SoA ciphertext batches [2][fl][ne], ne = (2^W - 1) * nwin * nb, entry (d, w, base) at element
+// (d-1)*nwin*nb + w*nb + base (coop_ops.cuh cq_tabprod), built with the batched squaring / composition launches:
+//   B_w = ct^(2^(W w)) by W squarings per window; T[d] = T[d-1] o T[1] over all (w, base) at once for d = 2 .. 2^W - 1.
+// dst[r][e] (row stride dst_n) = src[r][src_off + e] (row stride src_n) for e < cnt: a range of elements as its own batch
+__global__ void __launch_bounds__(kBlock) k_cols_copy(int rows, size_t cnt, u32 *dst, size_t dst_n, const u32 *src, size_t src_n, size_t src_off) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)rows * cnt) return;
+  size_t r = t / cnt, e = t % cnt;
+  dst[r * dst_n + e] = src[r * src_n + src_off + e];
+}
+bool use_coop_tab(const cofhe_b200_ctx *ctx) { return ctx->coopn && use_coop(ctx) && (!ctx->fastn || ctx->opt.coop == 1); }
+size_t coop_tab_entries(const MMShape &s) { return (size_t)s.n * s.m * s.nwin * ((1u << s.W) - 1); }
+// scratch words of coop_tables
+size_t coop_build_words(const cofhe_b200_ctx *ctx, const MMShape &s) {
+  const size_t rows = 2 * (2 * (size_t)ctx->na + ctx->nc), nb = (size_t)s.n * s.m;
+  return rows * (3 * nb * s.nwin + nb);
+}
+int cols_copy(cofhe_b200_ctx *ctx, int rows, size_t cnt, u32 *dst, size_t dst_n, const u32 *src, size_t src_n, cudaStream_t st) {
+  const size_t tot = (size_t)rows * cnt;
+  k_cols_copy<<<(unsigned)((tot + kBlock - 1) / kBlock), kBlock, 0, st>>>(rows, cnt, dst, dst_n, src, src_n, 0);
+  return check_launch(ctx);
+}
+int coop_tables(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, u32 *tab, u32 *scratch, cudaStream_t st) {
+  const int rows = (int)(2 * (2 * ctx->na + ctx->nc));
+  const size_t nb = (size_t)s.n * s.m, nbw = nb * s.nwin, ne = coop_tab_entries(s);
+  u32 *B = scratch, *X = B + (size_t)rows * nbw, *Y = X + (size_t)rows * nbw, *cur = Y + (size_t)rows * nbw;
+  int rc = cols_copy(ctx, rows, nb, cur, nb, ct, nb, st);
+  for (int w = 0; w < s.nwin && rc == COFHE_B200_OK; w++) {
+    rc = cols_copy(ctx, rows, nb, B + (size_t)w * nb, nbw, cur, nb, st);
+    if (w + 1 < s.nwin)
+      for (int t = 0; t < s.W && rc == COFHE_B200_OK; t++) rc = launch_op(ctx, 1, 2, nb, cur, cur, cur, 0, nullptr, 0, 0, nullptr, 0, st);
+  }
+  if (rc != COFHE_B200_OK) return rc;
+  rc = cols_copy(ctx, rows, nbw, tab, ne, B, nbw, st);
+  const u32 *prev = B;
+  const int nt = (1 << s.W) - 1;
+  for (int d = 2; d <= nt && rc == COFHE_B200_OK; d++) {
+    u32 *dst = (d & 1) ? X : Y;
+    rc = launch_op(ctx, d == 2 ? 1 : 0, 2, nbw, prev, B, dst, 0, nullptr, 0, 0, nullptr, 0, st);
+    if (rc == COFHE_B200_OK) rc = cols_copy(ctx, rows, nbw, tab + (size_t)(d - 1) * nbw, ne, dst, nbw, st);
+    prev = dst;
+  }
+  return rc;
+}
+// out[i,k] = init o prod_j prod_w T[...]: one cooperative launch over (chunk, output), the chunks combined by batched
+// compositions, flagged outputs redone from ct on the robust path.  part: chunks * 2 * fl * n*p words when chunks > 1.
+int coop_mm_eval(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32 *scal, const u32 *init, u32 *out, const u32 *tab, size_t ne,
+                 u32 *part, cudaStream_t st) {
+  Shape sh{(int)ctx->na, (int)ctx->nc};
+  const size_t no = (size_t)s.n * s.p, fl = 2 * (size_t)ctx->na + ctx->nc;
+  const size_t need = 2 * no * s.chunks + 2;
+  if (need > ctx->tpbail_cap) {
+    if (ctx->d_tpbail) cudaFree(ctx->d_tpbail);
+    ctx->d_tpbail = nullptr; ctx->tpbail_cap = 0;
+    if (cudaMalloc(&ctx->d_tpbail, need * sizeof(u32)) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+    ctx->tpbail_cap = need;
+  }
+  if (cudaMemsetAsync(ctx->d_tpbail, 0, 2 * sizeof(u32), st) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ECUDA; }
+  const GSel gs = gsel(ctx, 2);
+  u32 *dst = s.chunks > 1 ? part : out;
+  // 256-thread blocks (8 warps aligned by the barriers, two blocks per SM) once every SM gets one: measured at T1, 8 192
+  // fixed-base pairs 108 -> 68 ms, 2 048 pairs 39 -> 46 ms
+  const size_t tp_groups = 2 * no * s.chunks, tp_lanes = ctx->coopn >= 33 ? 4 : 2;
+  const int tp_block = ctx->opt.coop_pb == 256 ? 256 : (ctx->opt.coop_pb == 128 ? 128 :
+                       (tp_groups >= (size_t)(ctx->sms > 0 ? ctx->sms : 148) * (256 / tp_lanes) ? 256 : 128));
+  COOP_DISPATCH(ctx->coopn, {
+    typedef CoopKernels<CT, CL, CN, CCAP> K;
+    K::tabprod(2, st, gs.G, gs.dbits, (int)ctx->nc, s, scal, tab, ne, init, dst, ctx->d_tpbail + 2, (int *)ctx->d_tpbail, tp_block);
+  })
+  int rc = check_launch(ctx);
+  for (unsigned c = 1; c < s.chunks && rc == COFHE_B200_OK; c++)
+    rc = launch_op(ctx, 0, 2, no, c == 1 ? part : out, part + (size_t)c * 2 * fl * no, out, 0, nullptr, 0, 0, nullptr, 0, st);
+  if (rc != COFHE_B200_OK) return rc;
+  CAP_DISPATCH(ctx->cap, k_mm_robust<CAP><<<32, 128, 0, st>>>((const Group<CAP> *)gs.G, sh, s, ct, scal, init, out, ctx->d_tpbail + 2,
+                                                              (const int *)ctx->d_tpbail, (int *)ctx->d_tpbail + 1, ctx->d_err, gs.alt))
+  return check_launch(ctx);
+}
+
 // (h^e, pk^e) for n exponents into a ciphertext-shaped batch `out`; part: scratch of mm_part_words(fb with p = n)
 int fb_pow(cofhe_b200_ctx *ctx, size_t n, const u32 *exps, u32 el, u32 *out, u32 *part, cudaStream_t st) {
   MMShape s = ctx->fb;
@@ -458,8 +543,9 @@ int fb_pow(cofhe_b200_ctx *ctx, size_t n, const u32 *exps, u32 el, u32 *out, u32
   UseK in_cl_g(ctx);  // compact variant: h and pk are elements of Cl(DeltaK) (CL_HSM2k.inl:76-80, Cl_G :255)
   s.p = (unsigned)n;
   s.el = (int)el;
+  if (ctx->fb_coop) return coop_mm_eval(ctx, s, ctx->d_fb_bases, exps, nullptr, out, ctx->d_fb_tab, ctx->fb_ne, nullptr, st);
   if (!ctx->fastn && use_coop(ctx)) {
-    // no table kernels at this width: (h^e, pk^e) as two exponentiations per element on the cooperative kernel
+    // no tables (set_bases ran while the cooperative path was off): (h^e, pk^e) as two exponentiations per element
     const int rows = (int)(2 * (2 * ctx->na + ctx->nc));
     k_bcast<<<grid_for(n), kBlock, 0, st>>>(n, rows, ctx->d_fb_bases, out);
     int rc = check_launch(ctx);
@@ -598,7 +684,8 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->opt.host_chunks = env_opt("COFHE_B200_HOST_CHUNKS", 0, 64);
   ctx->opt.host_trace = getenv("COFHE_B200_HOST_TRACE") ? 1 : 0;
   ctx->opt.coop = env_opt("COFHE_B200_COOP", 0, 1);
-  ctx->opt.coop_mb = env_opt("COFHE_B200_COOP_MB", 3, 5);
+  ctx->opt.coop_mb = env_opt("COFHE_B200_COOP_MB", 3, 24);
+  ctx->opt.coop_pb = env_opt("COFHE_B200_COOP_PB", 128, 256);
   ctx->device = device;
   ctx->sms = 0;
   if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); ctx->sms = 0; }
@@ -664,6 +751,7 @@ void cofhe_b200_destroy(cofhe_b200_ctx *ctx) {
   if (ctx->d_tmp) cudaFree(ctx->d_tmp);
   if (ctx->d_powtab) cudaFree(ctx->d_powtab);
   if (ctx->d_lift) cudaFree(ctx->d_lift);
+  if (ctx->d_tpbail) cudaFree(ctx->d_tpbail);
   if (ctx->d_scheme) cudaFree(ctx->d_scheme);
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   if (ctx->d_fb_bases) cudaFree(ctx->d_fb_bases);
@@ -715,7 +803,7 @@ int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
   struct { const char *n; long *p; } tab[] = {
       {"mm_w", &ctx->opt.mm_w}, {"mm_chunks", &ctx->opt.mm_chunks}, {"mm_block", &ctx->opt.mm_block}, {"fb_w", &ctx->opt.fb_w},
       {"host_staged", &ctx->opt.host_staged}, {"host_loadc", &ctx->opt.host_loadc}, {"host_chunks", &ctx->opt.host_chunks},
-      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}, {"coop_mb", &ctx->opt.coop_mb}};
+      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}, {"coop_mb", &ctx->opt.coop_mb}, {"coop_pb", &ctx->opt.coop_pb}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) { *t.p = value; return COFHE_B200_OK; }
   return COFHE_B200_EINVAL;
@@ -797,7 +885,7 @@ int cofhe_b200_add_ciphertexts_static(cofhe_b200_ctx *ctx, size_t n, const uint3
   if (coop) {
     COOP_DISPATCH(ctx->coopn, {
       typedef CoopKernels<CT, CL, CN, CCAP> K;
-      K::compose(false, ny, st, gs.G, dbits, nc, n, ct1, ct2, out, 0, bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 4);
+      K::compose(false, ny, st, gs.G, dbits, nc, n, ct1, ct2, out, 0, bail, cnt, ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : 14);
     })
   } else {
     FAST_DISPATCH(ctx->fastn, {
@@ -831,13 +919,14 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   {
     size_t fm = 0, tm = 0;
     if (cudaMemGetInfo(&fm, &tm) != cudaSuccess) { cudaGetLastError(); fm = (size_t)8 << 30; }
-    const double te_bytes = 4.0 * (((3 * ctx->fastn + 1) + 3) & ~3);
+    const bool ctab = use_coop_tab(ctx);
+    const double te_bytes = ctab ? 4.0 * (2 * ctx->na + ctx->nc) : 4.0 * (((3 * ctx->fastn + 1) + 3) & ~3);
     double best = 0;
     s.W = 4;
     for (int W = 2; W <= 8; W++) {
       double nwin = (double)((ebits + W - 1) / W), ent = (double)((1u << W) - 1);
       double bytes = 2.0 * (double)n * (double)m * nwin * ent * te_bytes;
-      if (ctx->fastn && bytes > 0.4 * (double)fm && W > 2) continue;
+      if ((ctx->fastn || ctab) && bytes > 0.4 * (double)fm && W > 2) continue;
       double cost = (double)p * nwin * (1.0 - 1.0 / (double)(1u << W)) + 2.0 * nwin * ent + nwin * W;
       if (best == 0 || cost < best) { best = cost; s.W = W; }
     }
@@ -846,6 +935,27 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
   s.nwin = (int)((ebits + s.W - 1) / s.W);
   s.chunks = 1; s.jper = (unsigned)m; s.block = 0;
   size_t no = n * p;
+  if (use_coop_tab(ctx) && m > 0) {
+    // cooperative kernels: SoA tables, one lane group per (chunk, output); enough chunks of the j range to fill the machine
+    // (3 blocks of 128 threads per SM), each extra chunk costs one batched composition per output
+    const size_t sms = (size_t)(ctx->sms > 0 ? ctx->sms : 148);
+    const size_t lanes = ctx->coopn >= 33 ? 4 : 2;
+    const size_t slots = sms * 3 * (kCoopBlock / lanes);
+    size_t ch = (slots + 2 * no - 1) / (2 * no);
+    if (ch > m) ch = m;
+    if (ch < 1) ch = 1;
+    if (ctx->opt.mm_chunks >= 1 && (size_t)ctx->opt.mm_chunks <= m) ch = (size_t)ctx->opt.mm_chunks;
+    s.jper = (unsigned)((m + ch - 1) / ch);
+    s.chunks = (unsigned)((m + s.jper - 1) / s.jper);
+    const size_t fl = 2 * (size_t)ctx->na + ctx->nc, ne = coop_tab_entries(s);
+    const size_t tw = 2 * fl * ne, bw = coop_build_words(ctx, s), pw = s.chunks > 1 ? (size_t)s.chunks * 2 * fl * no : 0;
+    int rc = ensure_work(ctx, (tw + (bw > pw ? bw : pw)) * sizeof(u32));
+    if (rc != COFHE_B200_OK) return rc;
+    u32 *tab = ctx->d_work, *rest = tab + tw;  // the build scratch is dead when the partial products are written
+    rc = coop_tables(ctx, s, ct, tab, rest, st);
+    if (rc != COFHE_B200_OK) return rc;
+    return coop_mm_eval(ctx, s, ct, scal, init, out, tab, ne, rest, st);
+  }
   if (!ctx->fastn || m == 0) return mm_robust_all(ctx, s, ct, scal, init, out, st);
   // split the j range so that small n*p still fills the machine
   // k_mm_accum: blocks of `block` threads, 512 / block of them resident per SM (128 registers), all equally long: pick
@@ -1001,6 +1111,26 @@ int cofhe_b200_set_bases(cofhe_b200_ctx *ctx, const uint32_t *h, const uint32_t 
   s.nwin = (32 * s.el + s.W - 1) / s.W;
   ctx->fb = s;
   ctx->fb_set = 1;
+  ctx->fb_coop = 0;
+  if (use_coop_tab(ctx)) {
+    // tables for the cooperative multi-exponentiation (the widths without register kernels: T1)
+    const size_t ne = coop_tab_entries(s);
+    if (ctx->d_fb_tab) { cudaFree(ctx->d_fb_tab); ctx->d_fb_tab = nullptr; }
+    u32 *scratch = nullptr;
+    if (cudaMalloc(&ctx->d_fb_tab, 2 * fl * ne * sizeof(u32)) != cudaSuccess ||
+        cudaMalloc(&scratch, coop_build_words(ctx, s) * sizeof(u32)) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
+    int rc;
+    {
+      UseK in_cl_g(ctx);
+      rc = coop_tables(ctx, s, ctx->d_fb_bases, ctx->d_fb_tab, scratch, ctx->xfer);
+    }
+    if (rc == COFHE_B200_OK) rc = cofhe_b200_status(ctx, ctx->xfer);
+    cudaFree(scratch);
+    if (rc != COFHE_B200_OK) return rc;
+    ctx->fb_coop = 1;
+    ctx->fb_ne = ne;
+    return COFHE_B200_OK;
+  }
   if (!ctx->fastn) return COFHE_B200_OK;
   if (ctx->d_fb_tab) { cudaFree(ctx->d_fb_tab); ctx->d_fb_tab = nullptr; }
   if (cudaMalloc(&ctx->d_fb_tab, mm_tab_words(ctx, s) * sizeof(u32)) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
@@ -1293,14 +1423,6 @@ __global__ void __launch_bounds__(kBlock) k_ctmm_slabs(int rows, size_t n, size_
   size_t r = t / tot, e = t % tot, j = j0 + e / np, ik = e % np, i = ik / p, k = ik % p;
   dst[t] = prod[r * (n * m * p) + (i * m + j) * p + k];
 }
-// dst[r][e] (row stride dst_n) = src[r][src_off + e] (row stride src_n) for e < cnt: a range of elements as its own batch
-__global__ void __launch_bounds__(kBlock) k_cols_copy(int rows, size_t cnt, u32 *dst, size_t dst_n, const u32 *src, size_t src_n, size_t src_off) {
-  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= (size_t)rows * cnt) return;
-  size_t r = t / cnt, e = t % cnt;
-  dst[r * dst_n + e] = src[r * src_n + src_off + e];
-}
-
 int cofhe_b200_ct_matmul_expand(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, const uint32_t *ct1, const uint32_t *ct2, uint32_t *out1,
                                 uint32_t *out2, void *stream) {
   if (!ctx || !ct1 || !ct2 || !out1 || !out2 || n == 0 || m == 0 || p == 0 || (n * m * p) >> 30) return COFHE_B200_EINVAL;

@@ -128,3 +128,52 @@ def test_coop_pow_equals_other_path(groups, name):
             assert out[i] == O.power(fs[i], es[i])
     finally:
         G.set_option("coop", -1)
+
+
+@pytest.mark.parametrize("name", ["t0", "node", "t1"])
+def test_coop_tables_matmul_and_fixed_base(name):
+    """the multi-exponentiation from window tables on the cooperative kernels (k_coop_tabprod; the path of T1, forced on
+    the narrower widths with the "coop" option set BEFORE set_bases): fixed base and encryption against the reference's
+    fixtures, the scal_matmul fixtures, and a larger matmul (several chunks of the inner index, every window width)
+    against the oracle"""
+    from cofhe_b200.group import ClassGroupB200
+    t = load_golden("ref_%s.json" % name)
+    p = t["params"]
+    G = ClassGroupB200(int(p["Delta"]))
+    if not int(G.lib.cofhe_b200_coop_limbs(G.h)):
+        G.close()
+        pytest.skip("no cooperative instantiation for this width")
+    try:
+        G.set_option("coop", 1)
+        G.set_scheme(int(p["k"]), int(p["N"]))
+        G.set_bases(I(p["h"]), I(t["pk"]), int(p["exponent_bound"]).bit_length())
+        vs = t["fixed_base"]
+        assert G.cts_out(G.fixed_base_pow([int(v["r"]) for v in vs])) == [(I(v["h"]), I(v["pk"])) for v in vs]
+        G.status()
+        es = t["encrypt"]
+        ct = G.encrypt([int(v["m"]) for v in es], [int(v["r"]) for v in es])
+        assert G.cts_out(ct) == [I(v["ct"]) for v in es]
+        assert G.ints_out(G.decrypt(ct, int(t["sk"]))) == [int(v["dec"]) for v in es]
+        G.status()
+        for c in t["scal_matmul"]:
+            res = G.scal_matmul(G.cts(I(c["ct"])), [int(x) for x in c["s"]], c["n"], c["m"], c["p"], G.cts([I(c["zero"])]))
+            assert G.cts_out(res) == list(I(c["res"])), c["label"]
+        G.status()
+        # a larger product: 2 x 6 . 6 x 5, scalars with zero digits and zero scalars, chunked inner index
+        rng = random.Random(77)
+        n, m, pp = 2, 6, 5
+        cts = [t["add_tensors"]["ct1"][i % 4] if i % 2 else t["add_tensors"]["ct2"][i % 4] for i in range(n * m)]
+        cts = [I(c) for c in cts]
+        sc = [rng.getrandbits(rng.choice([3, 13, 17, 40])) for _ in range(m * pp)]
+        sc[4] = 0
+        sc[7] = 1 << 12
+        zero = I(t["scal_matmul"][0]["zero"])
+        want = O.scal_matmul(zero, cts, sc, n, m, pp)
+        for w, ch in ((-1, -1), (2, 3), (3, 1), (5, 6)):
+            G.set_option("mm_w", w)
+            G.set_option("mm_chunks", ch)
+            res = G.scal_matmul(G.cts(cts), sc, n, m, pp, G.cts([zero]))
+            G.status()
+            assert G.cts_out(res) == want, (w, ch)
+    finally:
+        G.close()

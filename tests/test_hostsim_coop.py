@@ -129,3 +129,31 @@ def test_coop_pow(name, shape):
     for i in range(n):
         if es[i]:
             assert got[i] == O.power(f[i], -es[i] if sg[i] else es[i]), i
+
+
+def test_coop_slow_compose_fallback(tier):
+    """cq_slow_compose (coop_ops.cuh): the robust composition one lane runs for its group when the cooperative composition
+    declines inside an exponentiation / table loop -- forced for every group, and for every other group of a warp"""
+    ss = sims(tier)
+    if not ss:
+        pytest.skip("no cooperative instantiation for this width")
+    vs = tier["compose"]
+    f1, f2 = [I(v["f1"]) for v in vs], [I(v["f2"]) for v in vs]
+    lib = HS.load()
+    try:
+        for S in ss[:1]:
+            lib.hs_coop_force_slow(2)
+            g, b = S.run(f1, f2)
+            assert int(b.sum()) == 0 and g == [I(v["r"]) for v in vs]
+            g, b = S.run(f1, dupl=True)
+            assert int(b.sum()) == 0 and g == [I(v["sq"]) for v in vs]
+            lib.hs_coop_force_slow(1)
+            g, b = S.run(f1, f2)
+            groups = 32 // S.T
+            for i, v in enumerate(vs):
+                if (i % groups) % 2 == 0:
+                    assert not b[i] and g[i] == I(v["r"])
+                else:
+                    assert b[i]
+    finally:
+        lib.hs_coop_force_slow(0)

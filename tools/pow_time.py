@@ -29,8 +29,9 @@ for tier in (sys.argv[1:] or ["t1", "t0"]):
         ms = [rng.getrandbits(int(p["k"])) for _ in range(n)]
         ct = G.encrypt(ms, rng.randrange(1, int(p["exponent_bound"])))
         G.status()
-        for mode in ((0, 1) if int(G.lib.cofhe_b200_coop_limbs(G.h)) else (0,)):
-            G.set_option("coop", mode)
+        for mode in ((0, 1, 256) if int(G.lib.cofhe_b200_coop_limbs(G.h)) else (0,)):   # 256: cooperative kernels in 256-thread blocks
+            G.set_option("coop", 1 if mode else 0)
+            G.set_option("coop_pb", 256 if mode == 256 else 128)
             dt = timeit(lambda: G.part_decrypt(ct, sk))
             G.status()
             dd = timeit(lambda: G.decrypt(ct, sk), reps=1)
@@ -38,4 +39,16 @@ for tier in (sys.argv[1:] or ["t1", "t0"]):
             G.status()
             print("%s n=%6d coop=%d part_decrypt(%d-bit) %9.3f ms %9.1f k/s | decrypt %9.3f ms %9.1f k/s ok=%s" % (tier, n, mode, sk.bit_length(), dt * 1e3, n / dt / 1e3, dd * 1e3, n / dd / 1e3, ok))
         G.set_option("coop", -1)
+        G.set_option("coop_pb", -1)
+        for pb in (128, 256):
+            G.set_option("coop_pb", pb)
+            # encryption with own randomness per ciphertext (2 fixed-base exponentiations + f^m + 1 composition each)
+            rs = [rng.randrange(1, int(p["exponent_bound"])) for _ in range(n)]
+            rd, md = G.ints(rs, G.el_r), G.ints(ms, G.ml)
+            de = timeit(lambda: G.encrypt(md, rd))
+            G.status()
+            ok = G.ints_out(G.decrypt(G.encrypt(md, rd), sk)) == ms
+            G.status()
+            print("%s n=%6d encrypt pb=%d (own r, %d-bit) %9.3f ms %9.1f k/s roundtrip=%s" % (tier, n, pb, int(p["exponent_bound"]).bit_length(), de * 1e3, n / de / 1e3, ok))
+        G.set_option("coop_pb", -1)
     G.close()
