@@ -8,8 +8,8 @@
 namespace cofhe {
 
 // grid.y selects the form block inside a ciphertext batch (0: c1, 1: c2); plain form batches use grid.y == 1
-template <int N, int CAP, bool DUPL>
-__global__ void __launch_bounds__(kBlock, 4) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
+template <int N, int CAP, bool DUPL, int BLK = kBlock>
+__global__ void __launch_bounds__(BLK, 512 / BLK) k_fast_compose(const Group<CAP> *G, int dbits, int nc, size_t n, const u32 *in1, const u32 *in2, u32 *out,
                                                          int neg2, u32 *bail, int *nbail) {
   if (gs_pick(dbits, blockIdx.y)) G += 1;  // compact variant: form block 0 (c1) lives in Cl(DeltaK)
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -72,6 +72,21 @@ template <int FN, int FCAP>
 void FastKernels<FN, FCAP>::compose(bool dupl, dim3 grid, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in1,
                                     const u32 *in2, u32 *out, int flags, u32 *bail, int *nbail) {
   const Group<FCAP> *g = (const Group<FCAP> *)G;
+  // grid.x arrives sized for kBlock threads; `wide` != 0 asks for blocks of that many threads (256 / 512: 8 / 16 warps kept in
+  // the same region of the code by the phase barriers) -- for batches that fill the machine several times over
+  const int wide = (flags >> 8) & 0xfff;
+  flags &= 0xff;
+  if (wide == 256 || wide == 512) {
+    dim3 g2((unsigned)((n + wide - 1) / wide), grid.y);
+    if (wide == 256) {
+      if (dupl) k_fast_compose<FN, FCAP, true, 256><<<g2, 256, 0, st>>>(g, dbits, nc, n, in1, in1, out, flags & ~1, bail, nbail);
+      else k_fast_compose<FN, FCAP, false, 256><<<g2, 256, 0, st>>>(g, dbits, nc, n, in1, in2, out, flags, bail, nbail);
+    } else {
+      if (dupl) k_fast_compose<FN, FCAP, true, 512><<<g2, 512, 0, st>>>(g, dbits, nc, n, in1, in1, out, flags & ~1, bail, nbail);
+      else k_fast_compose<FN, FCAP, false, 512><<<g2, 512, 0, st>>>(g, dbits, nc, n, in1, in2, out, flags, bail, nbail);
+    }
+    return;
+  }
   if (dupl) k_fast_compose<FN, FCAP, true><<<grid, kBlock, 0, st>>>(g, dbits, nc, n, in1, in1, out, flags & ~1, bail, nbail);
   else k_fast_compose<FN, FCAP, false><<<grid, kBlock, 0, st>>>(g, dbits, nc, n, in1, in2, out, flags, bail, nbail);
 }

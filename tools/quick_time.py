@@ -32,8 +32,14 @@ for n in sizes:
     g = G.nupow(seeds, exps=[rng.getrandbits(40) | 1 for _ in range(n)])
     G.status()
     out = torch.empty_like(f)
-    dt = timeit(lambda: G.nucomp(f, g, out=out)); print("n=%d nucomp  %.3f ms  %.1f M/s" % (n, dt * 1e3, n / dt / 1e6))
-    dt = timeit(lambda: G.nudupl(f, out=out)); print("n=%d nudupl  %.3f ms  %.1f M/s" % (n, dt * 1e3, n / dt / 1e6))
+    ref = None
+    for fb in (128, 256, 512):   # threads per block of the register composition kernel
+        G.set_option("fast_block", fb)
+        dt = timeit(lambda: G.nucomp(f, g, out=out)); print("n=%d block=%d nucomp  %.3f ms  %.1f M/s" % (n, fb, dt * 1e3, n / dt / 1e6))
+        if ref is None: ref = out.clone()
+        else: assert torch.equal(ref, out)
+        dt = timeit(lambda: G.nudupl(f, out=out)); print("n=%d block=%d nudupl  %.3f ms  %.1f M/s" % (n, fb, dt * 1e3, n / dt / 1e6))
+    G.set_option("fast_block", -1)
     e = int(t["sk"])
     dt = timeit(lambda: G.nupow(f, shared=e), reps=2); print("n=%d nupow(%d bits shared) %.3f ms  %.1f k/s" % (n, e.bit_length(), dt * 1e3, n / dt / 1e3))
     G.status()
