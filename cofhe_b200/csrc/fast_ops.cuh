@@ -131,12 +131,12 @@ QF_HD bool hy_compose(const Group<CAP> *G, FormR<N> &r, const FormR<N> &f1, cons
 // SYNC: the composition runs with block barriers between its phases (qf_fast.cuh), so EVERY thread of the block must
 // make the call; a thread with nothing to compose passes active = false, walks through on whatever x and t hold and
 // leaves x untouched.
-template <int N, int CAP, bool DUPL, bool SYNC = false>
+template <int N, int CAP, bool DUPL, bool SYNC = false, bool FLAT = false>
 QF_HDN bool cc_compose(const Group<CAP> *G, u32 *x, const u32 *t, bool neg2, int dbits, bool active = true) {
   FormR<N> f1, f2, r;
   fr_unpack<N>(f1, x);
   if (!DUPL) fr_unpack<N>(f2, t);
-  bool ok = fq_compose<N, DUPL, SYNC>(r, f1, DUPL ? f1 : f2, neg2, dbits);
+  bool ok = fq_compose<N, DUPL, SYNC, FLAT>(r, f1, DUPL ? f1 : f2, neg2, dbits);
   if (!active) return true;
   if (ok) fr_pack<N>(x, r);
   else {
@@ -162,7 +162,7 @@ QF_HD u32 exp_digit(const u32 *e, int el, size_t stride, int win, int w) {
 // (threads whose leading digits are zero idle until their first non-zero digit).
 // tab = per-thread scratch of (2^W - 1) packed forms f^1 .. f^(2^W-1).
 // Returns false when a step fails even on the robust path, or when e == 0 (the neutral form does not fit the register shape: robust path).
-template <int N, int CAP, int W>
+template <int N, int CAP, int W, bool FLAT = false>
 QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32 *e, int el, size_t stride, int dbits, u32 *tab) {
   constexpr int TE = 3 * N + 1, NT = (1 << W) - 1;
   int win = (32 * el + W - 1) / W - 1;
@@ -186,9 +186,9 @@ QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32
     // window position only); who takes part is not.
     const bool sq_phase = built < NT ? built == 1 : sq_left > 0;
     if (sq_phase) {
-      if (QF_BLOCK_ANY(op == 1)) { bool k = cc_compose<N, CAP, true, true>(G, xb, xb, false, dbits, op == 1); if (op == 1) ok = k; }
+      if (QF_BLOCK_ANY(op == 1)) { bool k = cc_compose<N, CAP, true, true, FLAT>(G, xb, xb, false, dbits, op == 1); if (op == 1) ok = k; }
     } else {
-      if (QF_BLOCK_ANY(op == 2)) { bool k = cc_compose<N, CAP, false, true>(G, xb, tab + src * TE, false, dbits, op == 2); if (op == 2) ok = k; }
+      if (QF_BLOCK_ANY(op == 2)) { bool k = cc_compose<N, CAP, false, true, FLAT>(G, xb, tab + src * TE, false, dbits, op == 2); if (op == 2) ok = k; }
     }
     if (op == 3) {
       QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = tab[src * TE + i];

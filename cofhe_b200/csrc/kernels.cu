@@ -83,7 +83,7 @@ struct cofhe_b200_ctx {
   struct Block { void *p; size_t bytes; };
   std::vector<Block> live, pool;
   size_t pool_bytes = 0;
-  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop, coop_mb, coop_pb, fast_block; } opt;
+  struct Opt { long no_fast, mm_w, mm_chunks, mm_block, fb_w, host_staged, host_loadc, host_chunks, host_trace, coop, coop_mb, coop_pb, fast_block, fast_flat; } opt;
 };
 
 namespace {
@@ -393,7 +393,10 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
       // measured at T0 (profiles/r2n_quick_time.txt): 256-thread blocks +6-7 % from 2^18 compositions, 512 slower everywhere
       const int wide = (ctx->opt.fast_block == 256 || ctx->opt.fast_block == 512) ? (int)ctx->opt.fast_block
                        : (ctx->opt.fast_block == 128 ? 0 : ((size_t)ny * n >= 200000 ? 256 : 0));
-      if (op < 2) K::compose(op == 1, grid, st, gs.G, dbits, nc, n, in1, in2, out, neg2 | (wide << 8), ctx->d_bail, cnt);
+      // branch-free scalar Euclid rounds: -5 % on launches that last as long as one warp (up to ~1.5 warps per scheduler),
+      // +3-6 % once the machine is full (profiles/r2o_quick_time.txt); automatic by batch size unless the option says otherwise
+      const bool flat = ctx->opt.fast_flat == 1 || (ctx->opt.fast_flat < 0 && !wide && (size_t)ny * n <= 49152);
+      if (op < 2) K::compose(op == 1, grid, st, gs.G, dbits, nc, n, in1, in2, out, neg2 | (wide << 8) | (flat ? (1 << 20) : 0), ctx->d_bail, cnt);
       else K::pow(dim3((unsigned)((n + pb - 1) / pb), ny), pb, st, gs.G, dbits, nc, n, in1, out, exp, el, per_elem, expneg,
                   shared_neg, ctx->d_bail, cnt);
     })
@@ -691,6 +694,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->opt.coop_mb = env_opt("COFHE_B200_COOP_MB", 3, 24);
   ctx->opt.coop_pb = env_opt("COFHE_B200_COOP_PB", 128, 256);
   ctx->opt.fast_block = env_opt("COFHE_B200_FAST_BLOCK", 128, 512);
+  ctx->opt.fast_flat = env_opt("COFHE_B200_FAST_FLAT", 0, 1);
   ctx->device = device;
   ctx->sms = 0;
   if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) { cudaGetLastError(); ctx->sms = 0; }
@@ -808,7 +812,7 @@ int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value) {
   struct { const char *n; long *p; } tab[] = {
       {"mm_w", &ctx->opt.mm_w}, {"mm_chunks", &ctx->opt.mm_chunks}, {"mm_block", &ctx->opt.mm_block}, {"fb_w", &ctx->opt.fb_w},
       {"host_staged", &ctx->opt.host_staged}, {"host_loadc", &ctx->opt.host_loadc}, {"host_chunks", &ctx->opt.host_chunks},
-      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}, {"coop_mb", &ctx->opt.coop_mb}, {"coop_pb", &ctx->opt.coop_pb}, {"fast_block", &ctx->opt.fast_block}};
+      {"host_trace", &ctx->opt.host_trace}, {"coop", &ctx->opt.coop}, {"coop_mb", &ctx->opt.coop_mb}, {"coop_pb", &ctx->opt.coop_pb}, {"fast_block", &ctx->opt.fast_block}, {"fast_flat", &ctx->opt.fast_flat}};
   for (auto &t : tab)
     if (!strcmp(t.n, name)) { *t.p = value; return COFHE_B200_OK; }
   return COFHE_B200_EINVAL;

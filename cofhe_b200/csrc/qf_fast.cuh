@@ -144,6 +144,50 @@ QF_HD Mat2 hgcd32(u32 ah, u32 bh, u32 min_r) {
   return m;
 }
 
+
+// hgcd32 without branches (the cooperative path uses the same routine: coop_qf.cuh hgcd32_flat): QF_HG_PAIRS double steps
+// are always executed, a step that is not accepted switches the rest off; the accepted steps -- and so the matrix -- are
+// those of hgcd32<false>.  Experimental on the register path (option "fast_flat"): no divergence inside the round, at the
+// price of predicated work in the lanes that stopped early.
+QF_HD Mat2 hgcd32_nb(u32 ah, u32 bh, u32 min_r, bool on) {
+  u32 rp = ah, rc = bh;
+  u32 Sp = 1, Tp = 0, Sc = 0, Tc = 1;
+  const u32 lim = min_r > 2u ? min_r : 2u;
+  const float kLow = 0.99999905f;
+  float fprev = (float)rp * kLow;
+  int j = 1;
+  bool go = on;
+#define QF_NB_STEP(RP, SP, TP, RC, SC, TC, ODD)                                                        \
+  {                                                                                                    \
+    bool ok = go && RC >= lim;                                                                         \
+    float fcur = (float)(RC | (ok ? 0u : 1u));                                                         \
+    float qf = fprev * rcp_approx(fcur);                                                               \
+    ok = ok && (qf < 524288.0f);                                                                       \
+    u32 q = ok ? (u32)qf : 0u;                                                                         \
+    u32 rn = RP - q * RC;                                                                              \
+    bool fixq = ok && rn >= RC;                                                                        \
+    q += fixq ? 1u : 0u;                                                                               \
+    rn -= fixq ? RC : 0u;                                                                              \
+    u32 Sn = q * SC + SP, Tn = q * TC + TP;                                                            \
+    ok = ok && (ODD ? (rn >= Tn && RC - rn >= Sn + SC) : (rn >= Sn && RC - rn >= Tn + TC));            \
+    RP = ok ? rn : RP; SP = ok ? Sn : SP; TP = ok ? Tn : TP;                                           \
+    fprev = ok ? fcur * kLow : fprev;                                                                  \
+    j += ok ? 1 : 0;                                                                                   \
+    go = ok;                                                                                           \
+  }
+  QF_UNROLL for (int it = 0; it < QF_HG_PAIRS; it++) {
+    QF_NB_STEP(rp, Sp, Tp, rc, Sc, Tc, true)
+    QF_NB_STEP(rc, Sc, Tc, rp, Sp, Tp, false)
+  }
+#undef QF_NB_STEP
+  const bool swapped = ((j - 1) & 1) != 0;
+  Mat2 m;
+  m.S0 = swapped ? Sc : Sp; m.T0 = swapped ? Tc : Tp;
+  m.S1 = swapped ? Sp : Sc; m.T1 = swapped ? Tp : Tc;
+  m.j = j;
+  return m;
+}
+
 // r = |x*A - y*B| where the sign is known: neg == true means the combination is <= 0.  x, y < 2^30.
 // Both products run as carry chains of 32x32+64 multiply-adds (one IMAD.WIDE per limb), then one borrow chain.
 template <int N>
@@ -179,7 +223,7 @@ QF_HD u32 fw_lin_add(u32 *r, u32 x, const u32 *A, u32 y, const u32 *B) {
 // Half-extended Euclid on fixed-width magnitudes, same contract as z_hxgcd (lehmer.cuh): in (R0 >= R1, C0, C1),
 // runs until the first remainder with bits <= stop_bits, returns the number of Euclidean steps.  `bail` is
 // raised when the sequence needs something this path does not do (a 31+ bit quotient, cofactor overflow).
-template <int N, int NC>
+template <int N, int NC, bool FLAT = false>
 QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail) {
   int lsh = fw_lead_zero_limbs<N>(R0);
   if (lsh >= N) { { bail = true; QF_NOTE; } return 0; }
@@ -219,6 +263,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       int h = 32 * (N - 1) - sh;
       u32 min_r = sb > h ? (1u << (sb - h)) : 0u;
       if (exact) M = hgcd32<true>(ah, bh, min_r);
+      else if (FLAT) M = hgcd32_nb(ah, bh, min_r, true);
       else M = hgcd32<false>(ah, bh, min_r);
       QF_STAT(0);
     }
@@ -400,7 +445,7 @@ QF_HD bool fw_reduce(u32 *a, u32 *b, u32 *c, int dbits) {
 #else
 #define QF_PHASE() ((void)0)
 #endif
-template <int N, bool DUPL, bool SYNC = false>
+template <int N, bool DUPL, bool SYNC = false, bool FLAT = false>
 QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool neg2, int dbits) {
   constexpr int W = N + 1;
   constexpr int M = (N + 1) / 2 + 1;  // half width of the post-Euclid quantities
@@ -447,7 +492,7 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
       if (fw_lt<N>(R0, R1)) QF_BAIL;
     }
     fw_zero<N>(Cv); fw_zero<N>(C1); C1[0] = 1;
-    st1 = fw_hxgcd<N, N>(R0, R1, Cv, C1, 0, bail);
+    st1 = fw_hxgcd<N, N, FLAT>(R0, R1, Cv, C1, 0, bail);
     if (bail) QF_BAIL;
     if (!fw_high_zero<N, 1>(R0)) QF_BAIL;  // gcd >= 2^32: robust path
     return true;
@@ -566,7 +611,7 @@ QF_HD bool fq_compose(FormR<N> &r, const FormR<N> &f1, const FormR<N> &f2, bool 
     int stop = (ba1 - ba2) / 2 + dbits / 4;
     if (stop < 1) stop = 1;
     fw_zero<M>(C0); fw_zero<M>(C1); C1[0] = 1;
-    st = fw_hxgcd<N, M>(By, Bx, C0, C1, stop, bail);  // (By, Bx) <- (R_{i-1}, R_i)
+    st = fw_hxgcd<N, M, FLAT>(By, Bx, C0, C1, stop, bail);  // (By, Bx) <- (R_{i-1}, R_i)
     if (bail) { QF_NOTE; ok = false; }
   }
   QF_PHASE();

@@ -77,7 +77,8 @@ int cofhe_b200_reg_limbs(const cofhe_b200_ctx *ctx);
  * kernels for every form operation, 0: never), "coop_mb" (3/4/5: resident blocks per SM the cooperative composition is compiled for; 14: 4 with block barriers
  * between the phases, 24: the same in 256-thread blocks; default 14 / 24 by batch size), "coop_pb" (128 / 256: threads
  * per block of the cooperative exponentiation and table kernels), "fast_block" (128 / 256 / 512: threads per block of the
- * register composition kernel; default 128, 256 from 200 000 compositions per launch).  They change how the work
+ * register composition kernel; default 128, 256 from 200 000 compositions per launch), "fast_flat" (1 / 0: branch-free
+ * scalar Euclid rounds in that kernel; default on up to 49 152 compositions per launch).  They change how the work
  * is laid out, never the results.  The COFHE_B200_<NAME> environment variables give the defaults at creation. */
 int cofhe_b200_set_option(cofhe_b200_ctx *ctx, const char *name, long value);
 

@@ -180,3 +180,34 @@ def test_fast_pow_kat_and_fixtures():
             if not bail[i]:
                 assert got[i] == O.power(vs[i][0], e)
     assert ran >= 100
+
+
+def test_fast_flat_variant(tier):
+    """the branch-free scalar Euclid rounds (hgcd32_nb; what the composition kernel runs on small batches): same accepted
+    steps, same results as the reference fixtures"""
+    S = FastSim(int(tier["params"]["Delta"]))
+    if not S.ok():
+        pytest.skip("no fast instantiation for %d limbs" % S.na)
+    vs = tier["compose"] + tier["compose_edge"]
+    f1, f2 = [I(v["f1"]) for v in vs], [I(v["f2"]) for v in vs]
+    S.lib.hs_fast_flat(1)
+    try:
+        g, b = S.run(f1, f2); check(g, b, [I(v["r"]) for v in vs])
+        assert int(b[:len(tier["compose"])].sum()) == 0
+        g, b = S.run(f1, f2, inv=True); check(g, b, [I(v["rinv"]) for v in vs])
+        g, b = S.run(f1, dupl=True); check(g, b, [I(v["sq"]) for v in vs])
+        # a longer chain against the oracle
+        rng = random.Random(4)
+        fs = [f1[rng.randrange(len(tier["compose"]))] for _ in range(64)]
+        gs = [f2[rng.randrange(len(tier["compose"]))] for _ in range(64)]
+        for _ in range(6):
+            out, bail = S.run(fs, gs)
+            S.lib.hs_fast_flat(0)
+            out0, bail0 = S.run(fs, gs)
+            S.lib.hs_fast_flat(1)
+            assert list(bail) == list(bail0)   # the same steps are accepted, so the same elements are declined
+            want = [O.compose(x, y) for x, y in zip(fs, gs)]
+            check(out, bail, want)
+            fs = want
+    finally:
+        S.lib.hs_fast_flat(0)

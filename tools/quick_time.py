@@ -33,13 +33,15 @@ for n in sizes:
     G.status()
     out = torch.empty_like(f)
     ref = None
-    for fb in (128, 256, 512):   # threads per block of the register composition kernel
-        G.set_option("fast_block", fb)
+    for fb in (128, 256, 1128):   # threads per block of the register composition kernel; 1128: 128 + branch-free Euclid rounds
+        G.set_option("fast_block", fb % 1000)
+        G.set_option("fast_flat", 1 if fb > 1000 else 0)
         dt = timeit(lambda: G.nucomp(f, g, out=out)); print("n=%d block=%d nucomp  %.3f ms  %.1f M/s" % (n, fb, dt * 1e3, n / dt / 1e6))
         if ref is None: ref = out.clone()
         else: assert torch.equal(ref, out)
         dt = timeit(lambda: G.nudupl(f, out=out)); print("n=%d block=%d nudupl  %.3f ms  %.1f M/s" % (n, fb, dt * 1e3, n / dt / 1e6))
     G.set_option("fast_block", -1)
+    G.set_option("fast_flat", -1)
     e = int(t["sk"])
     dt = timeit(lambda: G.nupow(f, shared=e), reps=2); print("n=%d nupow(%d bits shared) %.3f ms  %.1f k/s" % (n, e.bit_length(), dt * 1e3, n / dt / 1e3))
     G.status()
