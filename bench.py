@@ -422,7 +422,7 @@ def matmul_metric(args, G, fx, s, world, rank, imad_peak):
     from cofhe_b200.group import to_device, to_host
     n, m, p = MM
     if not G.reg:
-        n = 8 * world  # no table kernels at this width (generic path): 8 ct rows per GPU of the same 256-wide problem
+        n = 8 * world  # the 2053-bit tier (cooperative kernels, 25x the arithmetic per unit): 8 ct rows per GPU of the same 256-wide problem
     rows = n // world
     units = 2 * n * m * p
     sc = [i + 1 for i in range(m * p)]
