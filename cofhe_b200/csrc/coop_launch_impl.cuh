@@ -124,7 +124,11 @@ size_t CoopKernels<T, L, N, CAP>::pow_tab_words(unsigned ny, int nc, size_t n) {
 template <int T, int L, int N, int CAP>
 void CoopKernels<T, L, N, CAP>::pow(unsigned ny, cudaStream_t st, const void *G, int dbits, int nc, size_t n, const u32 *in, u32 *out, const u32 *exp, int el,
                                     int per_elem, const unsigned char *expneg, int shared_neg, u32 *tab, u32 *bail, int *nbail, int block) {
-  if (block == 256) {
+  if (block == 4) {  // 128 threads, compiled for 4 blocks per SM (128 registers)
+    constexpr int GPB = kCoopBlock / T;
+    dim3 grid((unsigned)((n + GPB - 1) / GPB), ny);
+    k_coop_pow<T, L, N, CAP, 4><<<grid, kCoopBlock, 0, st>>>((const Group<CAP> *)G, dbits, nc, n, in, out, exp, el, per_elem, expneg, shared_neg, tab, bail, nbail);
+  } else if (block == 256) {
     constexpr int GPB = 256 / T;
     dim3 grid((unsigned)((n + GPB - 1) / GPB), ny);
     k_coop_pow<T, L, N, CAP, 2, 256><<<grid, 256, 0, st>>>((const Group<CAP> *)G, dbits, nc, n, in, out, exp, el, per_elem, expneg, shared_neg, tab, bail, nbail);

@@ -375,6 +375,11 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
       if (op < 2) K::compose(op == 1, ny, st, gs.G, dbits, nc, n, in1, in2, out, neg2, ctx->d_bail, cnt,
                              ctx->opt.coop_mb > 0 ? (int)ctx->opt.coop_mb : ((size_t)ny * n >= 98304 ? 24 : 14));
       else {
+        // 256-thread blocks once every SM gets one (measured at T1: 16 384 exponentiations 690 -> 521 ms, 65 536: 2.06 -> 1.79 s;
+        // 2 048: 301 -> 353 ms)
+        const size_t pow_lanes = ctx->coopn >= 33 ? 4 : 2;
+        const int pow_block = ctx->opt.coop_pb == 256 ? 256 : (ctx->opt.coop_pb == 4 ? 4 : (ctx->opt.coop_pb == 128 ? 128 :
+                              ((size_t)ny * n >= (size_t)(ctx->sms > 0 ? ctx->sms : 148) * (256 / pow_lanes) ? 256 : 128)));
         size_t tw = K::pow_tab_words(ny, nc, n) * sizeof(u32);
         if (tw > ctx->powtab_bytes) {
           if (ctx->d_powtab) cudaFree(ctx->d_powtab);
@@ -382,7 +387,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
           if (cudaMalloc(&ctx->d_powtab, tw) != cudaSuccess) { cudaGetLastError(); return COFHE_B200_ENOMEM; }
           ctx->powtab_bytes = tw;
         }
-        K::pow(ny, st, gs.G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_powtab, ctx->d_bail, cnt, ctx->opt.coop_pb == 256 ? 256 : 128);
+        K::pow(ny, st, gs.G, dbits, nc, n, in1, out, exp, el, per_elem, expneg, shared_neg, ctx->d_powtab, ctx->d_bail, cnt, pow_block);
       }
     })
   } else {
@@ -692,7 +697,7 @@ int cofhe_b200_create(cofhe_b200_ctx **out, int device, const uint32_t *abs_delt
   ctx->opt.host_trace = getenv("COFHE_B200_HOST_TRACE") ? 1 : 0;
   ctx->opt.coop = env_opt("COFHE_B200_COOP", 0, 1);
   ctx->opt.coop_mb = env_opt("COFHE_B200_COOP_MB", 3, 24);
-  ctx->opt.coop_pb = env_opt("COFHE_B200_COOP_PB", 128, 256);
+  ctx->opt.coop_pb = env_opt("COFHE_B200_COOP_PB", 4, 256);
   ctx->opt.fast_block = env_opt("COFHE_B200_FAST_BLOCK", 128, 512);
   ctx->opt.fast_flat = env_opt("COFHE_B200_FAST_FLAT", 0, 1);
   ctx->device = device;

@@ -29,9 +29,9 @@ for tier in (sys.argv[1:] or ["t1", "t0"]):
         ms = [rng.getrandbits(int(p["k"])) for _ in range(n)]
         ct = G.encrypt(ms, rng.randrange(1, int(p["exponent_bound"])))
         G.status()
-        for mode in ((0, 1, 256) if int(G.lib.cofhe_b200_coop_limbs(G.h)) else (0,)):   # 256: cooperative kernels in 256-thread blocks
+        for mode in ((0, 1, 256, 4) if int(G.lib.cofhe_b200_coop_limbs(G.h)) else (0,)):   # 256: cooperative kernels in 256-thread blocks; 4: 128 threads, 4 blocks per SM
             G.set_option("coop", 1 if mode else 0)
-            G.set_option("coop_pb", 256 if mode == 256 else 128)
+            G.set_option("coop_pb", mode if mode in (256, 4) else 128)
             dt = timeit(lambda: G.part_decrypt(ct, sk))
             G.status()
             dd = timeit(lambda: G.decrypt(ct, sk), reps=1)
