@@ -18,6 +18,7 @@
 #ifndef COFHE_B200_CUDA_CRYPTO_SYSTEM_HPP_INCLUDED
 #define COFHE_B200_CUDA_CRYPTO_SYSTEM_HPP_INCLUDED
 
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <cstring>
@@ -332,6 +333,8 @@ namespace CoFHE
         const BICYCL::CL_HSM2k &get_hsm2k() const { return host_.get_hsm2k(); }
         // launches issued by this object's device context so far
         uint64_t gpu_launches() const { return cofhe_b200_launch_count(ctx_); }
+        // concurrency lanes in use (1 = only this object's own context; see lanes_)
+        size_t num_lanes() const { std::lock_guard<std::mutex> lk(lanes_mu_); return 1 + lanes_.size(); }
 
         // ---- device side: the batched entry points (definitions below) --------------------------------------------
         Vector<CipherText *> encrypt_vector(const PublicKey &pk, const Vector<PlainText *> &pt) const;
@@ -391,6 +394,14 @@ namespace CoFHE
         mutable std::atomic<bool> marshal_err_{false}; // set by put_int inside OpenMP loops, thrown by check_marshal
         mutable std::mutex mu_;        // one call at a time per context (the reference's methods are const and are
                                        // called from 8 server threads: node/server.hpp:16,187-196)
+        // Concurrency lanes: a call that finds this object busy runs on a twin of it (same device, own context, stream, staging
+        // arena and fixed-base tables), so that the server's threads do not queue behind one stream.  Twins are created on
+        // first contention, at most max_lanes_ - 1 of them (COFHE_B200_LANES, default 4; 1 = the single mutex of before).
+        // The RandGen stays on this object: draws are made before a call is handed to a lane.
+        mutable std::atomic<int> busy_{0};
+        mutable std::mutex lanes_mu_;
+        mutable std::vector<std::unique_ptr<B200CryptoSystem>> lanes_;
+        int max_lanes_ = 4;
         mutable bool pk_set_ = false;
         mutable BICYCL::QFI pk_cached_;
         // staging arena: pinned host memory + device memory of the same size, grown on demand
@@ -451,6 +462,8 @@ namespace CoFHE
             pk_set_ = false;
             if (is_peer_)
                 return;
+            if (const char *le = std::getenv("COFHE_B200_LANES"))
+                max_lanes_ = std::max(1, std::min(16, std::atoi(le)));
             if (devices_.empty())
             {
                 const char *env = std::getenv("COFHE_B200_DEVICES");
@@ -479,6 +492,7 @@ namespace CoFHE
         void close()
         {
             peers_.clear();
+            lanes_.clear();
             if (ctx_)
             {
                 if (d_arena_)
@@ -616,7 +630,26 @@ namespace CoFHE
             const size_t G = 1 + peers_.size();
             if (G == 1 || n < G * min_per_device)
             {
-                body(*this, (size_t)0, n);
+                // the whole call on one device: this object if it is free, else a free twin of it (see lanes_)
+                struct Release { std::atomic<int> *b; ~Release() { if (b) b->store(0); } };
+                const B200CryptoSystem *o = this;
+                Release rel{nullptr};
+                if (busy_.exchange(1) == 0)
+                    rel.b = &busy_;
+                else if (!is_peer_ && max_lanes_ > 1)
+                {
+                    std::lock_guard<std::mutex> lk(lanes_mu_);
+                    for (auto &l : lanes_)
+                        if (l->busy_.exchange(1) == 0) { o = l.get(); rel.b = &l->busy_; break; }
+                    if (o == this && (int)lanes_.size() + 1 < max_lanes_)
+                    {
+                        lanes_.emplace_back(new B200CryptoSystem(host_, device_, true));
+                        lanes_.back()->busy_.store(1);
+                        o = lanes_.back().get();
+                        rel.b = &lanes_.back()->busy_;
+                    }
+                }
+                body(*o, (size_t)0, n);  // every lane busy: queue on this object's mutex as before
                 return;
             }
             std::vector<std::exception_ptr> errs(G);

@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <thread>
 using namespace CoFHE;
 namespace {
 typedef B200CryptoSystem::CipherText CT;
@@ -114,8 +115,63 @@ int bench(int argc, char** argv) {
   return bad != 0;
 }
 }  // namespace
+// --threads T ROWS COLS ITERS: T host threads share ONE B200CryptoSystem, as the reference's server does with its 8 worker
+// threads (include/node/server.hpp:16,187-196); each chains ITERS add_ciphertext_tensors on its own ROWS x COLS tensor and
+// part-decrypts the result.  Results are compared with the reference class; the same work is also timed from one thread.
+int threads_mode(int argc, char** argv) {
+  if (argc < 6) return 2;
+  size_t T = atoi(argv[2]), rows = atoi(argv[3]), cols = atoi(argv[4]), iters = atoi(argv[5]);
+  B200CryptoSystem cs(128, 128);
+  CPUCryptoSystem ref(128, 128);
+  auto sk = cs.keygen(); auto pk = cs.keygen(sk);
+  auto sk2 = ref.keygen(); auto pk2 = ref.keygen(sk2);
+  auto shares = cs.keygen(sk, 3, 5);
+  const Tensor<CT*> e1(1, nullptr);
+  const Tensor<B200CryptoSystem::PartDecryptionResult*> e2(1, nullptr);
+  std::vector<Tensor<CT*>> in(T, e1), want(T, e1), got(T, e1);
+  std::vector<Tensor<B200CryptoSystem::PartDecryptionResult*>> wantp(T, e2), gotp(T, e2);
+  for (size_t t = 0; t < T; t++) {
+    auto pt = pattern(rows, cols);
+    in[t] = ref.encrypt_tensor(pk2, pt);
+    Tensor<CT*> r = ref.add_ciphertext_tensors(pk2, in[t], in[t]);
+    for (size_t i = 1; i < iters; i++) { auto nx = ref.add_ciphertext_tensors(pk2, r, in[t]); free_cts(r); r = nx; }
+    want[t] = r;
+    wantp[t] = ref.part_decrypt_tensor(shares[0][0], r);
+  }
+  auto work = [&](size_t t) {
+    Tensor<CT*> r = cs.add_ciphertext_tensors(pk, in[t], in[t]);
+    for (size_t i = 1; i < iters; i++) { auto nx = cs.add_ciphertext_tensors(pk, r, in[t]); free_cts(r); r = nx; }
+    got[t] = r;
+    gotp[t] = cs.part_decrypt_tensor(shares[0][0], r);
+  };
+  work(0);  // warm-up: tables, arenas
+  free_cts(got[0]);
+  double t0 = now();
+  for (size_t t = 0; t < T; t++) { work(t); if (t + 1 < T) free_cts(got[t]); }
+  double seq = now() - t0;
+  free_cts(got[T - 1]);
+  std::vector<std::exception_ptr> errs(T);
+  t0 = now();
+  {
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < T; t++) th.emplace_back([&, t]() { try { work(t); } catch (...) { errs[t] = std::current_exception(); } });
+    for (auto& x : th) x.join();
+  }
+  double par = now() - t0;
+  size_t bad = 0;
+  for (size_t t = 0; t < T; t++) {
+    if (errs[t]) { bad += 1000; continue; }
+    bad += diff(got[t], want[t]);
+    auto a = gotp[t], b = wantp[t]; a.flatten(); b.flatten();
+    for (size_t i = 0; i < a.num_elements(); i++) bad += !(*a.at(i) == *b.at(i));
+  }
+  std::cout << "{\"threads\": " << T << ", \"shape\": [" << rows << ", " << cols << "], \"iters\": " << iters << ", \"one_thread_s\": " << seq
+            << ", \"threads_s\": " << par << ", \"lanes\": " << cs.num_lanes() << ", \"mismatches\": " << bad << "}" << std::endl;
+  return bad != 0;
+}
 int main(int argc, char** argv) {
   if (argc > 2 && !strcmp(argv[1], "--bench")) return bench(argc, argv);
+  if (argc > 2 && !strcmp(argv[1], "--threads")) return threads_mode(argc, argv);
   unsigned nbits = argc > 2 ? atoi(argv[1]) : 128, kk = argc > 2 ? atoi(argv[2]) : 128;
   // third argument 1: the compact variant of CL_HSM2k (c1, h, pk in Cl(DeltaK)) on both sides
   const bool compact = argc > 3 && atoi(argv[3]) != 0;

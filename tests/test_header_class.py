@@ -83,3 +83,22 @@ def test_class_bench_parity(args):
     assert r.returncode == 0, r.stdout + r.stderr
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["mismatches"] == 0 and line["launches"] > 0
+
+
+@pytest.mark.gpu
+def test_class_shared_by_threads():
+    """ONE B200CryptoSystem shared by 8 host threads, as the reference's server shares its cryptosystem between its worker
+    threads (include/node/server.hpp:16,187-196): concurrent chained add_ciphertext_tensors + part_decrypt_tensor calls give
+    the reference's results, and run on the object's concurrency lanes instead of queueing on one stream"""
+    if not os.path.exists(BIN):
+        pytest.skip("tests/_cpp/b200_cs_parity was not built")
+    import json
+    r = subprocess.run([BIN, "--threads", "8", "32", "32", "6"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout + r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["mismatches"] == 0 and line["lanes"] >= 2
+    env = dict(os.environ, COFHE_B200_LANES="1")
+    r = subprocess.run([BIN, "--threads", "4", "16", "16", "3"], capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["mismatches"] == 0 and line["lanes"] == 1
