@@ -217,11 +217,12 @@ long env_opt(const char *name, long lo, long hi) {
     case 7: { constexpr int CT = 2, CL = 5, CN = 7, CCAP = 32; __VA_ARGS__; } break;             \
     case 11: { constexpr int CT = 2, CL = 7, CN = 11, CCAP = 48; __VA_ARGS__; } break;           \
     case 33: { constexpr int CT = 4, CL = 9, CN = 33, CCAP = 136; __VA_ARGS__; } break;          \
+    case 53: { constexpr int CT = 8, CL = 7, CN = 53, CCAP = 216; __VA_ARGS__; } break;          \
     default: return COFHE_B200_EINVAL;                                                           \
   }
-#define COOP_HAVE(na) ((na) == 7 || (na) == 11 || (na) == 33)
+#define COOP_HAVE(na) ((na) == 7 || (na) == 11 || (na) == 33 || (na) == 53)
 #endif
-int coop_cap(int cn) { return cn == 33 ? 136 : (cn == 11 ? 48 : 32); }
+int coop_cap(int cn) { return cn == 53 ? 216 : (cn == 33 ? 136 : (cn == 11 ? 48 : 32)); }
 // which path serves a batched form operation: the cooperative kernels where no register instantiation exists (the large
 // discriminants), or when forced ("coop" option: 1 always, 0 never)
 bool use_coop(const cofhe_b200_ctx *ctx) {
@@ -377,7 +378,7 @@ int launch_op(cofhe_b200_ctx *ctx, int op, unsigned ny, size_t n, const u32 *in1
       else {
         // 256-thread blocks once every SM gets one (measured at T1: 16 384 exponentiations 690 -> 521 ms, 65 536: 2.06 -> 1.79 s;
         // 2 048: 301 -> 353 ms)
-        const size_t pow_lanes = ctx->coopn >= 33 ? 4 : 2;
+        const size_t pow_lanes = ctx->coopn >= 53 ? 8 : (ctx->coopn >= 33 ? 4 : 2);
         const int pow_block = ctx->opt.coop_pb == 256 ? 256 : (ctx->opt.coop_pb == 4 ? 4 : (ctx->opt.coop_pb == 128 ? 128 :
                               ((size_t)ny * n >= (size_t)(ctx->sms > 0 ? ctx->sms : 148) * (256 / pow_lanes) ? 256 : 128)));
         size_t tw = K::pow_tab_words(ny, nc, n) * sizeof(u32);
@@ -532,7 +533,7 @@ int coop_mm_eval(cofhe_b200_ctx *ctx, const MMShape &s, const u32 *ct, const u32
   u32 *dst = s.chunks > 1 ? part : out;
   // 256-thread blocks (8 warps aligned by the barriers, two blocks per SM) once every SM gets one: measured at T1, 8 192
   // fixed-base pairs 108 -> 68 ms, 2 048 pairs 39 -> 46 ms
-  const size_t tp_groups = 2 * no * s.chunks, tp_lanes = ctx->coopn >= 33 ? 4 : 2;
+  const size_t tp_groups = 2 * no * s.chunks, tp_lanes = ctx->coopn >= 53 ? 8 : (ctx->coopn >= 33 ? 4 : 2);
   const int tp_block = ctx->opt.coop_pb == 256 ? 256 : (ctx->opt.coop_pb == 128 ? 128 :
                        (tp_groups >= (size_t)(ctx->sms > 0 ? ctx->sms : 148) * (256 / tp_lanes) ? 256 : 128));
   COOP_DISPATCH(ctx->coopn, {
@@ -953,7 +954,7 @@ int cofhe_b200_scal_matmul(cofhe_b200_ctx *ctx, size_t n, size_t m, size_t p, co
     // cooperative kernels: SoA tables, one lane group per (chunk, output); enough chunks of the j range to fill the machine
     // (3 blocks of 128 threads per SM), each extra chunk costs one batched composition per output
     const size_t sms = (size_t)(ctx->sms > 0 ? ctx->sms : 148);
-    const size_t lanes = ctx->coopn >= 33 ? 4 : 2;
+    const size_t lanes = ctx->coopn >= 53 ? 8 : (ctx->coopn >= 33 ? 4 : 2);
     const size_t slots = sms * 3 * (kCoopBlock / lanes);
     size_t ch = (slots + 2 * no - 1) / (2 * no);
     if (ch > m) ch = m;

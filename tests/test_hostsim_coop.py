@@ -157,3 +157,18 @@ def test_coop_slow_compose_fallback(tier):
                     assert b[i]
     finally:
         lib.hs_coop_force_slow(0)
+
+
+def test_coop_t2_shape():
+    """the 8-lane x 7-limb shape of the 53-limb coefficients (N of 3072 bits: |Delta| = 3333 bits) against reference vectors"""
+    t = load_golden("ref_t2.json")
+    S = CoopSim(int(t["params"]["Delta"]), 8, 7)
+    assert S.na == 53
+    vs = t["compose"] + t["compose_edge"]
+    nr = len(t["compose"])
+    f1, f2 = [I(v["f1"]) for v in vs], [I(v["f2"]) for v in vs]
+    g, b = S.run(f1, f2); check(g, b, [I(v["r"]) for v in vs])
+    assert int(b[:nr].sum()) == 0
+    g, b = S.run(f1, f2, inv=True); check(g, b, [I(v["rinv"]) for v in vs])
+    g, b = S.run(f1, dupl=True); check(g, b, [I(v["sq"]) for v in vs])
+    assert int(b[:nr].sum()) == 0
