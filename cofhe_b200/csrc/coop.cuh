@@ -153,9 +153,15 @@ CG_FN i64 g_propagate(const Grp<T> &g, u32 *x, i64 cw) {
     } else {
       c = (i64)(int)g_up<T>(g, (u32)cw, 0);
     }
-    QF_UNROLL for (int i = 0; i < L; i++) { c += x[i]; x[i] = (u32)c; c >>= 32; }
+    // the word lands in limb 0; what it pushes on is -1, 0 or +1 and dies in limb 1 unless that limb is all zeros / all ones
+    // (2^-32): the remaining limbs are touched only when some lane of the warp still carries something
+    static_assert(L >= 2, "two limbs absorb the word");
+    c += x[0]; x[0] = (u32)c; c >>= 32;
+    c += x[1]; x[1] = (u32)c; c >>= 32;
+    if (!w_any<T, 90>(g, c != 0)) break;
+    QF_UNROLL for (int i = 2; i < L; i++) { c += x[i]; x[i] = (u32)c; c >>= 32; }
     cw = c;
-    if (!w_any<T, 90>(g, cw != 0)) break;
+    if (!w_any<T, 91>(g, cw != 0)) break;
   }
   return top;
 }
