@@ -25,6 +25,8 @@ EXTRA_SIGS = {
     "hs_scheme": [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                   ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int,
                   ctypes.c_void_p],
+    "hs_coop_tabprod": [ctypes.c_int] * 5 + [ctypes.c_uint] * 3 + [ctypes.c_int] * 3 + [ctypes.c_uint] * 2 + [ctypes.c_void_p, ctypes.c_void_p,
+                        ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p],
     "hs_lift": [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                 ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p],
     "hs_fast_pow": [ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p,

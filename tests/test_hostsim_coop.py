@@ -172,3 +172,52 @@ def test_coop_t2_shape():
     g, b = S.run(f1, f2, inv=True); check(g, b, [I(v["rinv"]) for v in vs])
     g, b = S.run(f1, dupl=True); check(g, b, [I(v["sq"]) for v in vs])
     assert int(b[:nr].sum()) == 0
+
+
+@pytest.mark.parametrize("name,T,LL", [("t0", 2, 5), ("t1", 4, 9)])
+def test_coop_tabprod_body(name, T, LL):
+    """the window-table multi-exponentiation body (cq_tabprod: scal_matmul and fixed base on the cooperative kernels) in the
+    simulator: tables T[d][w][base] = base^(d 2^(W w)) from the oracle, a 2 x 3 . 3 x 2 product with an `init` ciphertext half,
+    two chunks of the inner index, zero digits and a zero scalar; partial products against the oracle"""
+    t = load_golden("ref_%s.json" % name)
+    D = int(t["params"]["Delta"])
+    S = CoopSim(D, T, LL)
+    lib = S.lib
+    n, m, p, W = 2, 3, 2, 2
+    rng = random.Random(12)
+    bases = [I(v["f1"]) for v in t["compose"][:n * m]]
+    sc = [rng.getrandbits(7) for _ in range(m * p)]
+    sc[1] = 0
+    sc[2] = 0b0100011
+    el, nwin, nt = 1, 4, (1 << W) - 1
+    nb = n * m
+    ne = nt * nwin * nb
+    ent = [None] * ne
+    for b in range(nb):
+        for w in range(nwin):
+            for d in range(1, nt + 1):
+                ent[(d - 1) * nwin * nb + w * nb + b] = O.power(bases[b], d << (W * w))
+    tab = L.forms_to_limbs(ent, S.na, S.nc)
+    init = I(t["compose"][7]["f1"])
+    initl = L.forms_to_limbs([init], S.na, S.nc)
+    scal = L.ints_to_limbs(sc, el)
+    chunks, jper = 2, 2
+    fl = 2 * S.na + S.nc
+    out = np.zeros((chunks, fl, n * p), dtype=np.uint32)
+    flagged = np.zeros(chunks * n * p, dtype=np.uint8)
+    nbad = lib.hs_coop_tabprod(T, LL, S.na, S.dbits, S.nc, n, m, p, nwin, W, el, chunks, jper, HS.P(scal), HS.P(tab), ne, HS.P(initl), HS.P(out), HS.P(flagged))
+    assert nbad >= 0
+    for c in range(chunks):
+        got = L.limbs_to_forms(out[c], S.na, S.nc)
+        for i in range(n):
+            for k in range(p):
+                o = i * p + k
+                acc = init if c == 0 else None
+                for j in range(c * jper, min((c + 1) * jper, m)):
+                    if sc[j * p + k]:
+                        f = O.power(bases[i * m + j], sc[j * p + k])
+                        acc = f if acc is None else O.compose(acc, f)
+                if acc is None:
+                    assert flagged[c * n * p + o]      # empty product: robust path
+                else:
+                    assert not flagged[c * n * p + o] and got[o] == acc, (c, i, k)
