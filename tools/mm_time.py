@@ -12,9 +12,11 @@ shapes = [tuple(int(v) for v in a.split(",")) for a in sys.argv[2:]] or [(8, 64,
 fx = B.fixture(tier)
 t = load_golden("ref_%s.json" % tier)
 G = ClassGroupB200(fx["Delta"])
+G.set_scheme(fx["k"], fx["N"])
+G.set_bases(fx["h"], fx["pk"], fx["bound"].bit_length())
 zero = G.cts([I(t["scal_matmul"][0]["zero"])])
 for (n, m, p) in shapes:
-    ct = B.synth_cts(G, fx, n * m, 5)
+    ct = B.random_cts(G, fx, n * m, 5)
     for label, s in (("pattern i+1", [i + 1 for i in range(m * p)]), ("uniform k-bit", [random.Random(3).getrandbits(fx["k"]) for _ in range(m * p)])):
         G.scal_matmul(ct, s, n, m, p, zero); torch.cuda.synchronize()
         best = 1e9
