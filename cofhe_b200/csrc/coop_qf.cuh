@@ -55,14 +55,12 @@ CG_FN Mat2 hgcd32_flat(u32 ah, u32 bh, u32 min_r, bool on) {
 #define CQ_HG_STEP(RP, SP, TP, RC, SC, TC, ODD)                                                        \
   {                                                                                                    \
     bool ok = go && RC >= lim;                                                                         \
-    float fcur = (float)(RC | (ok ? 0u : 1u));                                                         \
+    float fcur = (float)RC;                                                                            \
     float qf = fprev * rcp_approx(fcur);                                                               \
     ok = ok && (qf < 524288.0f);                                                                       \
-    u32 q = ok ? (u32)qf : 0u;                                                                         \
+    u32 q = hg_quotient(qf);                                                                           \
     u32 rn = RP - q * RC;                                                                              \
-    bool fixq = ok && rn >= RC;                                                                        \
-    q += fixq ? 1u : 0u;                                                                               \
-    rn -= fixq ? RC : 0u;                                                                              \
+    hg_fixup(q, rn, RC);                                                                               \
     u32 Sn, Tn;                                                                                        \
     if (EXACT) {                                                                                       \
       u64 S64 = (u64)q * SC + SP, T64 = (u64)q * TC + TP;                                              \
@@ -70,10 +68,10 @@ CG_FN Mat2 hgcd32_flat(u32 ah, u32 bh, u32 min_r, bool on) {
       Sn = (u32)S64; Tn = (u32)T64;                                                                    \
     } else {                                                                                           \
       Sn = q * SC + SP; Tn = q * TC + TP;                                                              \
-      ok = ok && (ODD ? (rn >= Tn && RC - rn >= Sn + SC) : (rn >= Sn && RC - rn >= Tn + TC));          \
+      ok = ODD ? (ok & (rn >= Tn) & (RC - rn >= Sn + SC)) : (ok & (rn >= Sn) & (RC - rn >= Tn + TC));  \
     }                                                                                                  \
     RP = ok ? rn : RP; SP = ok ? Sn : SP; TP = ok ? Tn : TP;                                           \
-    fprev = ok ? fcur * kLow : fprev;                                                                  \
+    fprev = fcur * kLow; /* after a refused step every later one is off: no select needed */           \
     j += ok ? 1 : 0;                                                                                   \
     go = ok;                                                                                           \
   }

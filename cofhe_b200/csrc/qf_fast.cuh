@@ -75,6 +75,28 @@ QF_HD float rcp_approx(float x) {
 #endif
 }
 
+// A branch-free Euclid step that is switched off never keeps what it computes (the selects at its end), so its divisor
+// goes into the reciprocal as it is -- 0 gives inf / NaN, which fail the quotient-size test -- and the quotient is
+// converted unguarded.  The device conversion saturates (cvt.rzi.u32.f32: NaN -> 0, too large -> 2^32 - 1); a host build
+// spells out the same values, so the simulator runs exactly what the SM runs.
+QF_HD u32 hg_quotient(float qf) {
+#if defined(__CUDA_ARCH__)
+  return (u32)qf;
+#else
+  return qf >= 4294967296.0f ? 0xffffffffu : (qf >= 0.0f ? (u32)qf : 0u);
+#endif
+}
+
+// The quotient estimate is q or q - 1: if (rn >= rc) { q++; rn -= rc; } as one 64-bit addition of -rc to (q : rn) -- the
+// carry out of the low word is exactly rn >= rc (rc > 0) and lands in q -- and an unsigned minimum that keeps the
+// remainder that did not wrap.
+QF_HD void hg_fixup(u32 &q, u32 &rn, u32 rc) {
+  u64 t = (((u64)q << 32) | rn) + (u64)(u32)(0u - rc);
+  u32 lo = (u32)t;
+  q = (u32)(t >> 32);
+  rn = lo < rn ? lo : rn;
+}
+
 // Single-precision Lehmer step: as hgcd2 (lehmer.cuh) on 32-bit leading parts; cofactors stay below 2^30.
 //
 // This loop is where a composition spends most of its instructions, so it is written for the SM: the quotient comes
@@ -160,18 +182,16 @@ QF_HD Mat2 hgcd32_nb(u32 ah, u32 bh, u32 min_r, bool on) {
 #define QF_NB_STEP(RP, SP, TP, RC, SC, TC, ODD)                                                        \
   {                                                                                                    \
     bool ok = go && RC >= lim;                                                                         \
-    float fcur = (float)(RC | (ok ? 0u : 1u));                                                         \
+    float fcur = (float)RC;                                                                            \
     float qf = fprev * rcp_approx(fcur);                                                               \
     ok = ok && (qf < 524288.0f);                                                                       \
-    u32 q = ok ? (u32)qf : 0u;                                                                         \
+    u32 q = hg_quotient(qf);                                                                           \
     u32 rn = RP - q * RC;                                                                              \
-    bool fixq = ok && rn >= RC;                                                                        \
-    q += fixq ? 1u : 0u;                                                                               \
-    rn -= fixq ? RC : 0u;                                                                              \
+    hg_fixup(q, rn, RC);                                                                               \
     u32 Sn = q * SC + SP, Tn = q * TC + TP;                                                            \
-    ok = ok && (ODD ? (rn >= Tn && RC - rn >= Sn + SC) : (rn >= Sn && RC - rn >= Tn + TC));            \
+    ok = ODD ? (ok & (rn >= Tn) & (RC - rn >= Sn + SC)) : (ok & (rn >= Sn) & (RC - rn >= Tn + TC));    \
     RP = ok ? rn : RP; SP = ok ? Sn : SP; TP = ok ? Tn : TP;                                           \
-    fprev = ok ? fcur * kLow : fprev;                                                                  \
+    fprev = fcur * kLow; /* after a refused step every later one is off: no select needed */           \
     j += ok ? 1 : 0;                                                                                   \
     go = ok;                                                                                           \
   }
@@ -238,6 +258,12 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
   // everybody meets again after the scalar loop.
   QF_CONVERGE_DECL(lanes);
   bool done = false;
+  // Two passes over the same loop body.  The last rounds of a full gcd run on operands that fit one limb (`exact`: no
+  // truncation, no Jebelean test, a long scalar run), and every lane gets there in a different round: taken where they
+  // fall, those runs execute a handful of lanes at a time (measured: 6.8 % of all issued instructions at 8 of 32
+  // lanes).  So a lane whose operands have come down to one limb waits (`tail` == false) until the others are there or
+  // finished, and the exact rounds of the whole warp then run together.  Per lane the sequence of rounds is unchanged.
+  bool tail = false;
   // invariant at the top of a round: the top limb of R0 is non-zero (operands are kept left-justified by whole limbs)
   for (int guard = 0;; guard++) {
     int b1 = 0;
@@ -249,11 +275,16 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       if (b1 <= sb) done = true;  // includes R1 == 0
       else if (guard >= 80 * N) { bail = true; QF_NOTE; done = true; }
     }
-    if (!QF_ANY(lanes, !done)) break;
+    const bool exact = lsh == N - 1;
+    const bool act = !done && exact == tail;
+    if (!QF_ANY(lanes, act)) {
+      if (tail) break;
+      tail = true;  // warp-uniform: what is left, if anything, are the one-limb lanes
+      continue;
+    }
     Mat2 M;
     M.S0 = 1; M.T0 = 0; M.S1 = 0; M.T1 = 1; M.j = 0;
-    if (!done) {
-      bool exact = lsh == N - 1;
+    if (act) {
       int sh = exact ? 0 : clz32(R0[N - 1]);
       u32 ah = R0[N - 1], bh = R1[N - 1];
       if (sh) {
@@ -268,7 +299,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       QF_STAT(0);
     }
     QF_CONVERGE(lanes);
-    if (!done && M.j == 1) {
+    if (act && M.j == 1) {
       QF_STAT(1);
       // one full-precision division step with a quotient of at most 30 bits (rare: about 1 in 100 compositions)
       int b0 = 32 * N - clz32(R0[N - 1]);
@@ -307,7 +338,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
         fw_copy<NC>(C1, cn);
         steps++;
       } else { bail = true; QF_NOTE; done = true; }
-    } else if (!done) {
+    } else if (act) {
       u32 t0[N], t1[N];
       bool odd = M.j & 1;
       // j odd : X_{j-1} = S0*A - T0*B >= 0 , X_j = T1*B - S1*A >= 0 ; j even: signs flipped
@@ -327,7 +358,7 @@ QF_HD int fw_hxgcd(u32 *R0, u32 *R1, u32 *C0, u32 *C1, int stop_bits, bool &bail
       }
     }
     // renormalise by whole limbs (a round removes at most ~30 bits, so this runs 0 or 1 times)
-    while (!done && R0[N - 1] == 0 && lsh < N - 1) {
+    while (act && !done && R0[N - 1] == 0 && lsh < N - 1) {
       QF_UNROLL for (int i = N - 1; i > 0; i--) { R0[i] = R0[i - 1]; R1[i] = R1[i - 1]; }
       R0[0] = 0; R1[0] = 0;
       lsh++; sb += 32;
