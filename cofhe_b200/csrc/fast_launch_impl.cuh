@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kPowBlock) k_fast_pow(const Group<CAP> *G, int
   u32 tab[((1 << W) - 1) * (3 * N + 1)];
   FormR<N> f, r;
   bool ok = fr_load<N>(f, in + off, nc, n, idx);
-  bool pok = per_elem ? fr_pow<N, CAP, W, FLAT>(G, r, f, exp + idx, el, n, dbits, tab) : fr_pow<N, CAP, W, FLAT>(G, r, f, exp, el, 1, dbits, tab);
+  bool pok = per_elem ? fr_pow<N, CAP, W, FLAT>(G, r, f, exp + idx, el, n, dbits, tab) : fr_pow_shared<N, CAP, W, FLAT>(G, r, f, exp, el, dbits, tab);
   ok = ok && pok;
   if (live) {
     if (ok) {

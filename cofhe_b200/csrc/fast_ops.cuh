@@ -211,4 +211,83 @@ QF_HD bool fr_pow(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32
   return ok && started;
 }
 
+// w <= 32 bits of an exponent starting at bit `bit` (from the least significant end), limbs contiguous
+QF_HD u32 exp_bits(const u32 *e, int el, int bit, int w) {
+  int li = bit >> 5, sh = bit & 31;
+  if (li >= el) return 0;
+  u64 v = e[li];
+  if (li + 1 < el) v |= (u64)e[li + 1] << 32;
+  return (u32)(v >> sh) & (w >= 32 ? 0xffffffffu : ((1u << w) - 1));
+}
+
+// x <- f^|e| for an exponent that the whole launch shares (part_decrypt, decrypt, tensor x scalar): left-to-right SLIDING
+// windows over a table of the odd powers f, f^3, .., f^(2^W - 1).  Every thread decodes the same exponent, so the op
+// sequence is uniform by construction and the windows may start wherever the next set bit is: 2^(W-1) - 1 compositions
+// and one squaring build the table (fixed windows: 2^W - 3 and one), and a window costs one composition per W + 1 bits on
+// average instead of one per W.  For a 105-bit share and W = 4: 104 + 8 + ~21 operations against 104 + 14 + 26.
+// The same two call sites as fr_pow (one squaring, one composition), the same barrier discipline.
+// tab = per-thread scratch of 2^(W-1) + 1 packed forms (the odd powers, then f^2 while the table is built).
+// Returns false when a step fails even on the robust path, or when e == 0 (robust path, as fr_pow).
+template <int N, int CAP, int W, bool FLAT = false>
+QF_HD bool fr_pow_shared(const Group<CAP> *G, FormR<N> &x, const FormR<N> &f, const u32 *e, int el, int dbits, u32 *tab) {
+  constexpr int TE = 3 * N + 1, NT = 1 << (W - 1);
+  int top = -1;
+  for (int i = 0; i < el; i++) if (e[i]) top = 32 * i + 31 - clz32(e[i]);
+  u32 xb[TE];
+  fr_pack<N>(tab, f);
+  fr_pack<N>(xb, f);
+  bool ok = true, started = false, have2 = false;
+  // the table only as far as the exponent can use it (e < 2^W: its odd part is the only window)
+  int nt = NT;
+  if (top >= 0 && top < W) { u32 v = e[0] >> ctz32(e[0]); nt = (int)((v + 1) >> 1); }
+  int built = 1, bit = top, sq_left = 0, pend = -1;
+  while (top >= 0) {
+    // ---- decide: 0 nothing, 1 square x, 2 compose x with table slot `src`, 3 load x from table slot `src`
+    int op = 0, src = 0;
+    if (built < nt) {
+      if (!have2) op = 1;            // x = f -> f^2
+      else { op = 2; src = NT; }     // x = f^(2 built - 1) o f^2
+    } else {
+      if (sq_left == 0 && pend < 0) {
+        if (bit < 0) break;
+        if (!exp_bits(e, el, bit, 1)) { sq_left = 1; bit--; }
+        else {
+          int l = bit + 1 < W ? bit + 1 : W;
+          u32 v = exp_bits(e, el, bit - l + 1, l);  // bits bit .. bit-l+1, the top one set
+          int tz = ctz32(v);
+          v >>= tz; l -= tz;                         // the window ends at its lowest set bit
+          sq_left = l; pend = (int)(v >> 1); bit -= l;
+        }
+      }
+      if (sq_left > 0) op = started ? 1 : 0;         // before the first window there is nothing to square
+      else { op = started ? 2 : 3; src = pend; }
+    }
+    const bool sq_phase = built < nt ? !have2 : sq_left > 0;
+    if (!ok) op = 0;  // a failed element idles: every thread of the block runs the same number of rounds
+    if (sq_phase) {
+      if (QF_BLOCK_ANY(op == 1)) { bool k = cc_compose<N, CAP, true, true, FLAT>(G, xb, xb, false, dbits, op == 1); if (op == 1) ok = k; }
+    } else {
+      if (QF_BLOCK_ANY(op == 2)) { bool k = cc_compose<N, CAP, false, true, FLAT>(G, xb, tab + src * TE, false, dbits, op == 2); if (op == 2) ok = k; }
+    }
+    if (op == 3) { QF_UNROLL for (int i = 0; i < TE; i++) xb[i] = tab[src * TE + i]; }
+    // ---- advance
+    if (built < nt) {
+      if (!have2) {
+        if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) { tab[NT * TE + i] = xb[i]; xb[i] = tab[i]; } }  // f^2 kept, x back to f
+        have2 = true;
+      } else {
+        if (ok) { QF_UNROLL for (int i = 0; i < TE; i++) tab[built * TE + i] = xb[i]; }
+        built++;
+      }
+    } else if (sq_left > 0) {
+      sq_left--;
+    } else {
+      pend = -1;
+      started = true;
+    }
+  }
+  fr_unpack<N>(x, xb);
+  return ok && started;
+}
+
 }  // namespace cofhe

@@ -182,6 +182,37 @@ def test_fast_pow_kat_and_fixtures():
     assert ran >= 100
 
 
+def test_fast_pow_shared_sliding_windows():
+    """fr_pow_shared (what part_decrypt / decrypt / tensor x scalar run on the register path: sliding windows over the odd
+    powers) against the oracle: every exponent below 70, powers of two and their neighbours, runs of ones, random shares."""
+    t = load_golden("ref_t0.json")
+    S = FastSim(int(t["params"]["Delta"]))
+    assert S.ok()
+    fs = [I(v["f"]) for v in t["nupow"]][:4] + [I(t["params"]["h"]), I(t["pk"])]
+    n = len(fs)
+    inp = L.forms_to_limbs(fs, S.na, S.nc)
+    rng = random.Random(11)
+    exps = list(range(1, 70)) + [1 << k for k in (7, 31, 32, 33, 63, 64, 65, 95, 96, 104)]
+    exps += [(1 << k) - 1 for k in (8, 31, 32, 33, 64, 97)] + [(1 << k) + 1 for k in (31, 32, 63, 64)]
+    exps += [0x11111111111111111111, 0x8000000080000000800000008, 0xF0F0F0F0F0F0F0F0F0F0F0F0F]
+    exps += [rng.getrandbits(b) | (1 << (b - 1)) for b in (40, 64, 65, 103, 104, 105, 127, 128, 129) for _ in range(2)]
+    for e in exps:
+        el = max(1, (e.bit_length() + 31) // 32)
+        for pad in (0, 1):  # leading zero limbs as the callers pass them
+            exs = L.ints_to_limbs([e], el + pad)[:, 0].copy()
+            out = np.zeros_like(inp)
+            bail = np.zeros(n, dtype=np.uint8)
+            S.lib.hs_fast_pow(S.na, HS.P(S.absd), S.nd, S.dbits, S.nc, n, HS.P(inp), HS.P(out), HS.P(exs), len(exs), 0, HS.P(bail))
+            assert int(bail.sum()) == 0, e
+            got = L.limbs_to_forms(out, S.na, S.nc)
+            assert got == [O.power(f, e) for f in fs], hex(e)
+    # e == 0: the neutral form does not fit the register shape -> declined, as on the fixed-window path
+    exs = L.ints_to_limbs([0], 2)[:, 0].copy()
+    bail = np.zeros(n, dtype=np.uint8)
+    S.lib.hs_fast_pow(S.na, HS.P(S.absd), S.nd, S.dbits, S.nc, n, HS.P(inp), HS.P(np.zeros_like(inp)), HS.P(exs), 2, 0, HS.P(bail))
+    assert int(bail.sum()) == n
+
+
 def test_fast_flat_variant(tier):
     """the branch-free scalar Euclid rounds (hgcd32_nb; what the composition kernel runs on small batches): same accepted
     steps, same results as the reference fixtures"""
