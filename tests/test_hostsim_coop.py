@@ -131,6 +131,32 @@ def test_coop_pow(name, shape):
             assert got[i] == O.power(f[i], -es[i] if sg[i] else es[i]), i
 
 
+@pytest.mark.parametrize("name,shape", [("t0", (2, 5)), ("t1", (4, 9))])
+def test_coop_pow_shared_sliding_windows(name, shape):
+    """the sliding-window schedule of cq_pow for an exponent the launch shares: every small exponent (tables shorter than
+    8 entries, windows cut by trailing zeros), bit patterns across limb boundaries, exponent 0 (declined)"""
+    t = load_golden("ref_%s.json" % name)
+    S = CoopSim(int(t["params"]["Delta"]), *shape)
+    rng = random.Random(9)
+    h, pk = I(t["params"]["h"]), I(t["pk"])
+    f = [O.power(h, rng.getrandbits(20) + 2), pk]
+    n = len(f)
+    a = L.forms_to_limbs(f, S.na, S.nc)
+    small = list(range(1, 36)) if name == "t0" else [1, 2, 3, 5, 6, 7, 8, 11, 12, 15, 16, 17, 23, 24, 31, 32, 33]
+    big = [(1 << 31) + 1, (1 << 32) - 1, 1 << 32, (1 << 33) | 5, 0xF0F0F0F0F0F, rng.getrandbits(62) | (1 << 61)] if name == "t0" else [(1 << 32) | 9, 0xF0F0F0F0F]
+    for e in small + big:
+        for el in (2, 3):
+            ex = L.ints_to_limbs([e], el)[:, 0].copy()
+            o = np.zeros_like(a); bail = np.zeros(n, dtype=np.uint8)
+            nb = S.lib.hs_coop_pow(S.T, S.L, S.na, S.dbits, S.nc, n, HS.P(a), HS.P(o), HS.P(ex), el, 0, None, 0, HS.P(bail))
+            assert nb == 0, e
+            assert L.limbs_to_forms(o, S.na, S.nc) == [O.power(x, e) for x in f], hex(e)
+    ex = L.ints_to_limbs([0], 2)[:, 0].copy()
+    o = np.zeros_like(a); bail = np.zeros(n, dtype=np.uint8)
+    S.lib.hs_coop_pow(S.T, S.L, S.na, S.dbits, S.nc, n, HS.P(a), HS.P(o), HS.P(ex), 2, 0, None, 0, HS.P(bail))
+    assert bail.tolist() == [1] * n
+
+
 def test_coop_slow_compose_fallback(tier):
     """cq_slow_compose (coop_ops.cuh): the robust composition one lane runs for its group when the cooperative composition
     declines inside an exponentiation / table loop -- forced for every group, and for every other group of a warp"""
