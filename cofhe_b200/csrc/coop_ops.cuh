@@ -106,127 +106,71 @@ template <int T> CG_FN bool b_any(const Grp<T> &g, bool p) { return w_any<T>(g, 
 constexpr bool kCoopLoopSync = false;
 #endif
 
-// Exponentiation, one lane group per element, left to right.  ONE inlined squaring and ONE inlined composition serve the
-// table build and the main loop (state machine): the two bodies are the bulk of the kernel's code.  Two schedules feed them:
-//  * an exponent per element: fixed 2^4-ary windows (the op sequence is the same for every element, so the groups of a warp
-//    stay in lock step whatever their exponents are): table T[d] = f^d, d = 1..15, in global scratch (one SoA batch per
-//    entry), then per window four squarings and one composition with T[digit];
-//  * ONE exponent for the launch (part_decrypt, decrypt, tensor x scalar): SLIDING windows over the odd powers f, f^3, ..,
-//    f^15 (slots 0..7; slot 8 holds f^2 while the table is built) -- every group decodes the same bits, so the windows may
-//    start at the next set bit: 7 compositions and a squaring build the table instead of 13 and one, and a window costs a
-//    composition per W + 1 bits on average instead of one per W (937-bit share: 936 + 8 + ~187 operations, was 936 + 14 + 234).
-// A step that declines is redone by the group's robust composition (cq_slow_compose); if that fails too the element is
-// left to the robust redo of the whole exponentiation.
+// Exponentiation, one lane group per element, fixed 2^4-ary windows left to right (the op sequence is the same for every
+// element, so the groups of a warp stay in lock step whatever their exponents are): table T[d] = f^d, d = 1..15, in global
+// scratch (one SoA batch per entry), then per window four squarings and one composition with T[digit].  ONE inlined
+// squaring and ONE inlined composition serve the table build and the main loop (state machine): the two bodies are the
+// bulk of the kernel's code.  A step that declines kills the element (robust redo of the whole exponentiation).
 constexpr int kCoopPowW = 4;
 // the per-group body: in / out / mytab are the element batches of this form block; returns false when the element has to be
 // redone by the robust path (nothing stored then)
 template <int T, int L, int N, int CAP>
 CG_FN bool cq_pow(const Grp<T> &g, const Group<CAP> *G, int dbits, int nc, size_t n, size_t idx, bool have, const u32 *in, u32 *out, u32 *mytab, const u32 *exp, int el,
                   int per_elem, const unsigned char *expneg, int shared_neg) {
-  constexpr int W = kCoopPowW, NT = (1 << W) - 1, NO = 1 << (W - 1);
+  constexpr int W = kCoopPowW, NT = (1 << W) - 1;
   const size_t fl = (size_t)(2 * N + nc);
   FormC<L> acc, opnd, r;
   bool alive = cq_load<T, L, N>(g, acc, in, nc, n, idx) && have;
-  // ---- table slot 0 = f
+  // ---- table: T[1] = f, T[d] = T[d-1] o f
   cq_store<T, L, N>(g, acc, mytab, nc, n, idx, true);
   g_sync<T>(g);
-  bool started = false;  // acc holds a partial power (main loop)
-  // fixed windows: steps 0 .. NT-2 table build (T[2] = f^2 is a squaring, then compositions with T[1]); then per window W
-  // squarings and one composition
   const int nwin = (32 * el + W - 1) / W;
+  bool started = false;  // acc holds a partial power (main loop)
+  // steps: 0 .. NT-2 table build (composition with T[1]); then per window W squarings and one composition
   const int nsteps = (NT - 1) + nwin * (W + 1);
-  int s = 0;
-  // sliding windows (shared exponent): the top bit, the part of the table the exponent can use, the decoder's state
-  const bool slide = !per_elem;
-  int top = -1;
-  if (slide) for (int i = 0; i < el; i++) if (exp[i]) top = 32 * i + 31 - clz32(exp[i]);
-  int nt = NO;
-  if (slide && top >= 0 && top < W) { u32 v = exp[0] >> ctz32(exp[0]); nt = (int)((v + 1) >> 1); }
-  int built = 1, bit = top, sq_left = 0, pend = -1;
-  bool have2 = false;
-  QF_NOUNROLL for (;;) {
-    // ---- decide (the same for every group of the launch): squaring or composition, with which table slot, what is kept
-    bool is_comp, need = true, first = false, reload = false;
-    int slot = 0, store = -1;
-    if (slide) {
-      if (top < 0) break;
-      if (built < nt) {
-        if (!have2) { is_comp = false; store = NO; reload = true; }  // acc = f -> f^2, kept in slot NO; acc back to f
-        else { is_comp = true; slot = NO; store = built; }           // acc = f^(2 built - 1) o f^2 -> slot built
-      } else {
-        if (sq_left == 0 && pend < 0) {
-          if (bit < 0) break;
-          if (!((exp[bit >> 5] >> (bit & 31)) & 1u)) { sq_left = 1; bit--; }
-          else {
-            int l = bit + 1 < W ? bit + 1 : W;
-            int lo = bit - l + 1;
-            u64 v64 = exp[lo >> 5];
-            if ((lo >> 5) + 1 < el) v64 |= (u64)exp[(lo >> 5) + 1] << 32;
-            u32 v = (u32)(v64 >> (lo & 31)) & ((1u << l) - 1);  // bits bit .. lo, the top one set
-            int tz = ctz32(v);
-            v >>= tz; l -= tz;                                   // the window ends at its lowest set bit
-            sq_left = l; pend = (int)(v >> 1); bit -= l;
-          }
-        }
-        if (sq_left > 0) { is_comp = false; need = started; }     // before the first window there is nothing to square
-        else { is_comp = true; slot = pend; first = !started; }
-      }
-    } else {
-      if (s >= nsteps) break;
-      const bool build = s < NT - 1;
-      const int ws = build ? 0 : (s - (NT - 1)), wi = nwin - 1 - ws / (W + 1), ph = ws % (W + 1);
-      is_comp = build ? s > 0 : ph == W;
-      if (build) store = s + 1;
-      if (!build && is_comp) {
-        int b = wi * W;
-        u32 digit = (exp[(size_t)(b >> 5) * n + idx] >> (b & 31)) & (u32)NT;
-        need = digit != 0;
-        slot = digit ? (int)digit - 1 : 0;
-        first = !started && digit != 0;
-      }
-      if (!is_comp) need = build || started;
+  QF_NOUNROLL for (int s = 0; s < nsteps; s++) {
+    const bool build = s < NT - 1;
+    const int ws = build ? 0 : (s - (NT - 1)), wi = nwin - 1 - ws / (W + 1), ph = ws % (W + 1);
+    const bool is_comp = build ? s > 0 : ph == W;  // T[2] = f^2 is a squaring (a form is not composed with itself)
+    u32 digit = 0;
+    if (!build) {
+      int bit = wi * W;
+      u32 limb = per_elem ? exp[(size_t)(bit >> 5) * n + idx] : exp[bit >> 5];
+      digit = (limb >> (bit & 31)) & (u32)NT;
     }
-    // ---- execute
     if (is_comp) {
-      // windows above the exponent's top digit: nothing to do anywhere in the block
-      if (b_any<T>(g, alive && need)) {
-        cq_load<T, L, N>(g, opnd, mytab + (size_t)slot * fl * n, nc, n, idx);
-        const bool act = alive && need && !first;  // the top window: acc = T[slot]
-        bool ok = cq_compose<T, L, N, false, kCoopLoopSync>(g, r, acc, opnd, false, dbits, act);
-        if (w_any<T>(g, act && !ok)) ok = cq_slow_compose<T, L, N, CAP>(g, G, r, acc, opnd, false, act && !ok) || ok;
-        if (act) {
-          if (ok) acc = r;
-          else alive = false;
-        }
-        if (alive && need && first) { acc = opnd; started = true; }
-        if (store >= 0) {
-          cq_store<T, L, N>(g, acc, mytab + (size_t)store * fl * n, nc, n, idx, alive);
-          g_sync<T>(g);
-        }
+      const bool need = build || digit != 0;
+      // windows above the exponent's top digit: nothing to do anywhere in the warp
+      if (!b_any<T>(g, alive && need)) continue;
+      const u32 d = build ? 1u : (digit ? digit : 1u);
+      cq_load<T, L, N>(g, opnd, mytab + (size_t)(d - 1) * fl * n, nc, n, idx);
+      const bool first = !build && !started && digit != 0;  // the top digit: acc = T[digit]
+      const bool act = alive && need && !first;
+      bool ok = cq_compose<T, L, N, false, kCoopLoopSync>(g, r, acc, opnd, false, dbits, act);
+      if (w_any<T>(g, act && !ok)) ok = cq_slow_compose<T, L, N, CAP>(g, G, r, acc, opnd, false, act && !ok) || ok;
+      if (act) {
+        if (ok) acc = r;
+        else alive = false;
+      }
+      if (alive && first) { acc = opnd; started = true; }
+      if (build) {
+        cq_store<T, L, N>(g, acc, mytab + (size_t)(s + 1) * fl * n, nc, n, idx, alive);
+        g_sync<T>(g);
       }
     } else {
-      const bool act = alive && need;
-      if (b_any<T>(g, act)) {
-        bool ok = cq_compose<T, L, N, true, kCoopLoopSync>(g, r, acc, acc, false, dbits, act);
-        if (w_any<T>(g, act && !ok)) ok = cq_slow_compose<T, L, N, CAP>(g, G, r, acc, acc, true, act && !ok) || ok;
-        if (act) {
-          if (ok) acc = r;
-          else alive = false;
-        }
-        if (store >= 0) {
-          cq_store<T, L, N>(g, acc, mytab + (size_t)store * fl * n, nc, n, idx, alive);
-          g_sync<T>(g);
-        }
-        if (reload) cq_load<T, L, N>(g, acc, mytab, nc, n, idx);
+      const bool act = alive && (build || started);
+      if (!b_any<T>(g, act)) continue;
+      bool ok = cq_compose<T, L, N, true, kCoopLoopSync>(g, r, acc, acc, false, dbits, act);
+      if (w_any<T>(g, act && !ok)) ok = cq_slow_compose<T, L, N, CAP>(g, G, r, acc, acc, true, act && !ok) || ok;
+      if (act) {
+        if (ok) acc = r;
+        else alive = false;
+      }
+      if (build) {
+        cq_store<T, L, N>(g, acc, mytab + (size_t)(s + 1) * fl * n, nc, n, idx, alive);
+        g_sync<T>(g);
       }
     }
-    // ---- advance
-    if (!slide) s++;
-    else if (built < nt) {
-      if (!have2) have2 = true;
-      else built++;
-    } else if (sq_left > 0) sq_left--;
-    else pend = -1;
   }
   if (!started) alive = false;  // exponent 0 (the neutral form does not fit the working shape): robust path
   const bool inv = per_elem ? (expneg && expneg[idx]) : shared_neg != 0;

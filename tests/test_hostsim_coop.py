@@ -133,8 +133,9 @@ def test_coop_pow(name, shape):
 
 @pytest.mark.parametrize("name,shape", [("t0", (2, 5)), ("t1", (4, 9))])
 def test_coop_pow_shared_sliding_windows(name, shape):
-    """the sliding-window schedule of cq_pow for an exponent the launch shares: every small exponent (tables shorter than
-    8 entries, windows cut by trailing zeros), bit patterns across limb boundaries, exponent 0 (declined)"""
+    """cq_pow with an exponent the launch shares: every small exponent, bit patterns across limb boundaries, exponent 0
+    (declined).  (Written for a sliding-window schedule of cq_pow that was taken out again -- DESIGN.md section 9 -- and kept
+    for the fixed-window one.)"""
     t = load_golden("ref_%s.json" % name)
     S = CoopSim(int(t["params"]["Delta"]), *shape)
     rng = random.Random(9)
